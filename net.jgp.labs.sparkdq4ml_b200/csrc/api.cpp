@@ -1,0 +1,1101 @@
+// api.cpp -- the extern "C" boundary declared in include/dq4ml.h: argument checking, host/device buffer resolution,
+// kernel launches, the cross-rank sum, and the hand-off to the host solvers.  There is deliberately no CPU code path
+// for the data passes: without a CUDA device these entry points fail with DQ4ML_ERR_NO_DEVICE.
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+#include <limits>
+#include <memory>
+#include <new>
+#include <vector>
+
+#include "context.hpp"
+#include "gram.hpp"
+#include "solver.hpp"
+
+using namespace dq4ml;
+
+struct dq4ml_lr_model {
+  LrModel m;
+};
+
+namespace dq4ml {
+
+static thread_local std::string g_error;
+
+void set_error(const char* fmt, ...) {
+  char buf[1024];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof(buf), fmt, ap);
+  va_end(ap);
+  g_error = buf;
+}
+const char* get_error() { return g_error.c_str(); }
+
+namespace {
+
+int cuda_fail(cudaError_t e, const char* what) {
+  set_error("%s: %s", what, cudaGetErrorString(e));
+  if (e == cudaErrorNoDevice || e == cudaErrorInsufficientDriver) return DQ4ML_ERR_NO_DEVICE;
+  return DQ4ML_ERR_CUDA;
+}
+#define CU(call)                                       \
+  do {                                                 \
+    cudaError_t e__ = (call);                          \
+    if (e__ != cudaSuccess) return cuda_fail(e__, #call); \
+  } while (0)
+
+bool is_device_ptr(const void* p) {
+  cudaPointerAttributes at;
+  const cudaError_t e = cudaPointerGetAttributes(&at, p);
+  if (e != cudaSuccess) {
+    cudaGetLastError();
+    return false;
+  }
+  return at.type == cudaMemoryTypeDevice || at.type == cudaMemoryTypeManaged;
+}
+
+// ---- staging arena -------------------------------------------------------------------------------------------------
+struct CallScope {  // resets the arena bookkeeping at the start of every entry point
+  explicit CallScope(dq4ml_ctx* c) : ctx(c) {
+    cudaSetDevice(c->device);
+    c->arena_used = 0;
+    c->staged.clear();
+  }
+  dq4ml_ctx* ctx;
+};
+
+int arena_reserve(dq4ml_ctx* ctx, size_t total) {
+  if (total <= ctx->arena_cap) return DQ4ML_OK;
+  CU(cudaStreamSynchronize(ctx->stream));
+  if (ctx->arena != nullptr) CU(cudaFree(ctx->arena));
+  ctx->arena = nullptr;
+  ctx->arena_cap = 0;
+  const size_t cap = (total + (64u << 20)) & ~static_cast<size_t>((1u << 20) - 1);
+  CU(cudaMalloc(reinterpret_cast<void**>(&ctx->arena), cap));
+  ctx->arena_cap = cap;
+  return DQ4ML_OK;
+}
+
+size_t round256(size_t b) { return (b + 255) & ~static_cast<size_t>(255); }
+
+void* arena_take(dq4ml_ctx* ctx, size_t bytes) {
+  void* p = ctx->arena + ctx->arena_used;
+  ctx->arena_used += round256(bytes);
+  return p;
+}
+
+// Plans which of `ptrs` (with byte sizes) live on the host, reserves arena space once, then uploads them.
+struct Resolver {
+  dq4ml_ctx* ctx;
+  struct Item {
+    const void** slot;
+    size_t bytes;
+  };
+  std::vector<Item> inputs;
+  size_t extra_bytes = 0;
+  explicit Resolver(dq4ml_ctx* c) : ctx(c) {}
+  void input(const void** slot, size_t bytes) {
+    if (*slot != nullptr) inputs.push_back({slot, bytes});
+  }
+  void reserve_output(size_t bytes) { extra_bytes += round256(bytes); }
+  int run() {
+    size_t need = extra_bytes;
+    std::vector<char> on_host(inputs.size(), 0);
+    std::unordered_map<const void*, size_t> seen;
+    for (size_t i = 0; i < inputs.size(); ++i) {
+      const void* p = *inputs[i].slot;
+      if (is_device_ptr(p)) {
+        if ((reinterpret_cast<uintptr_t>(p) & 15u) != 0) {
+          set_error("device column %p is not 16-byte aligned", p);
+          return DQ4ML_ERR_INVALID;
+        }
+        continue;
+      }
+      on_host[i] = 1;
+      auto it = seen.find(p);
+      if (it == seen.end()) {
+        seen[p] = inputs[i].bytes;
+        need += round256(inputs[i].bytes);
+      } else if (inputs[i].bytes > it->second) {
+        need += round256(inputs[i].bytes);  // conservative
+        it->second = inputs[i].bytes;
+      }
+    }
+    const int rc = arena_reserve(ctx, need);
+    if (rc != DQ4ML_OK) return rc;
+    for (size_t i = 0; i < inputs.size(); ++i) {
+      if (!on_host[i]) continue;
+      const void* hp = *inputs[i].slot;
+      auto it = ctx->staged.find(hp);
+      if (it == ctx->staged.end()) {
+        void* dp = arena_take(ctx, inputs[i].bytes);
+        CU(cudaMemcpyAsync(dp, hp, inputs[i].bytes, cudaMemcpyHostToDevice, ctx->stream));
+        ctx->staged[hp] = dp;
+        *inputs[i].slot = dp;
+      } else {
+        *inputs[i].slot = it->second;  // same host column referenced twice (e.g. price as label and as DQ column)
+      }
+    }
+    return DQ4ML_OK;
+  }
+};
+
+struct OutBuf {  // an output that may live on the host: kernels write `dev`, finish() copies back
+  void* user = nullptr;
+  void* dev = nullptr;
+  bool staged = false;
+};
+OutBuf make_out(dq4ml_ctx* ctx, void* user, size_t bytes) {
+  OutBuf o;
+  o.user = user;
+  if (user == nullptr) return o;
+  if (is_device_ptr(user)) {
+    o.dev = user;
+  } else {
+    o.dev = arena_take(ctx, bytes);
+    o.staged = true;
+  }
+  return o;
+}
+
+int check_ctx(const dq4ml_ctx* ctx) {
+  if (ctx == nullptr) {
+    set_error("null ctx");
+    return DQ4ML_ERR_INVALID;
+  }
+  return DQ4ML_OK;
+}
+
+void collect_pass_time(dq4ml_ctx* ctx);
+
+// ---- cross-rank sum of the result vector sitting in ctx->scratch.result; leaves it in ctx->h_result ----------------
+int finish_result(dq4ml_ctx* ctx, int64_t count) {
+  if (static_cast<size_t>(count) > kResultDoubles) {
+    set_error("result vector too long (%lld)", static_cast<long long>(count));
+    return DQ4ML_ERR_UNSUPPORTED;
+  }
+  if (ctx->nccl != nullptr) {
+    const int rc = nccl_allreduce_device(ctx, ctx->scratch.result, count);
+    if (rc != DQ4ML_OK) return rc;
+  }
+  CU(cudaMemcpyAsync(ctx->h_result, ctx->scratch.result, sizeof(double) * count, cudaMemcpyDeviceToHost, ctx->stream));
+  CU(cudaStreamSynchronize(ctx->stream));
+  collect_pass_time(ctx);
+  if (ctx->nccl == nullptr && ctx->allreduce_cb != nullptr) {
+    if (ctx->allreduce_cb(ctx->allreduce_user, ctx->h_result, count) != 0) {
+      set_error("all-reduce callback failed");
+      return DQ4ML_ERR_COMM;
+    }
+  }
+  return DQ4ML_OK;
+}
+
+int host_allreduce(dq4ml_ctx* ctx, double* buf, int64_t count) {
+  if (count <= 0) return DQ4ML_OK;
+  if (ctx->nccl != nullptr) {
+    if (static_cast<size_t>(count) > kResultDoubles) {
+      set_error("all-reduce of %lld doubles exceeds the staging buffer", static_cast<long long>(count));
+      return DQ4ML_ERR_UNSUPPORTED;
+    }
+    CU(cudaMemcpyAsync(ctx->scratch.result, buf, sizeof(double) * count, cudaMemcpyHostToDevice, ctx->stream));
+    const int rc = nccl_allreduce_device(ctx, ctx->scratch.result, count);
+    if (rc != DQ4ML_OK) return rc;
+    CU(cudaMemcpyAsync(buf, ctx->scratch.result, sizeof(double) * count, cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+  } else if (ctx->allreduce_cb != nullptr) {
+    if (ctx->allreduce_cb(ctx->allreduce_user, buf, count) != 0) {
+      set_error("all-reduce callback failed");
+      return DQ4ML_ERR_COMM;
+    }
+  }
+  return DQ4ML_OK;
+}
+
+bool multi_rank(const dq4ml_ctx* ctx) { return ctx->nccl != nullptr || ctx->allreduce_cb != nullptr; }
+
+// ---- column table plumbing -----------------------------------------------------------------------------------------
+struct PassInputs {
+  DeviceCols cols;
+  const double* label = nullptr;
+  DeviceDq dq;
+};
+
+int gather_inputs(dq4ml_ctx* ctx, const dq4ml_columns* features, const double* label, int64_t n,
+                  const dq4ml_dq_fused* dq, PassInputs* out, size_t out_bytes, int max_cols) {
+  if (features == nullptr || n < 0 || features->n_cols < 0 || (features->n_cols > 0 && features->cols == nullptr)) {
+    set_error("bad feature table / row count");
+    return DQ4ML_ERR_INVALID;
+  }
+  if (max_cols > kMaxCols) max_cols = kMaxCols;  // DeviceCols capacity
+  if (features->n_cols > max_cols) {
+    set_error("%d feature columns: this entry point handles at most %d", features->n_cols, max_cols);
+    return DQ4ML_ERR_UNSUPPORTED;
+  }
+  out->cols.n = features->n_cols;
+  for (int j = 0; j < features->n_cols; ++j) {
+    const dq4ml_column& c = features->cols[j];
+    if (c.data == nullptr || (c.dtype != DQ4ML_I32 && c.dtype != DQ4ML_F64)) {
+      set_error("feature column %d: null data or unknown dtype %d", j, c.dtype);
+      return DQ4ML_ERR_INVALID;
+    }
+    out->cols.ptr[j] = c.data;
+    out->cols.dtype[j] = c.dtype;
+  }
+  out->label = label;
+  if (dq != nullptr) {
+    if (dq->guest == nullptr || dq->price == nullptr) {
+      set_error("fused DQ needs both guest and price columns");
+      return DQ4ML_ERR_INVALID;
+    }
+    out->dq.guest = dq->guest;
+    out->dq.price = dq->price;
+    out->dq.params = dq->params;
+  }
+  Resolver rs(ctx);
+  for (int j = 0; j < out->cols.n; ++j)
+    rs.input(&out->cols.ptr[j], static_cast<size_t>(n) * (out->cols.dtype[j] == DQ4ML_I32 ? 4 : 8));
+  rs.input(reinterpret_cast<const void**>(&out->label), static_cast<size_t>(n) * 8);
+  rs.input(reinterpret_cast<const void**>(&out->dq.guest), static_cast<size_t>(n) * 4);
+  rs.input(reinterpret_cast<const void**>(&out->dq.price), static_cast<size_t>(n) * 8);
+  rs.reserve_output(out_bytes);
+  return rs.run();
+}
+
+// ---- the aggregation passes (device inputs) -------------------------------------------------------------------------
+
+// launch_stream_pass bracketed by CUDA events on the ctx stream when pass timing is on
+cudaError_t timed_stream_pass(dq4ml_ctx* ctx, StreamOpKind op, const DeviceCols& cols, const double* label,
+                              const DeviceDq& dq, int64_t n, const void* host_consts, double* row_out) {
+  if (ctx->pass_timing) cudaEventRecord(ctx->pass_ev0, ctx->stream);
+  const cudaError_t e = launch_stream_pass(op, cols, label, dq, n, host_consts, row_out, ctx->scratch, ctx->stream,
+                                           &ctx->launches);
+  if (ctx->pass_timing) {
+    cudaEventRecord(ctx->pass_ev1, ctx->stream);
+    ctx->pass_event_pending = true;
+  }
+  return e;
+}
+
+void collect_pass_time(dq4ml_ctx* ctx) {  // call after the stream has been synchronised
+  if (!ctx->pass_event_pending) return;
+  ctx->pass_event_pending = false;
+  float ms = 0.f;
+  if (cudaEventElapsedTime(&ms, ctx->pass_ev0, ctx->pass_ev1) == cudaSuccess) {
+    ctx->pass_ms_total += ms;
+    ++ctx->pass_count;
+  }
+}
+
+// WLS moments of a small-d table via the streaming kernel; result in `out` with the public layout.
+int wls_moments_small(dq4ml_ctx* ctx, const PassInputs& in, int64_t n, double* out) {
+  const int d = in.cols.n;
+  const int b = stream_bucket(d > 0 ? d : 1);
+  const int nacc = stream_nacc(kOpWls, b);
+  cudaError_t e = timed_stream_pass(ctx, kOpWls, in.cols, in.label, in.dq, n, nullptr, nullptr);
+  if (e != cudaSuccess) return cuda_fail(e, "wls moments pass");
+  const int rc = finish_result(ctx, nacc);
+  if (rc != DQ4ML_OK) return rc;
+  const double* r = ctx->h_result;
+  out[0] = r[0];
+  out[1] = r[0];
+  out[2] = r[0];
+  out[3] = r[1];
+  out[4] = r[2];
+  for (int j = 0; j < d; ++j) {
+    out[5 + j] = r[3 + j];
+    out[5 + d + j] = r[3 + b + j];
+  }
+  const size_t tri = static_cast<size_t>(d) * (d + 1) / 2;
+  for (size_t q = 0; q < tri; ++q) out[5 + 2 * d + q] = r[3 + 2 * b + q];  // packed index is independent of the order
+  return DQ4ML_OK;
+}
+
+int wls_moments_any(dq4ml_ctx* ctx, const PassInputs& in, int64_t n, double* out) {
+  if (in.label == nullptr) {
+    set_error("label column is required");
+    return DQ4ML_ERR_INVALID;
+  }
+  if (in.cols.n <= 8) return wls_moments_small(ctx, in, n, out);
+  return gram_wls_moments(ctx, in.cols, in.label, in.dq, n, out);
+}
+
+// Summarizer, core statistics (count, mean, sample variance per column; label last) for the l-bfgs branch.
+int summarize_core(dq4ml_ctx* ctx, const PassInputs& in, int64_t n, ColumnStats* st) {
+  const int d = in.cols.n;
+  const int b = stream_bucket(d > 0 ? d : 1);
+  cudaError_t e = launch_column_heads(in.cols, in.label, b, n, ctx->scratch, ctx->stream, &ctx->launches);
+  if (e != cudaSuccess) return cuda_fail(e, "column heads");
+  std::vector<double> centres(b + 1, 0.0);
+  CU(cudaMemcpyAsync(ctx->h_result, ctx->scratch.consts, sizeof(double) * (b + 1), cudaMemcpyDeviceToHost, ctx->stream));
+  CU(cudaStreamSynchronize(ctx->stream));
+  std::copy(ctx->h_result, ctx->h_result + b + 1, centres.begin());
+  if (multi_rank(ctx)) {  // every rank must shift by the same centres for the power sums to be addable
+    int rc = host_allreduce(ctx, centres.data(), b + 1);
+    if (rc != DQ4ML_OK) return rc;
+    for (double& c : centres) c /= ctx->world > 0 ? ctx->world : 1;
+    CU(cudaMemcpyAsync(ctx->scratch.consts, centres.data(), sizeof(double) * (b + 1), cudaMemcpyHostToDevice, ctx->stream));
+  }
+  e = timed_stream_pass(ctx, kOpSummCore, in.cols, in.label, in.dq, n, nullptr, nullptr);
+  if (e != cudaSuccess) return cuda_fail(e, "summarizer pass");
+  const int rc = finish_result(ctx, stream_nacc(kOpSummCore, b));
+  if (rc != DQ4ML_OK) return rc;
+  const double* r = ctx->h_result;
+  const double cnt = r[0];
+  st->count = cnt;
+  st->mean.assign(d + 1, 0.0);
+  st->variance.assign(d + 1, 0.0);
+  for (int c = 0; c <= d; ++c) {
+    const int slot = c < d ? c : b;
+    const double s1 = r[1 + 2 * slot], s2 = r[2 + 2 * slot];
+    if (cnt > 0) {
+      st->mean[c] = centres[slot] + s1 / cnt;
+      const double m2n = s2 - s1 * s1 / cnt;
+      st->variance[c] = cnt > 1 ? std::max(m2n / (cnt - 1.0), 0.0) : 0.0;
+    }
+  }
+  return DQ4ML_OK;
+}
+
+int lsq_pass(dq4ml_ctx* ctx, const PassInputs& in, int64_t n, const double* coef, const double* fstd,
+             const double* fmean, double ystd, double ymean, bool fit_intercept, double* loss_sum, double* weight_sum,
+             double* grad_sum) {
+  const int d = in.cols.n;
+  const int b = stream_bucket(d > 0 ? d : 1);
+  LsqConsts c{};
+  double s = 0.0;
+  for (int j = 0; j < d; ++j) {
+    if (fstd[j] != 0.0) {
+      c.eff[j] = coef[j] / fstd[j];
+      s += c.eff[j] * fmean[j];
+    } else {
+      c.eff[j] = 0.0;
+    }
+  }
+  c.offset = fit_intercept ? ymean / ystd - s : 0.0;
+  c.inv_ystd = 1.0 / ystd;
+  cudaError_t e = timed_stream_pass(ctx, kOpLsq, in.cols, in.label, in.dq, n, &c, nullptr);
+  if (e != cudaSuccess) return cuda_fail(e, "loss/gradient pass");
+  const int rc = finish_result(ctx, stream_nacc(kOpLsq, b));
+  if (rc != DQ4ML_OK) return rc;
+  const double* r = ctx->h_result;
+  *loss_sum = r[0];
+  *weight_sum = r[1];
+  for (int j = 0; j < d; ++j) grad_sum[j] = fstd[j] != 0.0 ? r[2 + j] / fstd[j] : 0.0;
+  return DQ4ML_OK;
+}
+
+LrParams to_params(const dq4ml_lr_params* p) {
+  LrParams q;
+  if (p != nullptr) {
+    q.max_iter = p->max_iter;
+    q.reg_param = p->reg_param;
+    q.elastic_net = p->elastic_net_param;
+    q.tol = p->tol;
+    q.fit_intercept = p->fit_intercept != 0;
+    q.standardization = p->standardization != 0;
+    q.solver = p->solver;
+  }
+  return q;
+}
+
+int check_params(const LrParams& p) {
+  if (p.max_iter < 0 || p.reg_param < 0.0 || p.elastic_net < 0.0 || p.elastic_net > 1.0 || p.tol < 0.0 || p.solver < 0 ||
+      p.solver > 2) {
+    set_error("LinearRegression params out of range (maxIter >= 0, regParam >= 0, 0 <= elasticNetParam <= 1, tol >= 0)");
+    return DQ4ML_ERR_INVALID;
+  }
+  return DQ4ML_OK;
+}
+
+}  // namespace
+}  // namespace dq4ml
+
+// =====================================================================================================================
+extern "C" {
+
+const char* dq4ml_last_error(void) { return get_error(); }
+int dq4ml_abi_version(void) { return DQ4ML_ABI_VERSION; }
+
+int dq4ml_ctx_create(int device, dq4ml_ctx** out) {
+  if (out == nullptr) {
+    set_error("null out");
+    return DQ4ML_ERR_INVALID;
+  }
+  *out = nullptr;
+  int count = 0;
+  cudaError_t e = cudaGetDeviceCount(&count);
+  if (e != cudaSuccess || count == 0) {
+    cudaGetLastError();
+    set_error("no CUDA device available (%s); this library has no CPU fallback", e == cudaSuccess ? "device count is 0" : cudaGetErrorString(e));
+    return DQ4ML_ERR_NO_DEVICE;
+  }
+  if (device < 0 || device >= count) {
+    set_error("device %d out of range (have %d)", device, count);
+    return DQ4ML_ERR_INVALID;
+  }
+  CU(cudaSetDevice(device));
+  cudaDeviceProp prop;
+  CU(cudaGetDeviceProperties(&prop, device));
+  if (prop.major < 10) {
+    set_error("device %d is sm_%d%d; libdq4ml is built for sm_100a (B200) only", device, prop.major, prop.minor);
+    return DQ4ML_ERR_NO_DEVICE;
+  }
+  auto* ctx = new (std::nothrow) dq4ml_ctx;
+  if (ctx == nullptr) {
+    set_error("out of memory");
+    return DQ4ML_ERR_INVALID;
+  }
+  ctx->device = device;
+  ctx->sm_count = prop.multiProcessorCount;
+  auto fail = [&](cudaError_t err, const char* what) {
+    const int rc = cuda_fail(err, what);
+    dq4ml_ctx_destroy(ctx);
+    return rc;
+  };
+  if ((e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking)) != cudaSuccess) return fail(e, "stream");
+  const size_t result_b = kResultDoubles * sizeof(double), consts_b = 4096, ticket_b = 256, counters_b = 256, err_b = 256;
+  const size_t total = kPartialsBytes + result_b + consts_b + ticket_b + counters_b + err_b;
+  if ((e = cudaMalloc(reinterpret_cast<void**>(&ctx->scratch_base), total)) != cudaSuccess) return fail(e, "scratch");
+  if ((e = cudaMemsetAsync(ctx->scratch_base, 0, total, ctx->stream)) != cudaSuccess) return fail(e, "scratch memset");
+  char* p = ctx->scratch_base;
+  ctx->scratch.partials = reinterpret_cast<double*>(p);
+  ctx->scratch.partials_bytes = kPartialsBytes;
+  p += kPartialsBytes;
+  ctx->scratch.result = reinterpret_cast<double*>(p);
+  p += result_b;
+  ctx->scratch.consts = reinterpret_cast<double*>(p);
+  p += consts_b;
+  ctx->scratch.ticket = reinterpret_cast<unsigned int*>(p);
+  p += ticket_b;
+  ctx->d_counters = reinterpret_cast<unsigned long long*>(p);
+  p += counters_b;
+  ctx->d_err = reinterpret_cast<int*>(p);
+  ctx->scratch.sm_count = ctx->sm_count;
+  if ((e = cudaMallocHost(reinterpret_cast<void**>(&ctx->h_result), result_b)) != cudaSuccess) return fail(e, "pinned result");
+  if ((e = cudaEventCreate(&ctx->pass_ev0)) != cudaSuccess) return fail(e, "event");
+  if ((e = cudaEventCreate(&ctx->pass_ev1)) != cudaSuccess) return fail(e, "event");
+  if ((e = cudaStreamSynchronize(ctx->stream)) != cudaSuccess) return fail(e, "sync");
+  *out = ctx;
+  return DQ4ML_OK;
+}
+
+void dq4ml_ctx_destroy(dq4ml_ctx* ctx) {
+  if (ctx == nullptr) return;
+  cudaSetDevice(ctx->device);
+  if (ctx->stream != nullptr) cudaStreamSynchronize(ctx->stream);
+  nccl_unbind(ctx);
+  if (ctx->arena != nullptr) cudaFree(ctx->arena);
+  if (ctx->d_tile_state != nullptr) cudaFree(ctx->d_tile_state);
+  if (ctx->scratch_base != nullptr) cudaFree(ctx->scratch_base);
+  if (ctx->h_result != nullptr) cudaFreeHost(ctx->h_result);
+  if (ctx->pass_ev0 != nullptr) cudaEventDestroy(ctx->pass_ev0);
+  if (ctx->pass_ev1 != nullptr) cudaEventDestroy(ctx->pass_ev1);
+  if (ctx->stream != nullptr) cudaStreamDestroy(ctx->stream);
+  delete ctx;
+}
+
+int dq4ml_ctx_synchronize(dq4ml_ctx* ctx) {
+  if (check_ctx(ctx) != DQ4ML_OK) return DQ4ML_ERR_INVALID;
+  CU(cudaStreamSynchronize(ctx->stream));
+  return DQ4ML_OK;
+}
+
+void* dq4ml_ctx_stream(dq4ml_ctx* ctx) { return ctx != nullptr ? ctx->stream : nullptr; }
+int64_t dq4ml_ctx_launch_count(dq4ml_ctx* ctx) { return ctx != nullptr ? ctx->launches : 0; }
+
+int dq4ml_ctx_enable_pass_timing(dq4ml_ctx* ctx, int enable) {
+  if (check_ctx(ctx) != DQ4ML_OK) return DQ4ML_ERR_INVALID;
+  ctx->pass_timing = enable != 0;
+  ctx->pass_event_pending = false;
+  ctx->pass_ms_total = 0.0;
+  ctx->pass_count = 0;
+  return DQ4ML_OK;
+}
+
+int dq4ml_ctx_pass_timing(dq4ml_ctx* ctx, double* total_ms, int64_t* passes) {
+  if (check_ctx(ctx) != DQ4ML_OK) return DQ4ML_ERR_INVALID;
+  if (total_ms != nullptr) *total_ms = ctx->pass_ms_total;
+  if (passes != nullptr) *passes = ctx->pass_count;
+  return DQ4ML_OK;
+}
+
+int dq4ml_nccl_unique_id(void* id128) {
+  if (id128 == nullptr) {
+    set_error("null id buffer");
+    return DQ4ML_ERR_INVALID;
+  }
+  return nccl_unique_id(id128);
+}
+
+int dq4ml_ctx_init_nccl(dq4ml_ctx* ctx, const void* id128, int rank, int world_size) {
+  if (check_ctx(ctx) != DQ4ML_OK || id128 == nullptr) {
+    set_error("null ctx or id");
+    return DQ4ML_ERR_INVALID;
+  }
+  return nccl_bind(ctx, id128, rank, world_size);
+}
+
+int dq4ml_ctx_set_allreduce(dq4ml_ctx* ctx, dq4ml_allreduce_fn fn, void* user) {
+  if (check_ctx(ctx) != DQ4ML_OK) return DQ4ML_ERR_INVALID;
+  ctx->allreduce_cb = fn;
+  ctx->allreduce_user = user;
+  return DQ4ML_OK;
+}
+
+int dq4ml_ctx_allreduce(dq4ml_ctx* ctx, double* buf, int64_t count) {
+  if (check_ctx(ctx) != DQ4ML_OK || (buf == nullptr && count > 0) || count < 0) {
+    set_error("bad all-reduce arguments");
+    return DQ4ML_ERR_INVALID;
+  }
+  cudaSetDevice(ctx->device);
+  return host_allreduce(ctx, buf, count);
+}
+
+int dq4ml_device_alloc(dq4ml_ctx* ctx, int64_t bytes, void** out) {
+  if (check_ctx(ctx) != DQ4ML_OK || out == nullptr || bytes < 0) {
+    set_error("bad alloc arguments");
+    return DQ4ML_ERR_INVALID;
+  }
+  CU(cudaSetDevice(ctx->device));
+  CU(cudaMalloc(out, static_cast<size_t>(bytes > 0 ? bytes : 1)));
+  return DQ4ML_OK;
+}
+int dq4ml_device_free(dq4ml_ctx* ctx, void* p) {
+  if (check_ctx(ctx) != DQ4ML_OK) return DQ4ML_ERR_INVALID;
+  CU(cudaSetDevice(ctx->device));
+  CU(cudaStreamSynchronize(ctx->stream));
+  CU(cudaFree(p));
+  return DQ4ML_OK;
+}
+int dq4ml_host_alloc_pinned(int64_t bytes, void** out) {
+  if (out == nullptr || bytes < 0) {
+    set_error("bad alloc arguments");
+    return DQ4ML_ERR_INVALID;
+  }
+  CU(cudaMallocHost(out, static_cast<size_t>(bytes > 0 ? bytes : 1)));
+  return DQ4ML_OK;
+}
+int dq4ml_host_free_pinned(void* p) {
+  CU(cudaFreeHost(p));
+  return DQ4ML_OK;
+}
+int dq4ml_memcpy(dq4ml_ctx* ctx, void* dst, const void* src, int64_t bytes) {
+  if (check_ctx(ctx) != DQ4ML_OK || bytes < 0 || (bytes > 0 && (dst == nullptr || src == nullptr))) {
+    set_error("bad memcpy arguments");
+    return DQ4ML_ERR_INVALID;
+  }
+  CU(cudaSetDevice(ctx->device));
+  CU(cudaMemcpyAsync(dst, src, static_cast<size_t>(bytes), cudaMemcpyDefault, ctx->stream));
+  CU(cudaStreamSynchronize(ctx->stream));
+  return DQ4ML_OK;
+}
+
+// ------------------------------------------------------------------------------------------------------------ DQ rules
+
+dq4ml_dq_params dq4ml_dq_params_default(void) {
+  dq4ml_dq_params p;
+  p.min_price = 20.0;  // MinimumPriceDataQualityService.MIN_PRICE
+  p.min_guest = 14;    // PriceCorrelationDataQualityService.checkPriceRange
+  p.max_price = 90.0;
+  return p;
+}
+
+double dq4ml_check_minimum_price(double price) {
+  if (price < 20) return -1;
+  return price;
+}
+
+double dq4ml_check_price_range(double price, int32_t guest) {
+  if (guest < 14 && price > 90) return -1;
+  return price;
+}
+
+int dq4ml_udf_minimumPriceRule(dq4ml_ctx* ctx, const double* price, const uint8_t* price_valid, int64_t n, double* out,
+                               const dq4ml_dq_params* params) {
+  if (check_ctx(ctx) != DQ4ML_OK) return DQ4ML_ERR_INVALID;
+  if (n < 0 || (n > 0 && (price == nullptr || out == nullptr))) {
+    set_error("minimumPriceRule: null column or negative n");
+    return DQ4ML_ERR_INVALID;
+  }
+  if (n == 0) return DQ4ML_OK;
+  CallScope scope(ctx);
+  const dq4ml_dq_params p = params != nullptr ? *params : dq4ml_dq_params_default();
+  Resolver rs(ctx);
+  rs.input(reinterpret_cast<const void**>(&price), static_cast<size_t>(n) * 8);
+  rs.input(reinterpret_cast<const void**>(&price_valid), static_cast<size_t>(n));
+  rs.reserve_output(static_cast<size_t>(n) * 8);
+  int rc = rs.run();
+  if (rc != DQ4ML_OK) return rc;
+  OutBuf ob = make_out(ctx, out, static_cast<size_t>(n) * 8);
+  CU(cudaMemsetAsync(ctx->d_err, 0, sizeof(int), ctx->stream));
+  cudaError_t e = launch_udf_min_price(price, price_valid, n, static_cast<double*>(ob.dev), p, ctx->d_err, ctx->stream,
+                                       &ctx->launches);
+  if (e != cudaSuccess) return cuda_fail(e, "minimumPriceRule kernel");
+  int flag = 0;
+  CU(cudaMemcpyAsync(&flag, ctx->d_err, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+  if (ob.staged) CU(cudaMemcpyAsync(out, ob.dev, static_cast<size_t>(n) * 8, cudaMemcpyDeviceToHost, ctx->stream));
+  CU(cudaStreamSynchronize(ctx->stream));
+  if (flag != 0) {
+    set_error("minimumPriceRule: null price (the reference's MinimumPriceDataQualityUdf.call throws NullPointerException)");
+    return DQ4ML_ERR_NULL_VALUE;
+  }
+  return DQ4ML_OK;
+}
+
+int dq4ml_udf_priceCorrelationRule(dq4ml_ctx* ctx, const double* price, const int32_t* guest, const uint8_t* price_valid,
+                                   const uint8_t* guest_valid, int64_t n, double* out, const dq4ml_dq_params* params) {
+  if (check_ctx(ctx) != DQ4ML_OK) return DQ4ML_ERR_INVALID;
+  if (n < 0 || (n > 0 && (price == nullptr || guest == nullptr || out == nullptr))) {
+    set_error("priceCorrelationRule: null column or negative n");
+    return DQ4ML_ERR_INVALID;
+  }
+  if (n == 0) return DQ4ML_OK;
+  CallScope scope(ctx);
+  const dq4ml_dq_params p = params != nullptr ? *params : dq4ml_dq_params_default();
+  Resolver rs(ctx);
+  rs.input(reinterpret_cast<const void**>(&price), static_cast<size_t>(n) * 8);
+  rs.input(reinterpret_cast<const void**>(&guest), static_cast<size_t>(n) * 4);
+  rs.input(reinterpret_cast<const void**>(&price_valid), static_cast<size_t>(n));
+  rs.input(reinterpret_cast<const void**>(&guest_valid), static_cast<size_t>(n));
+  rs.reserve_output(static_cast<size_t>(n) * 8);
+  int rc = rs.run();
+  if (rc != DQ4ML_OK) return rc;
+  OutBuf ob = make_out(ctx, out, static_cast<size_t>(n) * 8);
+  cudaError_t e = launch_udf_price_corr(price, guest, price_valid, guest_valid, n, static_cast<double*>(ob.dev), p,
+                                        ctx->stream, &ctx->launches);
+  if (e != cudaSuccess) return cuda_fail(e, "priceCorrelationRule kernel");
+  if (ob.staged) CU(cudaMemcpyAsync(out, ob.dev, static_cast<size_t>(n) * 8, cudaMemcpyDeviceToHost, ctx->stream));
+  CU(cudaStreamSynchronize(ctx->stream));
+  return DQ4ML_OK;
+}
+
+int dq4ml_dq_filter(dq4ml_ctx* ctx, const int32_t* guest, const double* price, int64_t n, const dq4ml_dq_params* params,
+                    int32_t* guest_out, double* price_out, int64_t* n_out, int64_t* n_after_rule1) {
+  if (check_ctx(ctx) != DQ4ML_OK) return DQ4ML_ERR_INVALID;
+  if (n < 0 || n_out == nullptr || (n > 0 && (guest == nullptr || price == nullptr || guest_out == nullptr || price_out == nullptr))) {
+    set_error("dq_filter: null column / output or negative n");
+    return DQ4ML_ERR_INVALID;
+  }
+  if (n > 0 && (static_cast<const void*>(guest) == static_cast<const void*>(guest_out) ||
+                static_cast<const void*>(price) == static_cast<const void*>(price_out))) {
+    set_error("dq_filter: in-place compaction is not supported");
+    return DQ4ML_ERR_INVALID;
+  }
+  *n_out = 0;
+  if (n_after_rule1 != nullptr) *n_after_rule1 = 0;
+  if (n == 0) return DQ4ML_OK;
+  CallScope scope(ctx);
+  const dq4ml_dq_params p = params != nullptr ? *params : dq4ml_dq_params_default();
+  const size_t need_state = dq_filter_state_bytes(n);
+  if (need_state > ctx->tile_state_cap) {
+    CU(cudaStreamSynchronize(ctx->stream));
+    if (ctx->d_tile_state != nullptr) CU(cudaFree(ctx->d_tile_state));
+    ctx->d_tile_state = nullptr;
+    ctx->tile_state_cap = 0;
+    CU(cudaMalloc(reinterpret_cast<void**>(&ctx->d_tile_state), need_state));
+    ctx->tile_state_cap = need_state;
+  }
+  Resolver rs(ctx);
+  rs.input(reinterpret_cast<const void**>(&guest), static_cast<size_t>(n) * 4);
+  rs.input(reinterpret_cast<const void**>(&price), static_cast<size_t>(n) * 8);
+  rs.reserve_output(static_cast<size_t>(n) * 4);
+  rs.reserve_output(static_cast<size_t>(n) * 8);
+  int rc = rs.run();
+  if (rc != DQ4ML_OK) return rc;
+  OutBuf og = make_out(ctx, guest_out, static_cast<size_t>(n) * 4);
+  OutBuf op = make_out(ctx, price_out, static_cast<size_t>(n) * 8);
+  cudaError_t e = launch_dq_filter(guest, price, n, p, static_cast<int32_t*>(og.dev), static_cast<double*>(op.dev),
+                                   ctx->d_tile_state, ctx->d_counters, ctx->stream, &ctx->launches);
+  if (e != cudaSuccess) return cuda_fail(e, "dq_filter kernel");
+  unsigned long long counts[2] = {0, 0};
+  CU(cudaMemcpyAsync(counts, ctx->d_counters, sizeof(counts), cudaMemcpyDeviceToHost, ctx->stream));
+  CU(cudaStreamSynchronize(ctx->stream));
+  *n_out = static_cast<int64_t>(counts[0]);
+  if (n_after_rule1 != nullptr) *n_after_rule1 = static_cast<int64_t>(counts[1]);
+  if (og.staged && counts[0] > 0) CU(cudaMemcpyAsync(guest_out, og.dev, counts[0] * 4, cudaMemcpyDeviceToHost, ctx->stream));
+  if (op.staged && counts[0] > 0) CU(cudaMemcpyAsync(price_out, op.dev, counts[0] * 8, cudaMemcpyDeviceToHost, ctx->stream));
+  CU(cudaStreamSynchronize(ctx->stream));
+  return DQ4ML_OK;
+}
+
+// ------------------------------------------------------------------------------------------------------------ LinearRegression
+
+dq4ml_lr_params dq4ml_lr_params_default(void) {
+  dq4ml_lr_params p;
+  p.max_iter = 100;
+  p.reg_param = 0.0;
+  p.elastic_net_param = 0.0;
+  p.tol = 1e-6;
+  p.fit_intercept = 1;
+  p.standardization = 1;
+  p.solver = DQ4ML_SOLVER_AUTO;
+  return p;
+}
+
+int64_t dq4ml_wls_moments_len(int32_t d) { return d < 0 ? 0 : 5 + 2 * static_cast<int64_t>(d) + static_cast<int64_t>(d) * (d + 1) / 2; }
+int64_t dq4ml_summary_len(int32_t d) { return d < 0 ? 0 : 3 + 7 * (static_cast<int64_t>(d) + 1); }
+
+int dq4ml_wls_moments(dq4ml_ctx* ctx, const dq4ml_columns* features, const double* label, int64_t n,
+                      const dq4ml_dq_fused* dq, double* out) {
+  if (check_ctx(ctx) != DQ4ML_OK) return DQ4ML_ERR_INVALID;
+  if (out == nullptr || label == nullptr) {
+    set_error("wls_moments: null label or output");
+    return DQ4ML_ERR_INVALID;
+  }
+  CallScope scope(ctx);
+  PassInputs in;
+  int rc = gather_inputs(ctx, features, label, n, dq, &in, 0, 4096);
+  if (rc != DQ4ML_OK) return rc;
+  return wls_moments_any(ctx, in, n, out);
+}
+
+int dq4ml_wls_solve(const double* moments, int32_t d, const dq4ml_lr_params* params, dq4ml_lr_model** out) {
+  if (moments == nullptr || out == nullptr || d < 0) {
+    set_error("wls_solve: null moments / out or negative d");
+    return DQ4ML_ERR_INVALID;
+  }
+  *out = nullptr;
+  const LrParams p = to_params(params ? params : nullptr);
+  dq4ml_lr_params defaults = dq4ml_lr_params_default();
+  const LrParams q = params ? p : to_params(&defaults);
+  if (check_params(q) != DQ4ML_OK) return DQ4ML_ERR_INVALID;
+  try {
+    auto* m = new dq4ml_lr_model;
+    m->m = wls_fit_from_moments(moments, d, q);
+    *out = m;
+    return DQ4ML_OK;
+  } catch (const SolveError& e) {
+    set_error("%s", e.what.c_str());
+    return e.code;
+  } catch (const std::exception& e) {
+    set_error("wls_solve: %s", e.what());
+    return DQ4ML_ERR_INVALID;
+  }
+}
+
+int dq4ml_summarize(dq4ml_ctx* ctx, const dq4ml_columns* features, const double* label, int64_t n,
+                    const dq4ml_dq_fused* dq, double* out) {
+  if (check_ctx(ctx) != DQ4ML_OK) return DQ4ML_ERR_INVALID;
+  if (out == nullptr || label == nullptr) {
+    set_error("summarize: null label or output");
+    return DQ4ML_ERR_INVALID;
+  }
+  CallScope scope(ctx);
+  PassInputs in;
+  int rc = gather_inputs(ctx, features, label, n, dq, &in, 0, 4096);
+  if (rc != DQ4ML_OK) return rc;
+  const int d = in.cols.n;
+  // every column (features, then the label) goes through the full summarizer in groups of four
+  std::vector<const void*> ptrs;
+  std::vector<int> dtypes;
+  for (int j = 0; j < d; ++j) {
+    ptrs.push_back(in.cols.ptr[j]);
+    dtypes.push_back(in.cols.dtype[j]);
+  }
+  ptrs.push_back(in.label);
+  dtypes.push_back(DQ4ML_F64);
+  const int total = d + 1;
+  double count = 0.0;
+  for (int c0 = 0; c0 < total; c0 += 4) {
+    DeviceCols g;
+    g.n = std::min(4, total - c0);
+    for (int j = 0; j < g.n; ++j) {
+      g.ptr[j] = ptrs[c0 + j];
+      g.dtype[j] = dtypes[c0 + j];
+    }
+    const int b = stream_bucket(g.n);
+    cudaError_t e = launch_column_heads(g, nullptr, b, n, ctx->scratch, ctx->stream, &ctx->launches);
+    if (e != cudaSuccess) return cuda_fail(e, "column heads");
+    std::vector<double> centres(b, 0.0);
+    CU(cudaMemcpyAsync(ctx->h_result, ctx->scratch.consts, sizeof(double) * b, cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    std::copy(ctx->h_result, ctx->h_result + b, centres.begin());
+    if (multi_rank(ctx)) {
+      rc = host_allreduce(ctx, centres.data(), b);
+      if (rc != DQ4ML_OK) return rc;
+      for (double& c : centres) c /= ctx->world > 0 ? ctx->world : 1;
+      CU(cudaMemcpyAsync(ctx->scratch.consts, centres.data(), sizeof(double) * b, cudaMemcpyHostToDevice, ctx->stream));
+    }
+    e = launch_stream_pass(kOpSummFull, g, nullptr, in.dq, n, nullptr, nullptr, ctx->scratch, ctx->stream, &ctx->launches);
+    if (e != cudaSuccess) return cuda_fail(e, "summarizer pass");
+    const int nacc = stream_nacc(kOpSummFull, b);
+    std::vector<double> r(nacc);
+    if (!multi_rank(ctx)) {
+      rc = finish_result(ctx, nacc);
+      if (rc != DQ4ML_OK) return rc;
+      std::copy(ctx->h_result, ctx->h_result + nacc, r.begin());
+    } else {
+      // min / max are not sums: gather every rank's vector through a zero-padded sum, then fold on the host
+      CU(cudaMemcpyAsync(ctx->h_result, ctx->scratch.result, sizeof(double) * nacc, cudaMemcpyDeviceToHost, ctx->stream));
+      CU(cudaStreamSynchronize(ctx->stream));
+      const int world = ctx->world > 0 ? ctx->world : 1;
+      std::vector<double> all(static_cast<size_t>(nacc) * world, 0.0);
+      std::copy(ctx->h_result, ctx->h_result + nacc, all.begin() + static_cast<size_t>(ctx->rank) * nacc);
+      rc = host_allreduce(ctx, all.data(), static_cast<int64_t>(all.size()));
+      if (rc != DQ4ML_OK) return rc;
+      for (int k = 0; k < nacc; ++k) {
+        const int kind = k == 0 ? 0 : ((k - 1) % 7 == 2 ? 1 : ((k - 1) % 7 == 3 ? 2 : 0));
+        double v = all[k];
+        for (int w = 1; w < world; ++w) {
+          const double o = all[static_cast<size_t>(w) * nacc + k];
+          v = kind == 0 ? v + o : (kind == 1 ? ((v != v || o != o) ? v + o : std::min(v, o)) : ((v != v || o != o) ? v + o : std::max(v, o)));
+        }
+        r[k] = v;
+      }
+    }
+    count = r[0];
+    for (int j = 0; j < g.n; ++j) {
+      const double* a = &r[1 + 7 * j];
+      double* o = out + 3 + 7 * (c0 + j);
+      if (count > 0) {
+        o[0] = centres[j] + a[0] / count;
+        const double m2n = a[1] - a[0] * a[0] / count;
+        o[1] = count > 1 ? std::max(m2n / (count - 1.0), 0.0) : 0.0;
+        o[2] = a[2];
+        o[3] = a[3];
+      } else {
+        o[0] = o[1] = o[2] = o[3] = 0.0;
+      }
+      o[4] = a[4];
+      o[5] = a[5];
+      o[6] = std::sqrt(a[6]);
+    }
+  }
+  out[0] = out[1] = out[2] = count;
+  return DQ4ML_OK;
+}
+
+int dq4ml_lsq_loss_grad(dq4ml_ctx* ctx, const dq4ml_columns* features, const double* label, int64_t n,
+                        const dq4ml_dq_fused* dq, const double* coef, const double* features_std,
+                        const double* features_mean, double label_std, double label_mean, int fit_intercept, double* out) {
+  if (check_ctx(ctx) != DQ4ML_OK) return DQ4ML_ERR_INVALID;
+  if (out == nullptr || label == nullptr || features == nullptr ||
+      (features->n_cols > 0 && (coef == nullptr || features_std == nullptr || features_mean == nullptr))) {
+    set_error("lsq_loss_grad: null argument");
+    return DQ4ML_ERR_INVALID;
+  }
+  CallScope scope(ctx);
+  PassInputs in;
+  int rc = gather_inputs(ctx, features, label, n, dq, &in, 0, kMaxCols);
+  if (rc != DQ4ML_OK) return rc;
+  return lsq_pass(ctx, in, n, coef, features_std, features_mean, label_std, label_mean, fit_intercept != 0, &out[0],
+                  &out[1], out + 2);
+}
+
+int dq4ml_linreg_fit(dq4ml_ctx* ctx, const dq4ml_columns* features, const double* label, int64_t n,
+                     const dq4ml_lr_params* params, const dq4ml_dq_fused* dq, dq4ml_lr_model** out) {
+  if (check_ctx(ctx) != DQ4ML_OK) return DQ4ML_ERR_INVALID;
+  if (out == nullptr || label == nullptr || features == nullptr) {
+    set_error("linreg_fit: null argument");
+    return DQ4ML_ERR_INVALID;
+  }
+  *out = nullptr;
+  dq4ml_lr_params defaults = dq4ml_lr_params_default();
+  const LrParams p = to_params(params != nullptr ? params : &defaults);
+  if (check_params(p) != DQ4ML_OK) return DQ4ML_ERR_INVALID;
+  CallScope scope(ctx);
+  const int d = features->n_cols;
+  // LinearRegression.train: squared-error loss goes to WeightedLeastSquares when solver is normal, or auto with
+  // numFeatures <= WeightedLeastSquares.MAX_NUM_FEATURES (4096); otherwise the summarizer + L-BFGS/OWL-QN branch.
+  const bool wls = p.solver == DQ4ML_SOLVER_NORMAL || (p.solver == DQ4ML_SOLVER_AUTO && d <= 4096);
+  PassInputs in;
+  int rc = gather_inputs(ctx, features, label, n, dq, &in, 0, wls ? 4096 : kMaxCols);
+  if (rc != DQ4ML_OK) return rc;
+  try {
+    auto model = std::make_unique<dq4ml_lr_model>();
+    if (wls) {
+      std::vector<double> mom(static_cast<size_t>(dq4ml_wls_moments_len(d)));
+      rc = wls_moments_any(ctx, in, n, mom.data());
+      if (rc != DQ4ML_OK) return rc;
+      model->m = wls_fit_from_moments(mom.data(), d, p);
+    } else {
+      ColumnStats st;
+      rc = summarize_core(ctx, in, n, &st);
+      if (rc != DQ4ML_OK) return rc;
+      int pass_rc = DQ4ML_OK;
+      LsqPassFn pass = [&](const Vec& coef, const Vec& fstd, const Vec& fmean, double ystd, double ymean,
+                           double& loss_sum, double& weight_sum, Vec& grad_sum) {
+        grad_sum.assign(d, 0.0);
+        const int r = lsq_pass(ctx, in, n, coef.data(), fstd.data(), fmean.data(), ystd, ymean, p.fit_intercept,
+                               &loss_sum, &weight_sum, grad_sum.data());
+        if (r != DQ4ML_OK) {
+          pass_rc = r;
+          throw SolveError{r, get_error()};
+        }
+      };
+      model->m = lbfgs_path_fit(st, d, p, pass);
+    }
+    *out = model.release();
+    return DQ4ML_OK;
+  } catch (const SolveError& e) {
+    set_error("%s", e.what.c_str());
+    return e.code;
+  } catch (const std::exception& e) {
+    set_error("linreg_fit: %s", e.what());
+    return DQ4ML_ERR_INVALID;
+  }
+}
+
+int32_t dq4ml_linreg_model_num_features(const dq4ml_lr_model* m) { return m ? static_cast<int32_t>(m->m.coefficients.size()) : 0; }
+int dq4ml_linreg_model_coefficients(const dq4ml_lr_model* m, double* coef) {
+  if (m == nullptr || (coef == nullptr && !m->m.coefficients.empty())) {
+    set_error("null model / buffer");
+    return DQ4ML_ERR_INVALID;
+  }
+  std::copy(m->m.coefficients.begin(), m->m.coefficients.end(), coef);
+  return DQ4ML_OK;
+}
+double dq4ml_linreg_model_intercept(const dq4ml_lr_model* m) { return m ? m->m.intercept : std::numeric_limits<double>::quiet_NaN(); }
+int32_t dq4ml_linreg_model_total_iterations(const dq4ml_lr_model* m) {
+  return m ? static_cast<int32_t>(m->m.objective_history.size()) : 0;  // Spark 2.4.4: totalIterations = objectiveHistory.length
+}
+int dq4ml_linreg_model_objective_history(const dq4ml_lr_model* m, double* hist, int32_t cap) {
+  if (m == nullptr || (hist == nullptr && cap > 0)) {
+    set_error("null model / buffer");
+    return DQ4ML_ERR_INVALID;
+  }
+  const int32_t len = static_cast<int32_t>(m->m.objective_history.size());
+  for (int32_t i = 0; i < len && i < cap; ++i) hist[i] = m->m.objective_history[i];
+  return len;
+}
+int32_t dq4ml_linreg_model_data_passes(const dq4ml_lr_model* m) { return m ? m->m.data_passes : 0; }
+int64_t dq4ml_linreg_model_num_rows(const dq4ml_lr_model* m) { return m ? m->m.num_rows : 0; }
+const char* dq4ml_linreg_model_solver_used(const dq4ml_lr_model* m) { return m ? m->m.solver_used.c_str() : ""; }
+
+double dq4ml_linreg_predict1(const dq4ml_lr_model* m, const double* x) {
+  if (m == nullptr || (x == nullptr && !m->m.coefficients.empty())) return std::numeric_limits<double>::quiet_NaN();
+  double s = 0.0;  // BLAS.dot(features, coefficients) + intercept
+  for (size_t j = 0; j < m->m.coefficients.size(); ++j) s += x[j] * m->m.coefficients[j];
+  return s + m->m.intercept;
+}
+
+void dq4ml_linreg_model_destroy(dq4ml_lr_model* m) { delete m; }
+
+int dq4ml_linreg_model_create(const double* coef, int32_t d, double intercept, dq4ml_lr_model** out) {
+  if (out == nullptr || d < 0 || (d > 0 && coef == nullptr)) {
+    set_error("model_create: bad arguments");
+    return DQ4ML_ERR_INVALID;
+  }
+  auto* m = new dq4ml_lr_model;
+  m->m.coefficients.assign(coef, coef + d);
+  m->m.intercept = intercept;
+  m->m.objective_history = {0.0};
+  m->m.solver_used = "given";
+  *out = m;
+  return DQ4ML_OK;
+}
+
+static int eval_common(dq4ml_ctx* ctx, const dq4ml_lr_model* m, const dq4ml_columns* features, const double* label,
+                       int64_t n, const dq4ml_dq_fused* dq, int mode, double* row_out_user, double* sums) {
+  if (m == nullptr || features == nullptr) {
+    set_error("null model / features");
+    return DQ4ML_ERR_INVALID;
+  }
+  if (features->n_cols != static_cast<int>(m->m.coefficients.size())) {
+    set_error("feature table has %d columns, model has %zu coefficients", features->n_cols, m->m.coefficients.size());
+    return DQ4ML_ERR_INVALID;
+  }
+  CallScope scope(ctx);
+  PassInputs in;
+  int rc = gather_inputs(ctx, features, label, n, dq, &in, row_out_user != nullptr ? static_cast<size_t>(n) * 8 : 0, kMaxCols);
+  if (rc != DQ4ML_OK) return rc;
+  OutBuf ob = make_out(ctx, row_out_user, static_cast<size_t>(n) * 8);
+  EvalConsts c{};
+  for (int j = 0; j < in.cols.n; ++j) c.coef[j] = m->m.coefficients[j];
+  c.intercept = m->m.intercept;
+  c.mode = mode;
+  cudaError_t e = launch_stream_pass(kOpEval, in.cols, in.label, in.dq, n, &c, static_cast<double*>(ob.dev), ctx->scratch,
+                                     ctx->stream, &ctx->launches);
+  if (e != cudaSuccess) return cuda_fail(e, "predict/evaluate pass");
+  if (ob.staged && n > 0) CU(cudaMemcpyAsync(row_out_user, ob.dev, static_cast<size_t>(n) * 8, cudaMemcpyDeviceToHost, ctx->stream));
+  rc = finish_result(ctx, 5);
+  if (rc != DQ4ML_OK) return rc;
+  if (sums != nullptr) std::copy(ctx->h_result, ctx->h_result + 5, sums);
+  return DQ4ML_OK;
+}
+
+int dq4ml_linreg_transform(dq4ml_ctx* ctx, const dq4ml_lr_model* m, const dq4ml_columns* features, int64_t n,
+                           double* prediction) {
+  if (check_ctx(ctx) != DQ4ML_OK) return DQ4ML_ERR_INVALID;
+  if (prediction == nullptr && n > 0) {
+    set_error("transform: null prediction buffer");
+    return DQ4ML_ERR_INVALID;
+  }
+  // transform is per-rank: no cross-rank sum is wanted for the side statistics
+  dq4ml::NcclBinding* saved_nccl = ctx->nccl;
+  dq4ml_allreduce_fn saved_cb = ctx->allreduce_cb;
+  ctx->nccl = nullptr;
+  ctx->allreduce_cb = nullptr;
+  const int rc = eval_common(ctx, m, features, nullptr, n, nullptr, 0, prediction, nullptr);
+  ctx->nccl = saved_nccl;
+  ctx->allreduce_cb = saved_cb;
+  return rc;
+}
+
+int dq4ml_linreg_evaluate(dq4ml_ctx* ctx, const dq4ml_lr_model* m, const dq4ml_columns* features, const double* label,
+                          int64_t n, const dq4ml_dq_fused* dq, int fit_intercept, double* metrics, double* residuals) {
+  if (check_ctx(ctx) != DQ4ML_OK) return DQ4ML_ERR_INVALID;
+  if (metrics == nullptr || label == nullptr) {
+    set_error("evaluate: null label / metrics");
+    return DQ4ML_ERR_INVALID;
+  }
+  double s[5];
+  const int rc = eval_common(ctx, m, features, label, n, dq, 1, residuals, s);
+  if (rc != DQ4ML_OK) return rc;
+  const double cnt = s[0], ss_err = s[1], sy = s[2], syy = s[3], sabs = s[4];
+  for (int k = 0; k < 5; ++k) metrics[k] = s[k];
+  const double mse = cnt > 0 ? ss_err / cnt : 0.0;
+  const double ss_tot = fit_intercept ? syy - (cnt > 0 ? sy * sy / cnt : 0.0) : syy;
+  metrics[5] = std::sqrt(mse);          // rootMeanSquaredError
+  metrics[6] = 1.0 - ss_err / ss_tot;   // r2
+  metrics[7] = mse;
+  metrics[8] = cnt > 0 ? sabs / cnt : 0.0;
+  return DQ4ML_OK;
+}
+
+// ------------------------------------------------------------------------------------------------------------ synthetic data
+
+int dq4ml_synth_generate(dq4ml_ctx* ctx, const dq4ml_synth_params* p, int64_t row0, int64_t n, int32_t* guest,
+                         double* price, double* extra, int64_t extra_stride) {
+  if (check_ctx(ctx) != DQ4ML_OK) return DQ4ML_ERR_INVALID;
+  if (p == nullptr || n < 0 || row0 < 0 || p->d < 1 || (n > 0 && (guest == nullptr || price == nullptr)) ||
+      (p->d > 1 && extra != nullptr && extra_stride < n)) {
+    set_error("synth_generate: bad arguments");
+    return DQ4ML_ERR_INVALID;
+  }
+  if (n > 0 && (!is_device_ptr(guest) || !is_device_ptr(price) || (extra != nullptr && !is_device_ptr(extra)))) {
+    set_error("synth_generate writes device memory only");
+    return DQ4ML_ERR_INVALID;
+  }
+  CU(cudaSetDevice(ctx->device));
+  cudaError_t e = launch_synth(*p, row0, n, guest, price, extra, extra_stride, ctx->stream, &ctx->launches);
+  if (e != cudaSuccess) return cuda_fail(e, "synth kernel");
+  CU(cudaStreamSynchronize(ctx->stream));
+  return DQ4ML_OK;
+}
+
+int dq4ml_rows_digest(dq4ml_ctx* ctx, const int32_t* guest, const double* price, int64_t n, uint64_t seed, uint64_t* out) {
+  if (check_ctx(ctx) != DQ4ML_OK) return DQ4ML_ERR_INVALID;
+  if (out == nullptr || n < 0 || (n > 0 && (guest == nullptr || price == nullptr))) {
+    set_error("rows_digest: bad arguments");
+    return DQ4ML_ERR_INVALID;
+  }
+  CallScope scope(ctx);
+  Resolver rs(ctx);
+  rs.input(reinterpret_cast<const void**>(&guest), static_cast<size_t>(n) * 4);
+  rs.input(reinterpret_cast<const void**>(&price), static_cast<size_t>(n) * 8);
+  int rc = rs.run();
+  if (rc != DQ4ML_OK) return rc;
+  cudaError_t e = launch_rows_digest(guest, price, n, seed, ctx->d_counters, ctx->stream, &ctx->launches);
+  if (e != cudaSuccess) return cuda_fail(e, "digest kernel");
+  unsigned long long h[2];
+  CU(cudaMemcpyAsync(h, ctx->d_counters, sizeof(h), cudaMemcpyDeviceToHost, ctx->stream));
+  CU(cudaStreamSynchronize(ctx->stream));
+  out[0] = h[0];
+  out[1] = h[1];
+  return DQ4ML_OK;
+}
+
+}  // extern "C"

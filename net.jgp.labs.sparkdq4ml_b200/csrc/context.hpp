@@ -1,0 +1,65 @@
+// context.hpp -- dq4ml_ctx: one CUDA device, one stream, scratch, a grow-only staging arena for host inputs, and the
+// (optional) binding to the other ranks.
+#pragma once
+
+#include <cuda_runtime.h>
+
+#include <cstdarg>
+#include <cstdint>
+#include <cstdio>
+#include <string>
+#include <unordered_map>
+
+#include "../../include/dq4ml.h"
+#include "kernels.hpp"
+
+namespace dq4ml {
+
+void set_error(const char* fmt, ...);
+const char* get_error();
+
+struct NcclBinding;  // dist.cpp
+
+}  // namespace dq4ml
+
+struct dq4ml_ctx {
+  int device = 0;
+  int sm_count = 0;
+  cudaStream_t stream = nullptr;
+  dq4ml::Scratch scratch{};
+  char* scratch_base = nullptr;
+  double* h_result = nullptr;  // pinned, kResultDoubles
+  unsigned long long* d_counters = nullptr;
+  int* d_err = nullptr;
+  unsigned long long* d_tile_state = nullptr;
+  size_t tile_state_cap = 0;
+  char* arena = nullptr;  // staging for host-resident inputs/outputs
+  size_t arena_cap = 0, arena_used = 0;
+  std::unordered_map<const void*, void*> staged;  // host pointer -> device copy, per call
+  int64_t launches = 0;
+  // optional CUDA-event timing of the aggregation-pass kernels (bench.py's roofline leg)
+  bool pass_timing = false;
+  bool pass_event_pending = false;
+  cudaEvent_t pass_ev0 = nullptr, pass_ev1 = nullptr;
+  double pass_ms_total = 0.0;
+  int64_t pass_count = 0;
+  // ranks
+  dq4ml::NcclBinding* nccl = nullptr;
+  int rank = 0, world = 1;
+  dq4ml_allreduce_fn allreduce_cb = nullptr;
+  void* allreduce_user = nullptr;
+};
+
+namespace dq4ml {
+
+constexpr size_t kResultDoubles = 1 << 16;  // fits the packed Gram of d = 256 (33 411 doubles)
+constexpr size_t kPartialsBytes = 8u << 20;
+
+// dist.cpp
+int nccl_unique_id(void* id128);
+int nccl_bind(dq4ml_ctx* ctx, const void* id128, int rank, int world);
+void nccl_unbind(dq4ml_ctx* ctx);
+// In-stream sum all-reduce of `count` doubles at device pointer `buf` (no-op when no communicator is bound).
+int nccl_allreduce_device(dq4ml_ctx* ctx, double* buf, int64_t count);
+
+}  // namespace dq4ml

@@ -1,0 +1,354 @@
+// dq_kernels.cu -- the DQ section of the lab (DataQuality4MachineLearningApp.java:68-90) as sm_100a kernels:
+// the two UDF columns, and rule1 -> filter -> rule2 -> filter fused into one stable compaction pass.
+// Plus the synthetic-data generator and the row digest used by the benchmarks/tests.
+#include "device_utils.cuh"
+#include "kernels.hpp"
+
+namespace dq4ml {
+namespace {
+
+__host__ DqThresholds thresholds(const dq4ml_dq_params& p) {
+  DqThresholds t;
+  t.min_price = p.min_price;
+  t.max_price = p.max_price;
+  t.min_guest = p.min_guest;
+  return t;
+}
+
+// ------------------------------------------------------------------------------------------ UDF columns
+// minimumPriceRule over a column: MinimumPriceDataQualityUdf.call -> checkMinimumPrice
+// (MinimumPriceDataQualityService.java:7-13).  A null (valid == 0) is the reference's NullPointerException.
+__global__ void __launch_bounds__(256) udf_min_price_kernel(const double* __restrict__ price,
+                                                            const uint8_t* __restrict__ valid, int64_t n,
+                                                            double* __restrict__ out, double min_price,
+                                                            int* __restrict__ err_flag) {
+  const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x * 2;
+  for (int64_t i = (static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x) * 2; i < n; i += stride) {
+    if (i + 2 <= n) {
+      const double2 p = ldg_stream_d2(price + i);
+      if (valid != nullptr && (valid[i] == 0 || valid[i + 1] == 0)) *err_flag = 1;
+      stg_stream_d2(out + i, make_double2(p.x < min_price ? -1.0 : p.x, p.y < min_price ? -1.0 : p.y));
+    } else {
+      if (valid != nullptr && valid[i] == 0) *err_flag = 1;
+      const double p = price[i];
+      out[i] = p < min_price ? -1.0 : p;
+    }
+  }
+}
+
+// priceCorrelationRule over columns: PriceCorrelationDataQualityUdf.call (null -> -1.0, .java:12-14) ->
+// checkPriceRange (PriceCorrelationDataQualityService.java:5-10).
+__global__ void __launch_bounds__(256) udf_price_corr_kernel(const double* __restrict__ price,
+                                                             const int* __restrict__ guest,
+                                                             const uint8_t* __restrict__ pvalid,
+                                                             const uint8_t* __restrict__ gvalid, int64_t n,
+                                                             double* __restrict__ out, double max_price,
+                                                             int min_guest) {
+  const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x * 2;
+  for (int64_t i = (static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x) * 2; i < n; i += stride) {
+    if (i + 2 <= n) {
+      const double2 p = ldg_stream_d2(price + i);
+      const int2 g = ldg_stream_i2(guest + i);
+      const bool null0 = (pvalid != nullptr && pvalid[i] == 0) || (gvalid != nullptr && gvalid[i] == 0);
+      const bool null1 = (pvalid != nullptr && pvalid[i + 1] == 0) || (gvalid != nullptr && gvalid[i + 1] == 0);
+      double2 o;
+      o.x = (null0 || (g.x < min_guest && p.x > max_price)) ? -1.0 : p.x;
+      o.y = (null1 || (g.y < min_guest && p.y > max_price)) ? -1.0 : p.y;
+      stg_stream_d2(out + i, o);
+    } else {
+      const bool nul = (pvalid != nullptr && pvalid[i] == 0) || (gvalid != nullptr && gvalid[i] == 0);
+      const double p = price[i];
+      out[i] = (nul || (guest[i] < min_guest && p > max_price)) ? -1.0 : p;
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------ filter + compaction
+// One CTA per tile of kFilterThreads x 4 consecutive rows.  Tile t publishes its survivor count in tile_state[t] as
+// {flag:2 | value:62}; flag 1 = "aggregate of this tile", flag 2 = "inclusive prefix up to this tile".  A tile finds
+// its output offset by walking back over its predecessors' words (decoupled look-back), so the data is read once and
+// written once, and the output order is the input order (Spark's filter is order preserving within a partition).
+constexpr int kFilterThreads = 512;
+constexpr int kFilterRows = 4;
+constexpr int64_t kFilterTile = static_cast<int64_t>(kFilterThreads) * kFilterRows;
+constexpr unsigned long long kFlagAgg = 1ull << 62, kFlagPrefix = 2ull << 62, kValueMask = (1ull << 62) - 1;
+
+__device__ __forceinline__ unsigned long long ld_state(const unsigned long long* p) {
+  unsigned long long v;
+  asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_state(unsigned long long* p, unsigned long long v) {
+  asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+
+__global__ void __launch_bounds__(kFilterThreads)
+    dq_filter_compact_kernel(const int* __restrict__ guest, const double* __restrict__ price, const int64_t n,
+                             const DqThresholds t, int* __restrict__ guest_out, double* __restrict__ price_out,
+                             unsigned long long* __restrict__ tile_state, unsigned long long* __restrict__ counters) {
+  __shared__ unsigned int s_warp_keep[kFilterThreads / 32];
+  __shared__ unsigned int s_warp_rule1[kFilterThreads / 32];
+  __shared__ unsigned long long s_tile_offset;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int64_t tile = blockIdx.x;
+  const int64_t row = tile * kFilterTile + static_cast<int64_t>(tid) * kFilterRows;
+
+  int g[kFilterRows];
+  double p[kFilterRows];
+  unsigned keep_bits = 0, rule1 = 0;
+  if (row + kFilterRows <= n) {
+    load_i32<kFilterRows, true>(guest, row, g);
+    load_f64<kFilterRows, true>(price, row, p);
+#pragma unroll
+    for (int r = 0; r < kFilterRows; ++r) {
+      keep_bits |= (dq_keep(g[r], p[r], t) ? 1u : 0u) << r;
+      rule1 += dq_keep_rule1(p[r], t) ? 1u : 0u;
+    }
+  } else {
+#pragma unroll
+    for (int r = 0; r < kFilterRows; ++r) {
+      if (row + r < n) {
+        g[r] = guest[row + r];
+        p[r] = price[row + r];
+        keep_bits |= (dq_keep(g[r], p[r], t) ? 1u : 0u) << r;
+        rule1 += dq_keep_rule1(p[r], t) ? 1u : 0u;
+      }
+    }
+  }
+  const unsigned cnt = __popc(keep_bits);
+
+  // exclusive scan of cnt over the CTA (row order == thread order)
+  unsigned incl = cnt;
+#pragma unroll
+  for (int off = 1; off < 32; off <<= 1) {
+    const unsigned v = __shfl_up_sync(0xffffffffu, incl, off);
+    if (lane >= off) incl += v;
+  }
+  unsigned r1sum = rule1;
+#pragma unroll
+  for (int off = 16; off > 0; off >>= 1) r1sum += __shfl_down_sync(0xffffffffu, r1sum, off);
+  if (lane == 31) s_warp_keep[warp] = incl;
+  if (lane == 0) s_warp_rule1[warp] = r1sum;
+  __syncthreads();
+  if (warp == 0) {
+    // 16 warp totals -> exclusive offsets per warp, tile aggregate, rule-1 total
+    unsigned wt = lane < kFilterThreads / 32 ? s_warp_keep[lane] : 0u;
+    unsigned r1 = lane < kFilterThreads / 32 ? s_warp_rule1[lane] : 0u;
+    unsigned wincl = wt;
+#pragma unroll
+    for (int off = 1; off < 32; off <<= 1) {
+      const unsigned v = __shfl_up_sync(0xffffffffu, wincl, off);
+      if (lane >= off) wincl += v;
+    }
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) r1 += __shfl_down_sync(0xffffffffu, r1, off);
+    const unsigned aggregate = __shfl_sync(0xffffffffu, wincl, 31);
+    if (lane < kFilterThreads / 32) s_warp_keep[lane] = wincl - wt;  // exclusive
+    if (lane == 0 && r1 != 0u) atomicAdd(&counters[1], static_cast<unsigned long long>(r1));
+
+    // decoupled look-back
+    unsigned long long exclusive = 0;
+    if (tile == 0) {
+      if (lane == 0) st_state(&tile_state[0], kFlagPrefix | aggregate);
+    } else {
+      if (lane == 0) st_state(&tile_state[tile], kFlagAgg | aggregate);
+      int64_t idx = tile - 1;
+      for (;;) {
+        const int64_t my = idx - lane;
+        unsigned long long w = kFlagPrefix;  // tiles before 0 contribute an (empty) prefix
+        if (my >= 0) {
+          do { w = ld_state(&tile_state[my]); } while ((w >> 62) == 0ull);
+        }
+        const unsigned has_prefix = __ballot_sync(0xffffffffu, (w >> 62) == 2ull);
+        const int first = has_prefix ? __ffs(has_prefix) - 1 : 31;  // nearest predecessor that holds a full prefix
+        unsigned long long contrib = lane <= first ? (w & kValueMask) : 0ull;
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) contrib += __shfl_down_sync(0xffffffffu, contrib, off);
+        exclusive += __shfl_sync(0xffffffffu, contrib, 0);
+        if (has_prefix) break;
+        idx -= 32;
+      }
+      if (lane == 0) st_state(&tile_state[tile], kFlagPrefix | (exclusive + aggregate));
+    }
+    if (lane == 0) {
+      s_tile_offset = exclusive;
+      if (tile == static_cast<int64_t>(gridDim.x) - 1) counters[0] = exclusive + aggregate;
+    }
+  }
+  __syncthreads();
+  unsigned long long pos = s_tile_offset + s_warp_keep[warp] + (incl - cnt);
+#pragma unroll
+  for (int r = 0; r < kFilterRows; ++r) {
+    if ((keep_bits >> r) & 1u) {
+      guest_out[pos] = g[r];
+      price_out[pos] = p[r];
+      ++pos;
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------ synthetic data
+// Counter-based generator, bit-identical to oracle/dq4ml_oracle.c:orc_synth_generate (integer hashing plus
+// individually rounded fp64 add/mul: explicit __dadd_rn/__dmul_rn so that nothing is contracted into an FMA).
+__device__ __forceinline__ unsigned long long mix64(unsigned long long z) {
+  z ^= z >> 30; z *= 0xBF58476D1CE4E5B9ull;
+  z ^= z >> 27; z *= 0x94D049BB133111EBull;
+  z ^= z >> 31;
+  return z;
+}
+constexpr unsigned long long kPhi = 0x9E3779B97F4A7C15ull;
+__device__ __forceinline__ unsigned long long row_key(unsigned long long seed, unsigned long long r) { return mix64(seed + (r + 1) * kPhi); }
+__device__ __forceinline__ unsigned long long stream_of(unsigned long long key, unsigned long long k) { return mix64(key + k * kPhi); }
+__device__ __forceinline__ double u01(unsigned long long h) { return __dmul_rn(static_cast<double>(h >> 11), 0x1.0p-53); }
+
+__global__ void __launch_bounds__(256) synth_kernel(const dq4ml_synth_params sp, const double thr1, const double thr2,
+                                                    const int64_t row0, const int64_t n, int* __restrict__ guest,
+                                                    double* __restrict__ price, double* __restrict__ extra,
+                                                    const int64_t extra_stride) {
+  const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
+  for (int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += stride) {
+    const unsigned long long r = static_cast<unsigned long long>(row0 + i);
+    const unsigned long long key = row_key(sp.seed_data, r);
+    const int g = 1 + static_cast<int>(((stream_of(key, 1) >> 32) * 35ull) >> 32);
+    double s = __dadd_rn(u01(stream_of(key, 2)), u01(stream_of(key, 3)));
+    s = __dadd_rn(s, u01(stream_of(key, 4)));
+    s = __dadd_rn(s, u01(stream_of(key, 5)));
+    const double noise = __dmul_rn(__dadd_rn(s, -2.0), 2.6);
+    double pr = __dadd_rn(static_cast<double>(5 * g + 22), noise);
+    for (int k = 1; k < sp.d; ++k) {
+      const double xk = __dmul_rn(u01(stream_of(key, 8ull + k)), static_cast<double>(1 + (k & 3)));
+      if (extra != nullptr) extra[static_cast<int64_t>(k - 1) * extra_stride + i] = xk;
+      const double gamma = static_cast<double>((k * 7) % 5 - 2) * 0.5;
+      pr = __dadd_rn(pr, __dmul_rn(gamma, xk));
+    }
+    const unsigned long long akey = row_key(sp.seed_anom, r);
+    const double ua = u01(mix64(akey));
+    const double ub = u01(stream_of(akey, 1));
+    if (ua < thr1) pr = __dadd_rn(3.0, __dmul_rn(12.0, ub));
+    else if (ua < thr2 && g < 14) pr = __dadd_rn(100.0, __dmul_rn(50.0, ub));
+    guest[i] = g;
+    price[i] = pr;
+  }
+}
+
+// Order-sensitive digest: two 64-bit sums of per-row hashes keyed by the row's position (integer adds commute, so the
+// reduction order does not matter and atomics are exact).
+__global__ void __launch_bounds__(256) rows_digest_kernel(const int* __restrict__ guest, const double* __restrict__ price,
+                                                          const int64_t n, const unsigned long long seed,
+                                                          unsigned long long* __restrict__ out) {
+  unsigned long long a = 0, b = 0;
+  const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
+  for (int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += stride) {
+    const unsigned long long bits = static_cast<unsigned long long>(__double_as_longlong(price[i]));
+    unsigned long long h = mix64((seed + (static_cast<unsigned long long>(i) + 1) * kPhi) ^ bits);
+    h = mix64(h + static_cast<unsigned long long>(static_cast<unsigned int>(guest[i])) * 0xD1B54A32D192ED03ull);
+    a += h;
+    b += mix64(h ^ (static_cast<unsigned long long>(i) * 0x2545F4914F6CDD1Dull));
+  }
+#pragma unroll
+  for (int off = 16; off > 0; off >>= 1) {
+    a += __shfl_down_sync(0xffffffffu, a, off);
+    b += __shfl_down_sync(0xffffffffu, b, off);
+  }
+  if ((threadIdx.x & 31) == 0) {
+    atomicAdd(&out[0], a);
+    atomicAdd(&out[1], b);
+  }
+}
+
+// mean of the first (up to 256) values of each column: provisional centres for the shifted-sum summarizer
+__global__ void __launch_bounds__(256) column_heads_kernel(const DeviceCols cols, const double* __restrict__ label,
+                                                           const int label_slot, const int64_t n,
+                                                           double* __restrict__ centres) {
+  __shared__ double s_red[256 / 32];
+  const int64_t m = n < 256 ? n : 256;
+  // slots [0, cols.n) = feature columns, [cols.n, label_slot) = unused (0), label_slot = label
+  for (int c = 0; c <= label_slot; ++c) {
+    double v = 0.0;
+    const bool live = c < cols.n || (c == label_slot && label != nullptr);
+    if (live && threadIdx.x < m) {
+      if (c < cols.n) {
+        v = cols.dtype[c] == DQ4ML_I32 ? static_cast<double>(static_cast<const int*>(cols.ptr[c])[threadIdx.x])
+                                       : static_cast<const double*>(cols.ptr[c])[threadIdx.x];
+      } else {
+        v = label[threadIdx.x];
+      }
+      if (!(fabs(v) <= 1.79e308)) v = 0.0;  // NaN/Inf must not become the centre
+    }
+    v = block_reduce(v, kSum, s_red);
+    if (threadIdx.x == 0) centres[c] = (live && m > 0) ? v / static_cast<double>(m) : 0.0;
+  }
+}
+
+int grid_for(int64_t work_items, int threads, int cap_blocks) {
+  int64_t b = (work_items + threads - 1) / threads;
+  if (b < 1) b = 1;
+  if (b > cap_blocks) b = cap_blocks;
+  return static_cast<int>(b);
+}
+
+}  // namespace
+
+cudaError_t launch_udf_min_price(const double* price, const uint8_t* valid, int64_t n, double* out,
+                                 const dq4ml_dq_params& p, int* err_flag, cudaStream_t stream, int64_t* launches) {
+  if (n <= 0) return cudaSuccess;
+  udf_min_price_kernel<<<grid_for((n + 1) / 2, 256, 148 * 16), 256, 0, stream>>>(price, valid, n, out, p.min_price, err_flag);
+  ++*launches;
+  return cudaGetLastError();
+}
+
+cudaError_t launch_udf_price_corr(const double* price, const int32_t* guest, const uint8_t* pvalid,
+                                  const uint8_t* gvalid, int64_t n, double* out, const dq4ml_dq_params& p,
+                                  cudaStream_t stream, int64_t* launches) {
+  if (n <= 0) return cudaSuccess;
+  udf_price_corr_kernel<<<grid_for((n + 1) / 2, 256, 148 * 16), 256, 0, stream>>>(price, guest, pvalid, gvalid, n, out,
+                                                                                   p.max_price, p.min_guest);
+  ++*launches;
+  return cudaGetLastError();
+}
+
+size_t dq_filter_state_bytes(int64_t n) {
+  const int64_t tiles = (n + kFilterTile - 1) / kFilterTile;
+  return static_cast<size_t>(tiles > 0 ? tiles : 1) * sizeof(unsigned long long);
+}
+
+cudaError_t launch_dq_filter(const int32_t* guest, const double* price, int64_t n, const dq4ml_dq_params& p,
+                             int32_t* guest_out, double* price_out, unsigned long long* tile_state,
+                             unsigned long long* counters, cudaStream_t stream, int64_t* launches) {
+  cudaError_t e = cudaMemsetAsync(counters, 0, 2 * sizeof(unsigned long long), stream);
+  if (e != cudaSuccess || n <= 0) return e;
+  e = cudaMemsetAsync(tile_state, 0, dq_filter_state_bytes(n), stream);
+  if (e != cudaSuccess) return e;
+  const int64_t tiles = (n + kFilterTile - 1) / kFilterTile;
+  dq_filter_compact_kernel<<<static_cast<unsigned>(tiles), kFilterThreads, 0, stream>>>(
+      guest, price, n, thresholds(p), guest_out, price_out, tile_state, counters);
+  ++*launches;
+  return cudaGetLastError();
+}
+
+cudaError_t launch_synth(const dq4ml_synth_params& p, int64_t row0, int64_t n, int32_t* guest, double* price,
+                         double* extra, int64_t extra_stride, cudaStream_t stream, int64_t* launches) {
+  if (n <= 0) return cudaSuccess;
+  synth_kernel<<<grid_for(n, 256, 148 * 32), 256, 0, stream>>>(p, p.p_low, p.p_low + p.p_high, row0, n, guest, price,
+                                                               extra, extra_stride);
+  ++*launches;
+  return cudaGetLastError();
+}
+
+cudaError_t launch_rows_digest(const int32_t* guest, const double* price, int64_t n, uint64_t seed,
+                               unsigned long long* out2, cudaStream_t stream, int64_t* launches) {
+  cudaError_t e = cudaMemsetAsync(out2, 0, 2 * sizeof(unsigned long long), stream);
+  if (e != cudaSuccess || n <= 0) return e;
+  rows_digest_kernel<<<grid_for(n, 256, 148 * 16), 256, 0, stream>>>(guest, price, n, seed, out2);
+  ++*launches;
+  return cudaGetLastError();
+}
+
+cudaError_t launch_column_heads(const DeviceCols& cols, const double* label, int label_slot, int64_t n,
+                                const Scratch& scratch, cudaStream_t stream, int64_t* launches) {
+  column_heads_kernel<<<1, 256, 0, stream>>>(cols, label, label_slot, n, scratch.consts);
+  ++*launches;
+  return cudaGetLastError();
+}
+
+}  // namespace dq4ml

@@ -1,0 +1,163 @@
+// ops.cuh -- the per-row bodies plugged into stream_reduce_kernel.  Each one is the seqOp of a Spark ML 2.4.4
+// aggregator reached from lr.fit / model.summary (DataQuality4MachineLearningApp.java:126,129,132-139), with w = 1.
+//
+// Contract with the kernel: x[j] and y arrive already zeroed for rows the DQ rules dropped (keep == false) and for
+// j >= d; `c` holds Op::NCONST doubles the kernel preloaded from device memory.
+#pragma once
+
+#include "device_utils.cuh"
+
+namespace dq4ml {
+
+// WeightedLeastSquares.Aggregator.add: count, bSum, bbSum, aSum[d], abSum[d], aaSum (packed upper, column-major).
+// wSum and wwSum equal count when every weight is 1, so they are not accumulated separately.
+template <int DMAX>
+struct WlsOp {
+  static constexpr int TRI = DMAX * (DMAX + 1) / 2;
+  static constexpr int NACC = 3 + 2 * DMAX + TRI;
+  static constexpr int NCONST = 0;
+  static constexpr bool HAS_OUT = false;
+  __host__ __device__ static constexpr double identity(int) { return 0.0; }
+  __host__ __device__ static constexpr int kind(int) { return kSum; }
+
+  __device__ __forceinline__ double row(double (&acc)[NACC], const double*, const double (&x)[DMAX], double y,
+                                        bool keep, int) const {
+    acc[0] += keep ? 1.0 : 0.0;
+    acc[1] += y;
+    acc[2] = fma(y, y, acc[2]);
+#pragma unroll
+    for (int j = 0; j < DMAX; ++j) {
+      acc[3 + j] += x[j];
+      acc[3 + DMAX + j] = fma(x[j], y, acc[3 + DMAX + j]);
+    }
+#pragma unroll
+    for (int j = 0; j < DMAX; ++j)
+#pragma unroll
+      for (int i = 0; i <= j; ++i) acc[3 + 2 * DMAX + i + j * (j + 1) / 2] = fma(x[i], x[j], acc[3 + 2 * DMAX + i + j * (j + 1) / 2]);
+    return 0.0;
+  }
+};
+
+// LeastSquaresAggregator.add: diff = x.(c/sigma) - y/sigma_y + offset; lossSum += diff^2/2; gradSum_j += diff * x_j
+// (the 1/sigma_j factor of Spark's per-row update is applied once on the host: w = 1 makes it a common factor).
+template <int DMAX>
+struct LsqOp {
+  static constexpr int NACC = 2 + DMAX;
+  static constexpr int NCONST = 0;
+  static constexpr bool HAS_OUT = false;
+  double eff[DMAX];
+  double offset;
+  double inv_ystd;
+  __host__ __device__ static constexpr double identity(int) { return 0.0; }
+  __host__ __device__ static constexpr int kind(int) { return kSum; }
+
+  __device__ __forceinline__ double row(double (&acc)[NACC], const double*, const double (&x)[DMAX], double y,
+                                        bool keep, int) const {
+    double dotp = 0.0;
+#pragma unroll
+    for (int j = 0; j < DMAX; ++j) dotp = fma(x[j], eff[j], dotp);
+    double diff = dotp - y * inv_ystd + offset;
+    diff = keep ? diff : 0.0;
+    acc[0] = fma(0.5 * diff, diff, acc[0]);
+    acc[1] += keep ? 1.0 : 0.0;
+#pragma unroll
+    for (int j = 0; j < DMAX; ++j) acc[2 + j] = fma(diff, x[j], acc[2 + j]);
+    return 0.0;
+  }
+};
+
+// MultivariateOnlineSummarizer, the part LinearRegression.train needs (mean and variance of every feature and of the
+// label).  Spark updates a running mean per value (one division each); here each thread keeps shifted power sums
+// S1 = sum(v - s), S2 = sum((v - s)^2) around a provisional centre s taken from the head of the column, which is as
+// stable as Welford when s is within a few sigma of the mean and costs two FMAs.  Column DMAX is the label.
+template <int DMAX>
+struct SummCoreOp {
+  static constexpr int NACC = 1 + 2 * (DMAX + 1);
+  static constexpr int NCONST = DMAX + 1;  // the centres
+  static constexpr bool HAS_OUT = false;
+  __host__ __device__ static constexpr double identity(int) { return 0.0; }
+  __host__ __device__ static constexpr int kind(int) { return kSum; }
+
+  __device__ __forceinline__ double row(double (&acc)[NACC], const double* c, const double (&x)[DMAX], double y,
+                                        bool keep, int) const {
+    acc[0] += keep ? 1.0 : 0.0;
+#pragma unroll
+    for (int j = 0; j < DMAX; ++j) {
+      const double t = keep ? x[j] - c[j] : 0.0;
+      acc[1 + 2 * j] += t;
+      acc[2 + 2 * j] = fma(t, t, acc[2 + 2 * j]);
+    }
+    const double t = keep ? y - c[DMAX] : 0.0;
+    acc[1 + 2 * DMAX] += t;
+    acc[2 + 2 * DMAX] = fma(t, t, acc[2 + 2 * DMAX]);
+    return 0.0;
+  }
+};
+
+// Full MultivariateOnlineSummarizer read-out for a group of up to DMAX columns: shifted sums, min, max, numNonzeros,
+// normL1, sum of squares.  Used by dq4ml_summarize only (the fit uses SummCoreOp).
+template <int DMAX>
+struct SummFullOp {
+  static constexpr int PER = 7;
+  static constexpr int NACC = 1 + PER * DMAX;
+  static constexpr int NCONST = DMAX;
+  static constexpr bool HAS_OUT = false;
+  __host__ __device__ static constexpr int kind(int k) {
+    return k == 0 ? kSum : ((k - 1) % PER == 2 ? kMin : ((k - 1) % PER == 3 ? kMax : kSum));
+  }
+  __host__ __device__ static constexpr double identity(int k) {
+    return kind(k) == kMin ? __builtin_huge_val() : (kind(k) == kMax ? -__builtin_huge_val() : 0.0);
+  }
+
+  __device__ __forceinline__ double row(double (&acc)[NACC], const double* c, const double (&x)[DMAX], double,
+                                        bool keep, int d) const {
+    acc[0] += keep ? 1.0 : 0.0;
+#pragma unroll
+    for (int j = 0; j < DMAX; ++j) {
+      const bool on = keep && j < d;
+      const double v = x[j];
+      const double t = on ? v - c[j] : 0.0;
+      double* a = &acc[1 + PER * j];
+      a[0] += t;
+      a[1] = fma(t, t, a[1]);
+      a[2] = combine(kMin, a[2], on ? v : __builtin_huge_val());
+      a[3] = combine(kMax, a[3], on ? v : -__builtin_huge_val());
+      a[4] += (on && v != 0.0) ? 1.0 : 0.0;
+      a[5] += fabs(v);
+      a[6] = fma(v, v, a[6]);
+    }
+    return 0.0;
+  }
+};
+
+// LinearRegressionModel.transform + RegressionMetrics in one pass: yhat = x.beta + b; residual = y - yhat;
+// accumulators n, SSerr, sum y, sum y^2, sum |residual|.  Per-row output: prediction (mode 0) or residual (mode 1).
+template <int DMAX>
+struct EvalOp {
+  static constexpr int NACC = 5;
+  static constexpr int NCONST = 0;
+  static constexpr bool HAS_OUT = true;
+  double coef[DMAX];
+  double intercept;
+  int mode;
+  __host__ __device__ static constexpr double identity(int) { return 0.0; }
+  __host__ __device__ static constexpr int kind(int) { return kSum; }
+
+  __device__ __forceinline__ double row(double (&acc)[NACC], const double*, const double (&x)[DMAX], double y,
+                                        bool keep, int) const {
+    double yhat = 0.0;
+#pragma unroll
+    for (int j = 0; j < DMAX; ++j) yhat = fma(x[j], coef[j], yhat);
+    yhat += intercept;
+    yhat = keep ? yhat : 0.0;
+    const double res = y - yhat;  // y is already 0 for dropped rows
+    acc[0] += keep ? 1.0 : 0.0;
+    acc[1] = fma(res, res, acc[1]);
+    acc[2] += y;
+    acc[3] = fma(y, y, acc[3]);
+    acc[4] += fabs(res);
+    return mode == 0 ? yhat : res;
+  }
+};
+
+}  // namespace dq4ml

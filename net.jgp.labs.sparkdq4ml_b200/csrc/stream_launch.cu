@@ -1,0 +1,168 @@
+// stream_launch.cu -- instantiates stream_reduce_kernel for every (op, column-group bucket, DQ mode) the path uses
+// and picks one at run time.  Buckets 1,2,4,8 stream 4 rows per thread per tile, buckets 16,32 stream 2 (register
+// budget); grids are sized to (CTAs resident per SM) x (SM count) so the whole pass is one wave of persistent CTAs.
+#include <map>
+#include <mutex>
+
+#include "kernels.hpp"
+#include "ops.cuh"
+#include "stream_reduce.cuh"
+
+namespace dq4ml {
+
+int stream_bucket(int d) {
+  int b = 1;
+  while (b < d) b <<= 1;
+  return b;
+}
+
+int stream_nacc(StreamOpKind op, int bucket) {
+  switch (op) {
+    case kOpWls: return 3 + 2 * bucket + bucket * (bucket + 1) / 2;
+    case kOpLsq: return 2 + bucket;
+    case kOpSummCore: return 1 + 2 * (bucket + 1);
+    case kOpSummFull: return 1 + 7 * bucket;
+    case kOpEval: return 5;
+  }
+  return 0;
+}
+
+namespace {
+
+struct PassArgs {
+  ColTable cols;
+  int d;
+  const double* label;
+  DqArgs dq;
+  int dq_mode;
+  int64_t n;
+  const double* dev_consts;
+  double* row_out;
+  Scratch scratch;
+  cudaStream_t stream;
+};
+
+template <class Op, int DMAX, int ROWS, int DQMODE>
+cudaError_t launch_one(const Op& op, const PassArgs& a) {
+  auto kernel = stream_reduce_kernel<Op, DMAX, ROWS, DQMODE>;
+  static std::mutex mu;
+  static std::map<int, int> blocks_per_sm;  // per device
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  int per_sm = 0;
+  {
+    std::lock_guard<std::mutex> lk(mu);
+    auto it = blocks_per_sm.find(dev);
+    if (it == blocks_per_sm.end()) {
+      e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, kBlock, 0);
+      if (e != cudaSuccess) return e;
+      if (per_sm < 1) per_sm = 1;
+      blocks_per_sm[dev] = per_sm;
+    } else {
+      per_sm = it->second;
+    }
+  }
+  const int64_t tile_rows = static_cast<int64_t>(kBlock) * ROWS;
+  const int64_t n_tiles = (a.n + tile_rows - 1) / tile_rows;
+  int64_t grid = static_cast<int64_t>(per_sm) * a.scratch.sm_count;
+  if (grid > n_tiles) grid = n_tiles;
+  if (grid < 1) grid = 1;
+  const size_t need = static_cast<size_t>(grid) * Op::NACC * sizeof(double);
+  if (need > a.scratch.partials_bytes) return cudaErrorMemoryAllocation;
+  kernel<<<static_cast<unsigned>(grid), kBlock, 0, a.stream>>>(op, a.cols, a.d, a.label, a.dq, a.n, a.dev_consts,
+                                                                a.row_out, a.scratch.partials, a.scratch.ticket,
+                                                                a.scratch.result);
+  return cudaGetLastError();
+}
+
+template <class Op, int DMAX, int ROWS>
+cudaError_t launch_mode(const Op& op, const PassArgs& a) {
+  switch (a.dq_mode) {
+    case kDqNone: return launch_one<Op, DMAX, ROWS, kDqNone>(op, a);
+    case kDqSeparate: return launch_one<Op, DMAX, ROWS, kDqSeparate>(op, a);
+    default: return launch_one<Op, DMAX, ROWS, kDqLab>(op, a);
+  }
+}
+
+template <int DMAX>
+LsqOp<DMAX> make_lsq(const LsqConsts& c) {
+  LsqOp<DMAX> op;
+  for (int j = 0; j < DMAX; ++j) op.eff[j] = c.eff[j];
+  op.offset = c.offset;
+  op.inv_ystd = c.inv_ystd;
+  return op;
+}
+template <int DMAX>
+EvalOp<DMAX> make_eval(const EvalConsts& c) {
+  EvalOp<DMAX> op;
+  for (int j = 0; j < DMAX; ++j) op.coef[j] = c.coef[j];
+  op.intercept = c.intercept;
+  op.mode = c.mode;
+  return op;
+}
+
+template <int DMAX>
+cudaError_t launch_bucket(StreamOpKind kind, const PassArgs& a, const void* host_consts) {
+  constexpr int ROWS = DMAX <= 8 ? 4 : 2;
+  switch (kind) {
+    case kOpWls:
+      if constexpr (DMAX <= 8) return launch_mode<WlsOp<DMAX>, DMAX, ROWS>(WlsOp<DMAX>{}, a);
+      return cudaErrorInvalidValue;
+    case kOpLsq: return launch_mode<LsqOp<DMAX>, DMAX, ROWS>(make_lsq<DMAX>(*static_cast<const LsqConsts*>(host_consts)), a);
+    case kOpSummCore: return launch_mode<SummCoreOp<DMAX>, DMAX, ROWS>(SummCoreOp<DMAX>{}, a);
+    case kOpSummFull:
+      if constexpr (DMAX <= 4) return launch_mode<SummFullOp<DMAX>, DMAX, ROWS>(SummFullOp<DMAX>{}, a);
+      return cudaErrorInvalidValue;
+    case kOpEval: return launch_mode<EvalOp<DMAX>, DMAX, ROWS>(make_eval<DMAX>(*static_cast<const EvalConsts*>(host_consts)), a);
+  }
+  return cudaErrorInvalidValue;
+}
+
+}  // namespace
+
+cudaError_t launch_stream_pass(StreamOpKind op, const DeviceCols& cols, const double* label, const DeviceDq& dq,
+                               int64_t n, const void* host_consts, double* row_out, const Scratch& scratch,
+                               cudaStream_t stream, int64_t* launches) {
+  if (cols.n < 0 || cols.n > kMaxCols) return cudaErrorInvalidValue;
+  PassArgs a;
+  a.d = cols.n;
+  a.cols.i32_mask = 0;
+  for (int j = 0; j < kMaxStreamD; ++j) a.cols.ptr[j] = nullptr;
+  for (int j = 0; j < cols.n; ++j) {
+    a.cols.ptr[j] = cols.ptr[j];
+    if (cols.dtype[j] == DQ4ML_I32) a.cols.i32_mask |= 1u << j;
+  }
+  a.label = label;
+  a.dq.guest = dq.guest;
+  a.dq.price = dq.price;
+  a.dq.t.min_price = dq.params.min_price;
+  a.dq.t.max_price = dq.params.max_price;
+  a.dq.t.min_guest = dq.params.min_guest;
+  if (dq.guest == nullptr) {
+    a.dq_mode = kDqNone;
+  } else if (cols.n > 0 && cols.dtype[0] == DQ4ML_I32 && cols.ptr[0] == dq.guest && label != nullptr &&
+             label == dq.price) {
+    a.dq_mode = kDqLab;
+  } else {
+    a.dq_mode = kDqSeparate;
+  }
+  a.n = n;
+  a.dev_consts = scratch.consts;
+  a.row_out = row_out;
+  a.scratch = scratch;
+  a.stream = stream;
+  cudaError_t e;
+  switch (stream_bucket(cols.n > 0 ? cols.n : 1)) {
+    case 1: e = launch_bucket<1>(op, a, host_consts); break;
+    case 2: e = launch_bucket<2>(op, a, host_consts); break;
+    case 4: e = launch_bucket<4>(op, a, host_consts); break;
+    case 8: e = launch_bucket<8>(op, a, host_consts); break;
+    case 16: e = launch_bucket<16>(op, a, host_consts); break;
+    default: e = launch_bucket<32>(op, a, host_consts); break;
+  }
+  if (e == cudaSuccess) ++*launches;
+  return e;
+}
+
+}  // namespace dq4ml

@@ -1,0 +1,158 @@
+// stream_reduce.cuh -- the one streaming pass every aggregation of the path is an instance of.
+//
+// A pass reads each column of the VectorAssembler table (plus label, plus the DQ columns when they are not already
+// among them) exactly once with 128-bit loads, applies the DQ predicate in registers, feeds each surviving row to an
+// `Op` that keeps NACC fp64 accumulators per thread, and ends with warp-shuffle -> shared-memory -> one partial per
+// CTA -> last-CTA fixed-order reduction.  No atomics on data, so results are reproducible for a given (n, grid).
+//
+// This is the GPU counterpart of `instances.treeAggregate(zero)(seqOp, combOp)` in Spark ML 2.4.4, which is what
+// lr.fit(df) (DataQuality4MachineLearningApp.java:126) spends its time in.
+#pragma once
+
+#include "device_utils.cuh"
+
+namespace dq4ml {
+
+struct ColTable {
+  const void* ptr[kMaxStreamD];
+  uint32_t i32_mask;  // bit j: column j holds int32 (else fp64)
+};
+
+struct DqArgs {
+  const int* guest;
+  const double* price;
+  DqThresholds t;
+};
+
+// DQ fusion modes
+constexpr int kDqNone = 0;      // every row counts
+constexpr int kDqSeparate = 1;  // guest/price are loaded as extra columns
+constexpr int kDqLab = 2;       // the lab's layout: guest is feature column 0 (int32) and price is the label -> no extra bytes
+
+template <class Op, int DMAX, int ROWS, int DQMODE, bool VEC>
+__device__ __forceinline__ void process_rows(const Op& op, double (&acc)[Op::NACC], const double* consts,
+                                             const ColTable& cols, int d,
+                                             const double* __restrict__ label, const DqArgs& dq, int64_t row,
+                                             double* __restrict__ row_out) {
+  double x[DMAX][ROWS];
+  int g[ROWS];
+  double y[ROWS];
+#pragma unroll
+  for (int r = 0; r < ROWS; ++r) {
+    g[r] = 0;
+    y[r] = 0.0;
+  }
+#pragma unroll
+  for (int j = 0; j < DMAX; ++j) {
+    if (j < d) {
+      if ((cols.i32_mask >> j) & 1u) {
+        int t[ROWS];
+        load_i32<ROWS, VEC>(static_cast<const int*>(cols.ptr[j]), row, t);
+#pragma unroll
+        for (int r = 0; r < ROWS; ++r) x[j][r] = static_cast<double>(t[r]);
+        if (DQMODE == kDqLab && j == 0) {
+#pragma unroll
+          for (int r = 0; r < ROWS; ++r) g[r] = t[r];
+        }
+      } else {
+        load_f64<ROWS, VEC>(static_cast<const double*>(cols.ptr[j]), row, x[j]);
+      }
+    } else {
+#pragma unroll
+      for (int r = 0; r < ROWS; ++r) x[j][r] = 0.0;
+    }
+  }
+  if (label != nullptr) load_f64<ROWS, VEC>(label, row, y);
+  bool keep[ROWS];
+  if (DQMODE == kDqSeparate) {
+    double pr[ROWS];
+    load_i32<ROWS, VEC>(dq.guest, row, g);
+    load_f64<ROWS, VEC>(dq.price, row, pr);
+#pragma unroll
+    for (int r = 0; r < ROWS; ++r) keep[r] = dq_keep(g[r], pr[r], dq.t);
+  } else if (DQMODE == kDqLab) {
+#pragma unroll
+    for (int r = 0; r < ROWS; ++r) keep[r] = dq_keep(g[r], y[r], dq.t);
+  } else {
+#pragma unroll
+    for (int r = 0; r < ROWS; ++r) keep[r] = true;
+  }
+  double o[ROWS];
+#pragma unroll
+  for (int r = 0; r < ROWS; ++r) {
+    double xr[DMAX];  // dropped rows reach the Op as all-zero rows (their payload may be NaN/Inf garbage)
+#pragma unroll
+    for (int j = 0; j < DMAX; ++j) xr[j] = keep[r] ? x[j][r] : 0.0;
+    o[r] = op.row(acc, consts, xr, keep[r] ? y[r] : 0.0, keep[r], d);
+  }
+  if (Op::HAS_OUT && row_out != nullptr) {
+    if constexpr (VEC && ROWS >= 2) {
+#pragma unroll
+      for (int r = 0; r < ROWS; r += 2) stg_stream_d2(row_out + row + r, make_double2(o[r], o[r + 1]));
+    } else {
+#pragma unroll
+      for (int r = 0; r < ROWS; ++r) row_out[row + r] = o[r];
+    }
+  }
+}
+
+template <class Op, int DMAX, int ROWS, int DQMODE>
+__global__ void __launch_bounds__(kBlock)
+    stream_reduce_kernel(const Op op, const ColTable cols, const int d, const double* __restrict__ label,
+                         const DqArgs dq, const int64_t n, const double* __restrict__ dev_consts,
+                         double* __restrict__ row_out, double* __restrict__ partials, unsigned int* __restrict__ ticket,
+                         double* __restrict__ result) {
+  constexpr int NACC = Op::NACC;
+  double acc[NACC];
+#pragma unroll
+  for (int k = 0; k < NACC; ++k) acc[k] = Op::identity(k);
+  double consts[Op::NCONST > 0 ? Op::NCONST : 1];
+#pragma unroll
+  for (int k = 0; k < Op::NCONST; ++k) consts[k] = __ldg(dev_consts + k);
+
+  const int64_t tile_rows = static_cast<int64_t>(kBlock) * ROWS;
+  const int64_t n_tiles = (n + tile_rows - 1) / tile_rows;
+  for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+    const int64_t row = tile * tile_rows + static_cast<int64_t>(threadIdx.x) * ROWS;
+    if (row + ROWS <= n) {
+      process_rows<Op, DMAX, ROWS, DQMODE, true>(op, acc, consts, cols, d, label, dq, row, row_out);
+    } else {
+      for (int64_t r = row; r < n; ++r) process_rows<Op, DMAX, 1, DQMODE, false>(op, acc, consts, cols, d, label, dq, r, row_out);
+    }
+  }
+
+  // ---- CTA reduction: shuffle inside each warp, then one shared-memory hop across the 8 warps
+  __shared__ double s_warp[(kBlock / 32) * NACC];
+  __shared__ bool s_last;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+  for (int k = 0; k < NACC; ++k) {
+    const double v = warp_reduce(acc[k], Op::kind(k));
+    if (lane == 0) s_warp[warp * NACC + k] = v;
+  }
+  __syncthreads();
+  for (int k = threadIdx.x; k < NACC; k += kBlock) {
+    double v = s_warp[k];
+    for (int w = 1; w < kBlock / 32; ++w) v = combine(Op::kind(k), v, s_warp[w * NACC + k]);
+    partials[static_cast<size_t>(blockIdx.x) * NACC + k] = v;
+  }
+  // ---- grid reduction by whichever CTA finishes last, in a fixed order
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) s_last = (atomicAdd(ticket, 1u) == gridDim.x - 1);
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence();
+  __shared__ double s_red[kBlock / 32];
+  for (int k = 0; k < NACC; ++k) {
+    const int kind = Op::kind(k);
+    double v = Op::identity(k);
+    for (unsigned b = threadIdx.x; b < gridDim.x; b += kBlock)
+      v = combine(kind, v, __ldcg(partials + static_cast<size_t>(b) * NACC + k));
+    v = block_reduce(v, kind, s_red);
+    if (threadIdx.x == 0) result[k] = v;
+  }
+  if (threadIdx.x == 0) *ticket = 0u;  // ready for the next launch on this stream
+}
+
+}  // namespace dq4ml

@@ -181,8 +181,11 @@ void orc_wls_moments(const orc_column* features, int32_t d, const double* label,
     int t = 0, T = 1;
 #endif
     double* x = (double*)malloc(sizeof(double) * (size_t)(d > 0 ? d : 1));
+    double* acc = (double*)calloc((size_t)len + 16, sizeof(double)); /* thread-private: no false sharing */
     int64_t lo = n * t / T, hi = n * (t + 1) / T;
-    wls_fold(features, d, label, lo, hi, dq_guest, dq_price, parts + (int64_t)t * len, x);
+    wls_fold(features, d, label, lo, hi, dq_guest, dq_price, acc, x);
+    memcpy(parts + (int64_t)t * len, acc, sizeof(double) * (size_t)len);
+    free(acc);
     free(x);
   }
   for (int t = 0; t < threads; ++t) /* Aggregator.merge = element-wise sum */
@@ -316,7 +319,7 @@ void orc_lsq_loss_grad(const orc_column* features, int32_t d, const double* labe
 #else
     int t = 0, T = 1;
 #endif
-    double* o = parts + (int64_t)t * len;
+    double* o = (double*)calloc((size_t)len + 16, sizeof(double)); /* thread-private: no false sharing */
     double* x = (double*)malloc(sizeof(double) * (size_t)(d > 0 ? d : 1));
     for (int64_t i = n * t / T; i < n * (t + 1) / T; ++i) {
       if (dq_guest && !orc_dq_keep(dq_guest[i], dq_price[i])) continue;
@@ -331,6 +334,8 @@ void orc_lsq_loss_grad(const orc_column* features, int32_t d, const double* labe
       }
       o[1] += weight;
     }
+    memcpy(parts + (int64_t)t * len, o, sizeof(double) * (size_t)len);
+    free(o);
     free(x);
   }
   for (int64_t k = 0; k < len; ++k) out[k] = 0.0;
@@ -354,7 +359,7 @@ void orc_predict_metrics(const orc_column* features, int32_t d, const double* la
 #else
     int t = 0, T = 1;
 #endif
-    double* o = parts + 5 * t;
+    double o[16] = {0}; /* thread-private: no false sharing */
     for (int64_t i = n * t / T; i < n * (t + 1) / T; ++i) {
       if (dq_guest && !orc_dq_keep(dq_guest[i], dq_price[i])) {
         if (prediction) prediction[i] = 0.0;
@@ -369,6 +374,7 @@ void orc_predict_metrics(const orc_column* features, int32_t d, const double* la
         o[0] += 1.0; o[1] += r * r; o[2] += label[i]; o[3] += label[i] * label[i]; o[4] += fabs(r);
       }
     }
+    memcpy(parts + 5 * t, o, sizeof(double) * 5);
   }
   for (int k = 0; k < 5; ++k) out[k] = 0.0;
   for (int t = 0; t < threads; ++t)

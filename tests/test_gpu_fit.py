@@ -1,0 +1,230 @@
+"""GPU parity, ML section: aggregation passes and whole fits against the oracle, through the C ABI."""
+import numpy as np
+import pytest
+import torch
+
+from conftest import RTOL, rel_err
+from oracle import passes, spark_ml
+
+pytestmark = pytest.mark.gpu
+
+
+def to_dev(*arrs):
+    return [torch.from_numpy(np.ascontiguousarray(a)).cuda() for a in arrs]
+
+
+def synth(n, d, **kw):
+    guest, price, extra = passes.synth_generate(n, d=d, **kw)
+    feats = [guest] + [np.ascontiguousarray(extra[k]) for k in range(d - 1)]
+    return guest, price, feats
+
+
+def estimator(pkg, p):
+    lr = pkg.LinearRegression().setMaxIter(p.get("max_iter", 100)).setRegParam(p.get("reg_param", 0.0))
+    lr.setElasticNetParam(p.get("elastic_net_param", 0.0)).setTol(p.get("tol", 1e-6))
+    lr.setFitIntercept(p.get("fit_intercept", True)).setStandardization(p.get("standardization", True))
+    lr.setSolver(p.get("solver", "auto"))
+    return lr
+
+
+@pytest.mark.parametrize("d", [1, 2, 3, 4, 7, 8])
+@pytest.mark.parametrize("n", [1, 5, 1023, 4096, 200_003])
+def test_wls_moments_vs_oracle(pkg, ctx, d, n):
+    from sparkdq4ml_b200 import ml
+    guest, price, feats = synth(n, d, p_low=0.05, p_high=0.05)
+    ref = passes.wls_moments(feats, price, dq=(guest, price), threads=4)
+    dfeats = to_dev(*feats)
+    dprice = to_dev(price)[0]
+    got = ml.wls_moments(ctx, dfeats, dprice, dq=(dfeats[0], dprice))  # lab layout: guest is feature 0, price is label
+    assert got[0] == ref[0] and got[1] == ref[1]  # survivor count is exact
+    assert rel_err(got, ref) < 1e-11
+    got2 = ml.wls_moments(ctx, dfeats, dprice, dq=(dfeats[0].clone(), dprice.clone()))  # DQ columns passed separately
+    assert got2.tobytes() == got.tobytes()
+    no_dq = ml.wls_moments(ctx, dfeats, dprice)
+    assert rel_err(no_dq, passes.wls_moments(feats, price, threads=4)) < 1e-11
+    host = ml.wls_moments(ctx, feats, price, dq=(guest, price))  # host buffers through the same entry point
+    assert host.tobytes() == got.tobytes()
+
+
+def test_wls_moments_empty_and_all_dropped(pkg, ctx):
+    from sparkdq4ml_b200 import ml
+    g = torch.zeros(0, dtype=torch.int32, device="cuda")
+    p = torch.zeros(0, dtype=torch.float64, device="cuda")
+    assert ml.wls_moments(ctx, [g], p).tolist() == [0.0] * 8
+    g = torch.full((1000,), 3, dtype=torch.int32, device="cuda")
+    p = torch.full((1000,), 5.0, dtype=torch.float64, device="cuda")
+    assert ml.wls_moments(ctx, [g], p, dq=(g, p)).tolist() == [0.0] * 8
+    df = pkg.Frame(ctx, {"guest": g, "price": p, "label": p}).with_fused_dq()
+    df = pkg.VectorAssembler().setInputCols(["guest"]).transform(df)
+    with pytest.raises(pkg.capi.Dq4mlError) as ei:
+        pkg.LinearRegression().fit(df)
+    assert ei.value.status == pkg.capi.ERR_EMPTY
+
+
+def test_nan_price_survives_dq_and_poisons_moments_like_spark(pkg, ctx):
+    from sparkdq4ml_b200 import ml
+    g = np.array([20, 21, 22, 23, 5], dtype=np.int32)
+    p = np.array([100.0, float("nan"), 110.0, 10.0, 120.0])
+    ref = passes.wls_moments([g], p, dq=(g, p))
+    got = ml.wls_moments(ctx, to_dev(g), to_dev(p)[0], dq=(to_dev(g)[0], to_dev(p)[0]))
+    assert got[0] == ref[0] == 3.0
+    assert np.isnan(got[3]) and np.isnan(ref[3]) and got[5] == ref[5]
+
+
+@pytest.mark.parametrize("name", ["abstract", "small", "full"])
+@pytest.mark.parametrize("fused", [False, True])
+def test_lab_app_on_reference_fixtures(pkg, ctx, golden, lab_csv, name, fused):
+    """Config 1: DataQuality4MachineLearningApp on the reference's CSVs."""
+    kat, doc = golden("survey_kats")[name], golden("dataset_" + name)
+    out = pkg.DataQuality4MachineLearningApp(ctx).start(lab_csv(name), fused=fused)
+    ref = doc["fits"]["lab_wls_lasso"]
+    w = kat["wls_lasso"]
+    assert out["n_loaded"] == kat["n"] and out["n_fit_rows"] == kat["n_after_rule2"]
+    if not fused:
+        assert (out["n_after_rule1"], out["n_after_rule2"]) == (kat["n_after_rule1"], kat["n_after_rule2"])
+        assert out["survivor_guest"].cpu().numpy().tolist() == doc["survivor_guest"]
+        assert out["survivor_price"].cpu().numpy().tolist() == doc["survivor_price"]
+    assert out["solver_used"] == "wls-owlqn" and out["numIterations"] == w["n_states"] == ref["total_iterations"]
+    assert rel_err(out["coefficients"], ref["coefficients"]) < RTOL and rel_err(out["coefficients"][0], w["coefficient"]) < RTOL
+    assert rel_err(out["intercept"], ref["intercept"]) < RTOL and rel_err(out["intercept"], w["intercept"]) < RTOL
+    assert rel_err(out["objectiveHistory"], ref["objective_history"]) < RTOL
+    assert rel_err(out["prediction"], w["predict_40"]) < RTOL
+    assert rel_err(out["RMSE"], w["rmse"]) < RTOL and rel_err(out["r2"], w["r2"]) < RTOL
+    assert out["regParam"] == 1.0 and out["tol"] == 1e-6
+    # per-row predictions and residuals against the oracle
+    go = np.asarray(doc["survivor_guest"], dtype=np.int32)
+    po = np.asarray(doc["survivor_price"], dtype=np.float64)
+    pred_ref, _ = passes.predict_metrics([go], po, np.asarray(ref["coefficients"]), ref["intercept"])
+    pred = out["prediction_column"].cpu().numpy()
+    res = out["residuals"].cpu().numpy()
+    if fused:  # rows the rules drop stay in place: compare on the survivors
+        g_all = np.asarray(doc["guest"], dtype=np.int32)
+        p_all = np.asarray(doc["price"], dtype=np.float64)
+        keep = np.array([bool(passes.lib().orc_dq_keep(int(a), float(b))) for a, b in zip(g_all, p_all)])
+        assert (res[~keep] == 0).all()
+        pred, res = pred[keep], res[keep]
+    assert rel_err(pred, pred_ref) < RTOL
+    np.testing.assert_allclose(res, po - pred_ref, rtol=0, atol=1e-9 * np.abs(po).max())
+
+
+@pytest.mark.parametrize("fit_name", ["lab_wls_lasso", "ols_cholesky", "ridge_cholesky", "enet_wls", "nostd_enet_wls",
+                                      "lab_lbfgs_lasso", "enet_lbfgs", "ols_lbfgs", "nointercept_lbfgs"])
+def test_fit_synth_small_all_solvers(pkg, ctx, golden, fit_name):
+    """d = 4 with fused DQ: every solver branch against the golden fits (oracle) and scikit-learn."""
+    doc = golden("synth_small")
+    ref = doc["fits"][fit_name]
+    g, p, x = ctx.synth_generate(doc["n"], d=doc["d"], p_low=doc["p_low"], p_high=doc["p_high"])
+    cols = {"guest": g, "price": p, "label": p}
+    names = ["guest"]
+    for k in range(doc["d"] - 1):
+        cols[f"x{k + 1}"] = x[k]
+        names.append(f"x{k + 1}")
+    df = pkg.Frame(ctx, cols).with_fused_dq("guest", "price")
+    df = pkg.VectorAssembler().setInputCols(names).setOutputCol("features").transform(df)
+    model = estimator(pkg, ref["params"]).fit(df)
+    assert model.num_rows == doc["n_survivors"]
+    assert model.solver_used == ref["solver_used"]
+    s = model.summary()
+    assert s.totalIterations() == ref["total_iterations"]
+    assert rel_err(s.objectiveHistory(), ref["objective_history"]) < 1e-8
+    np.testing.assert_allclose(model.coefficients(), ref["coefficients"], rtol=1e-8, atol=1e-10)
+    np.testing.assert_allclose(model.intercept(), ref["intercept"], rtol=1e-8, atol=1e-10)
+    assert rel_err(s.rootMeanSquaredError(), ref["rmse"]) < 1e-8 and rel_err(s.r2(), ref["r2"]) < 1e-8
+    if "sklearn_coefficients" in ref:
+        np.testing.assert_allclose(model.coefficients(), ref["sklearn_coefficients"], rtol=2e-5, atol=2e-6)
+
+
+@pytest.mark.parametrize("d", [1, 3, 8, 16, 17, 32])
+def test_summarizer_and_lsq_passes_vs_oracle(pkg, ctx, d):
+    from sparkdq4ml_b200 import ml
+    n = 150_001
+    guest, price, feats = synth(n, d, p_low=0.04, p_high=0.04)
+    dfeats, dprice = to_dev(*feats), to_dev(price)[0]
+    ref = passes.summarizer(feats, price, dq=(guest, price), threads=4)
+    got = ml.summarize(ctx, dfeats, dprice, dq=(dfeats[0], dprice))
+    assert got["count"] == ref["count"]
+    for key in ("mean", "variance", "normL1", "normL2"):
+        assert rel_err(got[key], ref[key]) < 1e-10, key
+    for key in ("min", "max", "nnz"):
+        assert got[key].tolist() == ref[key].tolist(), key
+    rng = np.random.default_rng(d)
+    coef = rng.normal(size=d)
+    fstd, fmean = np.sqrt(ref["variance"][:d]), ref["mean"][:d]
+    ystd, ymean = np.sqrt(ref["variance"][d]), ref["mean"][d]
+    for fit_intercept in (True, False):
+        rl, rw, rg = passes.lsq_loss_grad(feats, price, coef, fstd, fmean, ystd, ymean, fit_intercept, dq=(guest, price), threads=4)
+        gl, gw, gg = ml.lsq_loss_grad(ctx, dfeats, dprice, coef, fstd, fmean, ystd, ymean, fit_intercept, dq=(dfeats[0], dprice))
+        assert gw == rw
+        assert rel_err(gl, rl) < 1e-10
+        np.testing.assert_allclose(gg, rg, rtol=1e-9, atol=1e-9 * np.abs(rg).max())
+
+
+def test_config3_shape_d16_owlqn_fused(pkg, ctx):
+    """BASELINE config 3 at a test-sized n: 16 features through VectorAssembler, l-bfgs solver, elasticNet 0.5."""
+    n, d = 400_000, 16
+    guest, price, feats = synth(n, d)
+    params = dict(max_iter=40, reg_param=0.3, elastic_net_param=0.5, solver="l-bfgs")
+    ref = spark_ml.linear_regression_fit(feats, price, spark_ml.LRParams(**params), dq=(guest, price), threads=8)
+    g, p, x = ctx.synth_generate(n, d=d)
+    cols = {"guest": g, "label": p}
+    names = ["guest"]
+    for k in range(d - 1):
+        cols[f"x{k + 1}"] = x[k]
+        names.append(f"x{k + 1}")
+    df = pkg.Frame(ctx, cols).with_fused_dq("guest", "label")
+    df = pkg.VectorAssembler().setInputCols(names).transform(df)
+    model = estimator(pkg, params).fit(df)
+    assert model.solver_used == ref.solver_used == "owlqn"
+    s = model.summary()
+    assert s.totalIterations() == ref.total_iterations and model.data_passes == ref.data_passes
+    assert rel_err(s.objectiveHistory(), ref.objective_history) < 1e-8
+    np.testing.assert_allclose(model.coefficients(), ref.coefficients, rtol=1e-7, atol=1e-9)
+    np.testing.assert_allclose(model.intercept(), ref.intercept, rtol=1e-8)
+
+
+def test_host_buffers_equal_device_buffers(pkg, ctx):
+    n = 50_000
+    guest, price, feats = synth(n, 3)
+    def fit(cols_g, cols_p, cols_x):
+        df = pkg.Frame(ctx, {"guest": cols_g, "price": cols_p, "label": cols_p, "x1": cols_x[0], "x2": cols_x[1]}).with_fused_dq()
+        df = pkg.VectorAssembler().setInputCols(["guest", "x1", "x2"]).transform(df)
+        m = pkg.LinearRegression().setMaxIter(40).setRegParam(0.2).setElasticNetParam(1.0).fit(df)
+        return m.coefficients(), m.intercept(), m.summary().rootMeanSquaredError()
+    host = fit(guest, price, feats[1:])
+    dev = fit(*to_dev(guest, price), to_dev(*feats[1:]))
+    assert host[0].tobytes() == dev[0].tobytes() and host[1] == dev[1] and host[2] == dev[2]
+
+
+def test_repeatability_bitwise(pkg, ctx):
+    from sparkdq4ml_b200 import ml
+    g, p, _ = ctx.synth_generate(3_000_001, d=1)
+    a = ml.wls_moments(ctx, [g], p, dq=(g, p))
+    b = ml.wls_moments(ctx, [g], p, dq=(g, p))
+    assert a.tobytes() == b.tobytes()
+
+
+def test_fit_at_config2_size_properties(pkg, ctx):
+    """BASELINE config 2 size (1e8 rows, d = 1, lasso): checked through size-independent properties + the oracle's fit."""
+    from sparkdq4ml_b200 import ml
+    n = 100_000_000
+    g, p, _ = ctx.synth_generate(n, d=1)
+    mom = ml.wls_moments(ctx, [g], p, dq=(g, p))
+    # linearity: moments of the whole = sum of the moments of two halves (shard boundary on a 1024-row multiple)
+    h = (n // 2) // 1024 * 1024
+    a = ml.wls_moments(ctx, [g[:h]], p[:h], dq=(g[:h], p[:h]))
+    b = ml.wls_moments(ctx, [g[h:]], p[h:], dq=(g[h:], p[h:]))
+    assert mom[0] == a[0] + b[0]
+    assert rel_err(mom, a + b) < 1e-12
+    # filter-then-aggregate == fused
+    go, po, _ = pkg.dq_filter(ctx, g, p)
+    assert go.shape[0] == mom[0]
+    assert rel_err(ml.wls_moments(ctx, [go], po), mom) < 1e-12
+    og, op, _ = passes.synth_generate(n, d=1)
+    ref_mom = passes.wls_moments([og], op, dq=(og, op), threads=passes.max_threads())
+    assert ref_mom[0] == mom[0] and rel_err(mom, ref_mom) < 1e-11
+    lr = pkg.LinearRegression().setMaxIter(40).setRegParam(1).setElasticNetParam(1)
+    df = pkg.VectorAssembler().setInputCols(["guest"]).transform(pkg.Frame(ctx, {"guest": g, "price": p, "label": p}).with_fused_dq())
+    model = lr.fit(df)
+    ref = spark_ml.wls_fit_from_moments(ref_mom, 1, spark_ml.LRParams(max_iter=40, reg_param=1.0, elastic_net_param=1.0))
+    assert rel_err(model.coefficients(), ref.coefficients) < RTOL and rel_err(model.intercept(), ref.intercept) < RTOL
+    assert rel_err(model.summary().objectiveHistory(), ref.objective_history) < RTOL
