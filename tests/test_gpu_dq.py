@@ -100,7 +100,8 @@ def test_filter_rejects_bad_arguments(pkg, ctx):
     L = pkg.capi.lib()
     rc = L.dq4ml_dq_filter(ctx.handle, g.data_ptr(), p.data_ptr(), 8, None, g.data_ptr(), p.data_ptr(), C.byref(n_out), None)
     assert rc == pkg.capi.ERR_INVALID  # in-place
-    rc = L.dq4ml_dq_filter(ctx.handle, g.data_ptr() + 4, p.data_ptr(), 4, None, g.data_ptr(), p.data_ptr(), C.byref(n_out), None)
+    go, po = torch.zeros_like(g), torch.zeros_like(p)
+    rc = L.dq4ml_dq_filter(ctx.handle, g.data_ptr() + 4, p.data_ptr(), 4, None, go.data_ptr(), po.data_ptr(), C.byref(n_out), None)
     assert rc == pkg.capi.ERR_INVALID and b"aligned" in L.dq4ml_last_error()
 
 
