@@ -236,7 +236,7 @@ int gather_inputs(dq4ml_ctx* ctx, const dq4ml_columns* features, const double* l
   out->cols.n = features->n_cols;
   for (int j = 0; j < features->n_cols; ++j) {
     const dq4ml_column& c = features->cols[j];
-    if (c.data == nullptr || (c.dtype != DQ4ML_I32 && c.dtype != DQ4ML_F64)) {
+    if ((c.data == nullptr && n > 0) || (c.dtype != DQ4ML_I32 && c.dtype != DQ4ML_F64)) {
       set_error("feature column %d: null data or unknown dtype %d", j, c.dtype);
       return DQ4ML_ERR_INVALID;
     }
@@ -245,13 +245,24 @@ int gather_inputs(dq4ml_ctx* ctx, const dq4ml_columns* features, const double* l
   }
   out->label = label;
   if (dq != nullptr) {
-    if (dq->guest == nullptr || dq->price == nullptr) {
+    if ((dq->guest == nullptr || dq->price == nullptr) && n > 0) {
       set_error("fused DQ needs both guest and price columns");
       return DQ4ML_ERR_INVALID;
     }
     out->dq.guest = dq->guest;
     out->dq.price = dq->price;
     out->dq.params = dq->params;
+  }
+  if (n == 0) {
+    // an empty shard still takes part in the pass (and in the cross-rank sum): give the kernels valid, unread pointers
+    const void* dummy = ctx->scratch.consts;
+    for (int j = 0; j < out->cols.n; ++j) out->cols.ptr[j] = dummy;
+    out->label = static_cast<const double*>(dummy);
+    if (dq != nullptr) {
+      out->dq.guest = static_cast<const int32_t*>(dummy);
+      out->dq.price = static_cast<const double*>(dummy);
+    }
+    return arena_reserve(ctx, out_bytes);
   }
   Resolver rs(ctx);
   for (int j = 0; j < out->cols.n; ++j)
@@ -740,7 +751,7 @@ int64_t dq4ml_summary_len(int32_t d) { return d < 0 ? 0 : 3 + 7 * (static_cast<i
 int dq4ml_wls_moments(dq4ml_ctx* ctx, const dq4ml_columns* features, const double* label, int64_t n,
                       const dq4ml_dq_fused* dq, double* out) {
   if (check_ctx(ctx) != DQ4ML_OK) return DQ4ML_ERR_INVALID;
-  if (out == nullptr || label == nullptr) {
+  if (out == nullptr || (label == nullptr && n > 0)) {
     set_error("wls_moments: null label or output");
     return DQ4ML_ERR_INVALID;
   }
@@ -778,7 +789,7 @@ int dq4ml_wls_solve(const double* moments, int32_t d, const dq4ml_lr_params* par
 int dq4ml_summarize(dq4ml_ctx* ctx, const dq4ml_columns* features, const double* label, int64_t n,
                     const dq4ml_dq_fused* dq, double* out) {
   if (check_ctx(ctx) != DQ4ML_OK) return DQ4ML_ERR_INVALID;
-  if (out == nullptr || label == nullptr) {
+  if (out == nullptr || (label == nullptr && n > 0)) {
     set_error("summarize: null label or output");
     return DQ4ML_ERR_INVALID;
   }
@@ -871,7 +882,7 @@ int dq4ml_lsq_loss_grad(dq4ml_ctx* ctx, const dq4ml_columns* features, const dou
                         const dq4ml_dq_fused* dq, const double* coef, const double* features_std,
                         const double* features_mean, double label_std, double label_mean, int fit_intercept, double* out) {
   if (check_ctx(ctx) != DQ4ML_OK) return DQ4ML_ERR_INVALID;
-  if (out == nullptr || label == nullptr || features == nullptr ||
+  if (out == nullptr || (label == nullptr && n > 0) || features == nullptr ||
       (features->n_cols > 0 && (coef == nullptr || features_std == nullptr || features_mean == nullptr))) {
     set_error("lsq_loss_grad: null argument");
     return DQ4ML_ERR_INVALID;
@@ -887,7 +898,7 @@ int dq4ml_lsq_loss_grad(dq4ml_ctx* ctx, const dq4ml_columns* features, const dou
 int dq4ml_linreg_fit(dq4ml_ctx* ctx, const dq4ml_columns* features, const double* label, int64_t n,
                      const dq4ml_lr_params* params, const dq4ml_dq_fused* dq, dq4ml_lr_model** out) {
   if (check_ctx(ctx) != DQ4ML_OK) return DQ4ML_ERR_INVALID;
-  if (out == nullptr || label == nullptr || features == nullptr) {
+  if (out == nullptr || (label == nullptr && n > 0) || features == nullptr) {
     set_error("linreg_fit: null argument");
     return DQ4ML_ERR_INVALID;
   }
@@ -1037,7 +1048,7 @@ int dq4ml_linreg_transform(dq4ml_ctx* ctx, const dq4ml_lr_model* m, const dq4ml_
 int dq4ml_linreg_evaluate(dq4ml_ctx* ctx, const dq4ml_lr_model* m, const dq4ml_columns* features, const double* label,
                           int64_t n, const dq4ml_dq_fused* dq, int fit_intercept, double* metrics, double* residuals) {
   if (check_ctx(ctx) != DQ4ML_OK) return DQ4ML_ERR_INVALID;
-  if (metrics == nullptr || label == nullptr) {
+  if (metrics == nullptr || (label == nullptr && n > 0)) {
     set_error("evaluate: null label / metrics");
     return DQ4ML_ERR_INVALID;
   }
