@@ -168,6 +168,26 @@ int dq4ml_dq_filter(dq4ml_ctx* ctx, const int32_t* guest, const double* price, i
                     const dq4ml_dq_params* params, int32_t* guest_out, double* price_out, int64_t* n_out,
                     int64_t* n_after_rule1);
 
+/* The same filter for callers that cannot let the library allocate.  No counterpart in the reference: it exists for
+ * hosts where the GPU's memory is already owned by another allocator (an executor-wide memory pool, say), or where the
+ * device-wide stall inside cudaMalloc/cudaFree is not tolerable.  It takes no dq4ml_ctx and calls no allocator of any
+ * kind: the compaction kernel's look-back words and row counters live in a fixed array compiled into the library
+ * (about 256 KB of every GPU that loads libdq4ml.so, held until the process exits), which caps one call at
+ * DQ4ML_NOALLOC_MAX_ROWS rows -- larger inputs are refused with DQ4ML_ERR_UNSUPPORTED.
+ *   - Call it with the device that owns the buffers current (cudaSetDevice); `stream` is a cudaStream_t (NULL = the
+ *     default stream).  guest/price/guest_out/price_out must be DEVICE memory (inputs 16-byte aligned, outputs sized
+ *     for n rows); n_out and n_after_rule1 (nullable) are HOST int64.  The call returns after `stream` has drained.
+ *   - The first call on each device looks up the array's device address; make that first call before starting any
+ *     stream capture.
+ *   - All calls on a device share the one array, and it keeps whatever the previous call left there; each call
+ *     re-zeroes the part it is about to use, on `stream`, before its kernel runs.  Two calls whose GPU work overlaps
+ *     (different streams or threads) would race on it: serialise them.
+ * Results are identical to dq4ml_dq_filter's (same kernel). */
+#define DQ4ML_NOALLOC_MAX_ROWS (1ll << 26) /* 67 108 864 rows per call */
+int dq4ml_dq_filter_noalloc(void* stream, const int32_t* guest, const double* price, int64_t n,
+                            const dq4ml_dq_params* params, int32_t* guest_out, double* price_out, int64_t* n_out,
+                            int64_t* n_after_rule1);
+
 /* ------------------------------------------------------------------------------------------------ LinearRegression */
 
 /* [host-only] */

@@ -352,3 +352,105 @@ cudaError_t launch_column_heads(const DeviceCols& cols, const double* label, int
 }
 
 }  // namespace dq4ml
+
+// =====================================================================================================================
+// dq4ml_dq_filter_noalloc -- the DQ filter for callers that must not let this library allocate.
+//
+// Who needs it: a host process whose GPU memory already belongs to somebody else's pool (a Spark executor running an
+// RMM-style allocator that reserved the whole device, for instance), or a caller on a latency-critical path where
+// the device-wide synchronisation hidden in cudaMalloc/cudaFree is not acceptable.  The regular entry point,
+// dq4ml_dq_filter, needs a dq4ml_ctx (whose creation allocates scratch) and grows its tile-status buffer with
+// cudaMalloc; this one takes no ctx and touches no allocator at all.
+//
+// Where the scratch lives instead: the look-back words of the compaction kernel (one 64-bit word per 2048-row tile)
+// plus the two row counters sit in the file-scope device array below.  It is part of the library image, so every GPU
+// that loads libdq4ml.so carries these ~256 KB until the process exits, whether or not this entry point is ever used.
+// That fixed size is what bounds the call: at most DQ4ML_NOALLOC_MAX_ROWS rows per call.
+#include <mutex>
+
+#include "context.hpp"
+
+namespace dq4ml {
+namespace {
+
+constexpr int64_t kNoAllocMaxRows = DQ4ML_NOALLOC_MAX_ROWS;
+constexpr int64_t kNoAllocMaxTiles = (kNoAllocMaxRows + kFilterTile - 1) / kFilterTile;
+constexpr int kNoAllocHeaderWords = 32;  // words [0,1] = the two row counters; the rest of the first 256 bytes is unused
+constexpr int kNoAllocMaxDevices = 64;
+
+// In host code this name is only a handle for the runtime, not an address a kernel could use; the device address is
+// looked up once per device with cudaGetSymbolAddress (below) and that pointer is what the kernel receives.
+static __device__ __align__(256) unsigned long long g_noalloc_scratch[kNoAllocHeaderWords + kNoAllocMaxTiles];
+
+std::mutex g_noalloc_mu;
+unsigned long long* g_noalloc_dev_ptr[kNoAllocMaxDevices] = {nullptr};
+
+// Set-up step: resolves the array's address on the CURRENT device, once per device.
+cudaError_t noalloc_scratch_on_current_device(unsigned long long** out) {
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  if (dev < 0 || dev >= kNoAllocMaxDevices) return cudaErrorInvalidDevice;
+  std::lock_guard<std::mutex> lock(g_noalloc_mu);
+  if (g_noalloc_dev_ptr[dev] == nullptr) {
+    void* p = nullptr;
+    e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+    if (e != cudaSuccess) return e;
+    g_noalloc_dev_ptr[dev] = static_cast<unsigned long long*>(p);
+  }
+  *out = g_noalloc_dev_ptr[dev];
+  return cudaSuccess;
+}
+
+}  // namespace
+}  // namespace dq4ml
+
+extern "C" int dq4ml_dq_filter_noalloc(void* stream, const int32_t* guest, const double* price, int64_t n,
+                                       const dq4ml_dq_params* params, int32_t* guest_out, double* price_out,
+                                       int64_t* n_out, int64_t* n_after_rule1) {
+  using namespace dq4ml;
+  if (n < 0 || n_out == nullptr || (n > 0 && (guest == nullptr || price == nullptr || guest_out == nullptr || price_out == nullptr))) {
+    set_error("dq_filter_noalloc: null column / output or negative n");
+    return DQ4ML_ERR_INVALID;
+  }
+  if (n > kNoAllocMaxRows) {
+    set_error("dq_filter_noalloc: %lld rows exceed the %lld-row limit of the built-in scratch (DQ4ML_NOALLOC_MAX_ROWS); "
+              "split the input or use dq4ml_dq_filter",
+              static_cast<long long>(n), static_cast<long long>(kNoAllocMaxRows));
+    return DQ4ML_ERR_UNSUPPORTED;
+  }
+  if (n > 0 && (static_cast<const void*>(guest) == static_cast<const void*>(guest_out) ||
+                static_cast<const void*>(price) == static_cast<const void*>(price_out))) {
+    set_error("dq_filter_noalloc: in-place compaction is not supported");
+    return DQ4ML_ERR_INVALID;
+  }
+  if (((reinterpret_cast<uintptr_t>(guest) | reinterpret_cast<uintptr_t>(price)) & 15u) != 0) {
+    set_error("dq_filter_noalloc: input columns must be 16-byte aligned device memory");
+    return DQ4ML_ERR_INVALID;
+  }
+  *n_out = 0;
+  if (n_after_rule1 != nullptr) *n_after_rule1 = 0;
+  if (n == 0) return DQ4ML_OK;
+  unsigned long long* scratch = nullptr;
+  cudaError_t e = noalloc_scratch_on_current_device(&scratch);
+  if (e != cudaSuccess) {
+    set_error("dq_filter_noalloc: cudaGetSymbolAddress(scratch): %s", cudaGetErrorString(e));
+    return e == cudaErrorNoDevice || e == cudaErrorInsufficientDriver ? DQ4ML_ERR_NO_DEVICE : DQ4ML_ERR_CUDA;
+  }
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  const dq4ml_dq_params p = params != nullptr ? *params : dq4ml_dq_params_default();
+  int64_t launched = 0;
+  // The array still holds the previous call's words: launch_dq_filter zeroes the counters and the first
+  // ceil(n / 2048) look-back words on `s` (cudaMemsetAsync, no allocation) before the kernel reads them.
+  e = launch_dq_filter(guest, price, n, p, guest_out, price_out, scratch + kNoAllocHeaderWords, scratch, s, &launched);
+  unsigned long long counts[2] = {0, 0};
+  if (e == cudaSuccess) e = cudaMemcpyAsync(counts, scratch, sizeof(counts), cudaMemcpyDeviceToHost, s);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(s);
+  if (e != cudaSuccess) {
+    set_error("dq_filter_noalloc: %s", cudaGetErrorString(e));
+    return DQ4ML_ERR_CUDA;
+  }
+  *n_out = static_cast<int64_t>(counts[0]);
+  if (n_after_rule1 != nullptr) *n_after_rule1 = static_cast<int64_t>(counts[1]);
+  return DQ4ML_OK;
+}
