@@ -217,9 +217,12 @@ bool multi_rank(const dq4ml_ctx* ctx) { return ctx->nccl != nullptr || ctx->allr
 
 // ---- column table plumbing -----------------------------------------------------------------------------------------
 struct PassInputs {
-  DeviceCols cols;
+  std::vector<const void*> ptr;  // every feature column (any width)
+  std::vector<int> dtype;
+  DeviceCols cols;               // the same table in the fixed-size form the streaming kernels take (width <= kMaxCols)
   const double* label = nullptr;
   DeviceDq dq;
+  int width() const { return static_cast<int>(ptr.size()); }
 };
 
 int gather_inputs(dq4ml_ctx* ctx, const dq4ml_columns* features, const double* label, int64_t n,
@@ -228,20 +231,21 @@ int gather_inputs(dq4ml_ctx* ctx, const dq4ml_columns* features, const double* l
     set_error("bad feature table / row count");
     return DQ4ML_ERR_INVALID;
   }
-  if (max_cols > kMaxCols) max_cols = kMaxCols;  // DeviceCols capacity
   if (features->n_cols > max_cols) {
     set_error("%d feature columns: this entry point handles at most %d", features->n_cols, max_cols);
     return DQ4ML_ERR_UNSUPPORTED;
   }
-  out->cols.n = features->n_cols;
-  for (int j = 0; j < features->n_cols; ++j) {
+  const int d = features->n_cols;
+  out->ptr.assign(d, nullptr);
+  out->dtype.assign(d, DQ4ML_F64);
+  for (int j = 0; j < d; ++j) {
     const dq4ml_column& c = features->cols[j];
     if ((c.data == nullptr && n > 0) || (c.dtype != DQ4ML_I32 && c.dtype != DQ4ML_F64)) {
       set_error("feature column %d: null data or unknown dtype %d", j, c.dtype);
       return DQ4ML_ERR_INVALID;
     }
-    out->cols.ptr[j] = c.data;
-    out->cols.dtype[j] = c.dtype;
+    out->ptr[j] = c.data;
+    out->dtype[j] = c.dtype;
   }
   out->label = label;
   if (dq != nullptr) {
@@ -253,25 +257,33 @@ int gather_inputs(dq4ml_ctx* ctx, const dq4ml_columns* features, const double* l
     out->dq.price = dq->price;
     out->dq.params = dq->params;
   }
+  int rc = DQ4ML_OK;
   if (n == 0) {
     // an empty shard still takes part in the pass (and in the cross-rank sum): give the kernels valid, unread pointers
     const void* dummy = ctx->scratch.consts;
-    for (int j = 0; j < out->cols.n; ++j) out->cols.ptr[j] = dummy;
+    for (int j = 0; j < d; ++j) out->ptr[j] = dummy;
     out->label = static_cast<const double*>(dummy);
     if (dq != nullptr) {
       out->dq.guest = static_cast<const int32_t*>(dummy);
       out->dq.price = static_cast<const double*>(dummy);
     }
-    return arena_reserve(ctx, out_bytes);
+    rc = arena_reserve(ctx, out_bytes);
+  } else {
+    Resolver rs(ctx);
+    for (int j = 0; j < d; ++j) rs.input(&out->ptr[j], static_cast<size_t>(n) * (out->dtype[j] == DQ4ML_I32 ? 4 : 8));
+    rs.input(reinterpret_cast<const void**>(&out->label), static_cast<size_t>(n) * 8);
+    rs.input(reinterpret_cast<const void**>(&out->dq.guest), static_cast<size_t>(n) * 4);
+    rs.input(reinterpret_cast<const void**>(&out->dq.price), static_cast<size_t>(n) * 8);
+    rs.reserve_output(out_bytes);
+    rc = rs.run();
   }
-  Resolver rs(ctx);
-  for (int j = 0; j < out->cols.n; ++j)
-    rs.input(&out->cols.ptr[j], static_cast<size_t>(n) * (out->cols.dtype[j] == DQ4ML_I32 ? 4 : 8));
-  rs.input(reinterpret_cast<const void**>(&out->label), static_cast<size_t>(n) * 8);
-  rs.input(reinterpret_cast<const void**>(&out->dq.guest), static_cast<size_t>(n) * 4);
-  rs.input(reinterpret_cast<const void**>(&out->dq.price), static_cast<size_t>(n) * 8);
-  rs.reserve_output(out_bytes);
-  return rs.run();
+  if (rc != DQ4ML_OK) return rc;
+  out->cols.n = d <= kMaxCols ? d : 0;
+  for (int j = 0; j < out->cols.n; ++j) {
+    out->cols.ptr[j] = out->ptr[j];
+    out->cols.dtype[j] = out->dtype[j];
+  }
+  return DQ4ML_OK;
 }
 
 // ---- the aggregation passes (device inputs) -------------------------------------------------------------------------
@@ -328,8 +340,8 @@ int wls_moments_any(dq4ml_ctx* ctx, const PassInputs& in, int64_t n, double* out
     set_error("label column is required");
     return DQ4ML_ERR_INVALID;
   }
-  if (in.cols.n <= 8) return wls_moments_small(ctx, in, n, out);
-  return gram_wls_moments(ctx, in.cols, in.label, in.dq, n, out);
+  if (in.width() <= 8) return wls_moments_small(ctx, in, n, out);
+  return gram_wls_moments(ctx, in.ptr, in.dtype, in.label, in.dq, n, out);
 }
 
 // Summarizer, core statistics (count, mean, sample variance per column; label last) for the l-bfgs branch.
@@ -498,6 +510,8 @@ void dq4ml_ctx_destroy(dq4ml_ctx* ctx) {
   if (ctx->stream != nullptr) cudaStreamSynchronize(ctx->stream);
   nccl_unbind(ctx);
   if (ctx->arena != nullptr) cudaFree(ctx->arena);
+  if (ctx->gram_scratch != nullptr) cudaFree(ctx->gram_scratch);
+  if (ctx->gram_host != nullptr) cudaFreeHost(ctx->gram_host);
   if (ctx->d_tile_state != nullptr) cudaFree(ctx->d_tile_state);
   if (ctx->scratch_base != nullptr) cudaFree(ctx->scratch_base);
   if (ctx->h_result != nullptr) cudaFreeHost(ctx->h_result);
@@ -797,13 +811,13 @@ int dq4ml_summarize(dq4ml_ctx* ctx, const dq4ml_columns* features, const double*
   PassInputs in;
   int rc = gather_inputs(ctx, features, label, n, dq, &in, 0, 4096);
   if (rc != DQ4ML_OK) return rc;
-  const int d = in.cols.n;
+  const int d = in.width();
   // every column (features, then the label) goes through the full summarizer in groups of four
   std::vector<const void*> ptrs;
   std::vector<int> dtypes;
   for (int j = 0; j < d; ++j) {
-    ptrs.push_back(in.cols.ptr[j]);
-    dtypes.push_back(in.cols.dtype[j]);
+    ptrs.push_back(in.ptr[j]);
+    dtypes.push_back(in.dtype[j]);
   }
   ptrs.push_back(in.label);
   dtypes.push_back(DQ4ML_F64);

@@ -36,6 +36,10 @@ struct dq4ml_ctx {
   char* arena = nullptr;  // staging for host-resident inputs/outputs
   size_t arena_cap = 0, arena_used = 0;
   std::unordered_map<const void*, void*> staged;  // host pointer -> device copy, per call
+  char* gram_scratch = nullptr;  // Gram pass (d > 8): column table, per-CTA partial tiles, packed result
+  size_t gram_cap = 0;
+  double* gram_host = nullptr;   // pinned copy of the packed result
+  size_t gram_host_cap = 0;
   int64_t launches = 0;
   // optional CUDA-event timing of the aggregation-pass kernels (bench.py's roofline leg)
   bool pass_timing = false;

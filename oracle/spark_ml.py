@@ -330,6 +330,16 @@ def cholesky_solve(aa_packed, ab):
     k = ab.size
     A = np.array(aa_packed, dtype=np.float64)
     b = np.array(ab, dtype=np.float64)
+    if k > 16:  # the real thing: LAPACK dppsv('U') on the packed matrix, exactly what Spark calls
+        try:
+            from scipy.linalg import lapack
+            x, info = lapack.dppsv(k, A, b, lower=0)
+            if info > 0:
+                raise SingularMatrixException(f"leading minor of order {info} is not positive definite")
+            if info == 0:
+                return np.asarray(x, dtype=np.float64).reshape(-1)
+        except ImportError:
+            pass
 
     def idx(i, j):  # i <= j
         return i + j * (j + 1) // 2

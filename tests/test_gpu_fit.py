@@ -228,3 +228,78 @@ def test_fit_at_config2_size_properties(pkg, ctx):
     ref = spark_ml.wls_fit_from_moments(ref_mom, 1, spark_ml.LRParams(max_iter=40, reg_param=1.0, elastic_net_param=1.0))
     assert rel_err(model.coefficients(), ref.coefficients) < RTOL and rel_err(model.intercept(), ref.intercept) < RTOL
     assert rel_err(model.summary().objectiveHistory(), ref.objective_history) < RTOL
+
+
+# ---------------------------------------------------------------------------------------------- K5: wide tables (Gram)
+
+def wide_table(n, d, seed=0, int_cols=(0,)):
+    """guest (int32) + d-1 synthetic f64 columns; label = price."""
+    guest, price, extra = passes.synth_generate(n, d=d, p_low=0.05, p_high=0.05)
+    feats = [guest] + [np.ascontiguousarray(extra[k]) for k in range(d - 1)]
+    return guest, price, feats
+
+
+@pytest.mark.parametrize("d,n", [(9, 1), (9, 31), (16, 32), (16, 4097), (33, 1000), (64, 50_001), (65, 20_000),
+                                 (130, 10_007), (256, 20_011)])
+def test_gram_wls_moments_vs_oracle(pkg, ctx, d, n):
+    from sparkdq4ml_b200 import ml
+    guest, price, feats = wide_table(n, d)
+    ref = passes.wls_moments(feats, price, dq=(guest, price), threads=8)
+    dfeats, dprice = to_dev(*feats), to_dev(price)[0]
+    got = ml.wls_moments(ctx, dfeats, dprice, dq=(dfeats[0], dprice))
+    assert got.shape == ref.shape
+    assert got[0] == ref[0] == got[1] == got[2]  # survivor count exact
+    scale = np.maximum(np.abs(ref), 1e-300)
+    assert float(np.max(np.abs(got - ref) / scale)) < 1e-11
+    again = ml.wls_moments(ctx, dfeats, dprice, dq=(dfeats[0], dprice))
+    assert again.tobytes() == got.tobytes()  # fixed-order reduction: bit-reproducible
+    nodq = ml.wls_moments(ctx, dfeats, dprice)
+    ref2 = passes.wls_moments(feats, price, threads=8)
+    assert float(np.max(np.abs(nodq - ref2) / np.maximum(np.abs(ref2), 1e-300))) < 1e-11
+    host = ml.wls_moments(ctx, feats, price, dq=(guest, price))  # host columns through the same entry point
+    assert host.tobytes() == got.tobytes()
+
+
+def test_gram_nan_and_inf_rows(pkg, ctx):
+    """Rows the rules drop may hold anything (-inf price is dropped by rule 1) and must not poison the sums; a NaN price
+    survives DQ (Spark ordering) and must poison exactly the sums Spark's would."""
+    from sparkdq4ml_b200 import ml
+    d, n = 12, 300
+    guest, price, feats = wide_table(n, d)
+    price = price.copy()
+    price[7] = -np.inf
+    feats[3] = feats[3].copy()
+    feats[3][7] = np.nan  # garbage in a dropped row
+    ref = passes.wls_moments(feats, price, dq=(guest, price))
+    got = ml.wls_moments(ctx, to_dev(*feats), to_dev(price)[0], dq=(to_dev(guest)[0], to_dev(price)[0]))
+    assert np.isfinite(ref).all() and np.isfinite(got).all()
+    assert float(np.max(np.abs(got - ref) / np.maximum(np.abs(ref), 1e-300))) < 1e-11
+    price[11] = np.nan
+    ref = passes.wls_moments(feats, price, dq=(guest, price))
+    got = ml.wls_moments(ctx, to_dev(*feats), to_dev(price)[0], dq=(to_dev(guest)[0], to_dev(price)[0]))
+    assert (np.isnan(ref) == np.isnan(got)).all() and got[0] == ref[0]
+
+
+@pytest.mark.parametrize("params", [dict(max_iter=40, reg_param=0.0, elastic_net_param=0.0, solver="normal"),
+                                    dict(max_iter=40, reg_param=0.1, elastic_net_param=0.0),
+                                    dict(max_iter=40, reg_param=0.05, elastic_net_param=0.5)])
+def test_config4_shape_d256_normal_equations(pkg, ctx, params):
+    """BASELINE config 4 at a test-sized n: 256 features, normal-equation solver (Cholesky, or OWL-QN over the Gram when
+    an L1 term is present), DQ fused."""
+    n, d = 60_000, 256
+    guest, price, feats = wide_table(n, d)
+    ref = spark_ml.linear_regression_fit(feats, price, spark_ml.LRParams(**params), dq=(guest, price), threads=8)
+    g, p, x = ctx.synth_generate(n, d=d, p_low=0.05, p_high=0.05)
+    cols = {"guest": g, "label": p}
+    names = ["guest"]
+    for k in range(d - 1):
+        cols[f"x{k + 1}"] = x[k]
+        names.append(f"x{k + 1}")
+    df = pkg.Frame(ctx, cols).with_fused_dq("guest", "label")
+    df = pkg.VectorAssembler().setInputCols(names).transform(df)
+    model = estimator(pkg, params).fit(df)
+    assert model.solver_used == ref.solver_used and model.num_rows == int(passes.wls_moments([guest], price, dq=(guest, price))[0])
+    assert model.summary().totalIterations() == ref.total_iterations
+    np.testing.assert_allclose(model.coefficients(), ref.coefficients, rtol=1e-6, atol=1e-8)
+    np.testing.assert_allclose(model.intercept(), ref.intercept, rtol=1e-7)
+    assert rel_err(model.summary().objectiveHistory(), ref.objective_history) < 1e-7
