@@ -650,7 +650,7 @@ int dq4ml_udf_minimumPriceRule(dq4ml_ctx* ctx, const double* price, const uint8_
   Resolver rs(ctx);
   rs.input(reinterpret_cast<const void**>(&price), static_cast<size_t>(n) * 8);
   rs.input(reinterpret_cast<const void**>(&price_valid), static_cast<size_t>(n));
-  rs.reserve_output(static_cast<size_t>(n) * 8);
+  if (!is_device_ptr(out)) rs.reserve_output(static_cast<size_t>(n) * 8);
   int rc = rs.run();
   if (rc != DQ4ML_OK) return rc;
   OutBuf ob = make_out(ctx, out, static_cast<size_t>(n) * 8);
@@ -684,7 +684,7 @@ int dq4ml_udf_priceCorrelationRule(dq4ml_ctx* ctx, const double* price, const in
   rs.input(reinterpret_cast<const void**>(&guest), static_cast<size_t>(n) * 4);
   rs.input(reinterpret_cast<const void**>(&price_valid), static_cast<size_t>(n));
   rs.input(reinterpret_cast<const void**>(&guest_valid), static_cast<size_t>(n));
-  rs.reserve_output(static_cast<size_t>(n) * 8);
+  if (!is_device_ptr(out)) rs.reserve_output(static_cast<size_t>(n) * 8);
   int rc = rs.run();
   if (rc != DQ4ML_OK) return rc;
   OutBuf ob = make_out(ctx, out, static_cast<size_t>(n) * 8);
@@ -725,8 +725,8 @@ int dq4ml_dq_filter(dq4ml_ctx* ctx, const int32_t* guest, const double* price, i
   Resolver rs(ctx);
   rs.input(reinterpret_cast<const void**>(&guest), static_cast<size_t>(n) * 4);
   rs.input(reinterpret_cast<const void**>(&price), static_cast<size_t>(n) * 8);
-  rs.reserve_output(static_cast<size_t>(n) * 4);
-  rs.reserve_output(static_cast<size_t>(n) * 8);
+  if (!is_device_ptr(guest_out)) rs.reserve_output(static_cast<size_t>(n) * 4);
+  if (!is_device_ptr(price_out)) rs.reserve_output(static_cast<size_t>(n) * 8);
   int rc = rs.run();
   if (rc != DQ4ML_OK) return rc;
   OutBuf og = make_out(ctx, guest_out, static_cast<size_t>(n) * 4);
@@ -1024,7 +1024,7 @@ static int eval_common(dq4ml_ctx* ctx, const dq4ml_lr_model* m, const dq4ml_colu
   }
   CallScope scope(ctx);
   PassInputs in;
-  int rc = gather_inputs(ctx, features, label, n, dq, &in, row_out_user != nullptr ? static_cast<size_t>(n) * 8 : 0, kMaxCols);
+  int rc = gather_inputs(ctx, features, label, n, dq, &in, (row_out_user != nullptr && !is_device_ptr(row_out_user)) ? static_cast<size_t>(n) * 8 : 0, kMaxCols);
   if (rc != DQ4ML_OK) return rc;
   OutBuf ob = make_out(ctx, row_out_user, static_cast<size_t>(n) * 8);
   EvalConsts c{};

@@ -6,10 +6,13 @@
 // Gram.  Here the same sums are a tiled Z^T Z with Z = [x_0 .. x_{d-1} | y | 1]:
 //   * the d columns are cut into blocks of 64; one CTA owns one upper-triangular block pair (bi <= bj) and a slice of
 //     the rows, and walks its rows in chunks of 32;
-//   * a producer warp stages each chunk of the 64 (+64) columns it needs with one TMA bulk copy per column
-//     (cp.async.bulk ... mbarrier::complete_tx, 256 B each: the columnar layout makes a 32-row chunk of a column one
-//     contiguous run), two stages deep, full/empty mbarriers;
-//   * four consumer warps first fix the chunk up in shared memory (int32 -> fp64 for integer columns, DQ predicate ->
+//   * the four warps stage each chunk of the 64 (+64) columns they need with 16-byte cp.async copies (the columnar
+//     layout makes a 32-row chunk of a column one contiguous 256-byte run) into an XOR-swizzled, padding-free layout,
+//     three stages deep.  (Round 1 first tried one TMA bulk copy -- cp.async.bulk + mbarrier -- per column chunk from
+//     a producer warp: 130 copies of 256 B per stage kept the consumers spinning on the full barrier and the pass
+//     stayed at 23 % of the fp64 peak, see profiles/r1_gram_tma_bulk_full.json; a column table of arbitrary pointers
+//     cannot be described by one tensor map, so the LSU path is the general one);
+//   * the warps then fix the chunk up in shared memory (int32 -> fp64 for integer columns, DQ predicate ->
 //     rows the rules drop are zeroed, the ones column becomes the keep mask), then each owns a 32 x 32 output tile as
 //     4 x 4 fragments of mma.sync.m8n8k4.f64 (DMMA) accumulated in registers; on diagonal pairs the fourth warp, whose
 //     tile lies below the diagonal, computes the border columns (X^T y, X^T 1) and the y/1 corner instead;
@@ -27,21 +30,27 @@ namespace dq4ml {
 namespace {
 
 constexpr int GT = 64;          // CTA tile edge in columns
-constexpr int GKC = 32;         // rows per pipeline stage
-constexpr int GKP = 36;         // shared-memory pitch of one column chunk in doubles (32 + 4: conflict-free fragment loads)
-constexpr int GSTAGES = 2;
-constexpr int GCONSUMERS = 128; // 4 consumer warps; warp 4 is the producer
-constexpr int GTHREADS = 160;
+constexpr int GKC = 32;         // rows per pipeline stage: one column chunk is 256 B (fp64) or 128 B (int32)
+constexpr int GSTAGES = 3;
+constexpr int GTHREADS = 128;   // 4 warps, each owning a 32 x 32 output tile
 constexpr int GPART = GT * GT + GT * 8 + 64;  // doubles per CTA partial: tile, border (64 x 8), corner (8 x 8)
 
+// Shared-memory layout of a staged chunk.  Each column chunk is a dense 256-byte row of 16 x 16-byte pieces; the
+// position of a piece is XOR-ed with twice the column's index mod 8, which makes the 8-byte fragment loads of
+// mma.m8n8k4 (8 columns x 4 consecutive rows per warp) conflict-free without any padding: 3 stages of both panels fit
+// twice in one SM's 227 KB.
 struct __align__(16) GramStage {
-  double a[GT][GKP];       // column block bi
-  double b[GT][GKP];       // column block bj (unused on diagonal pairs)
-  double border[8][GKP];   // column 0 = y, column 1 = ones/keep mask, 2..7 stay zero
+  double a[GT][GKC];       // column block bi
+  double b[GT][GKC];       // column block bj (unused on diagonal pairs)
+  double border[8][GKC];   // column 0 = y, column 1 = ones/keep mask, 2..7 stay zero
   double dqp[GKC];         // DQ price chunk
   int dqg[GKC];            // DQ guest chunk
 };
-constexpr size_t kGramSmem = GSTAGES * sizeof(GramStage) + 2 * GSTAGES * sizeof(unsigned long long) + 16 * sizeof(unsigned);
+constexpr size_t kGramSmem = GSTAGES * sizeof(GramStage) + 2 * GT * sizeof(void*) + 2 * GT + 2 * GT + 64;
+
+__device__ __forceinline__ int swz(int col, int k) {  // index (in doubles) of element k of column `col` inside its 32-double row
+  return ((((k >> 1) ^ ((col & 7) << 1)) << 1) | (k & 1));
+}
 
 struct GramArgs {
   const void* const* col_ptr;  // device array [d]
@@ -57,39 +66,24 @@ struct GramArgs {
 };
 
 __device__ __forceinline__ unsigned smem_u32(const void* p) { return static_cast<unsigned>(__cvta_generic_to_shared(p)); }
-__device__ __forceinline__ void mbar_init(unsigned long long* bar, unsigned count) {
-  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+// 16-byte asynchronous copy global -> shared (SASS: LDGSTS), bypassing L1
+__device__ __forceinline__ void cp_async16(void* dst, const void* src) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(dst)), "l"(src) : "memory");
 }
-__device__ __forceinline__ void mbar_expect_tx(unsigned long long* bar, unsigned bytes) {
-  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void mbar_arrive(unsigned long long* bar) {
-  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
-}
-__device__ __forceinline__ void mbar_wait(unsigned long long* bar, unsigned parity) {
-  unsigned ok;
-  do {
-    asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }"
-                 : "=r"(ok) : "r"(smem_u32(bar)), "r"(parity) : "memory");
-  } while (ok == 0u);
-}
-// TMA bulk copy global -> shared, completion counted in bytes on an mbarrier (SASS: UBLKCP)
-__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, unsigned bytes, unsigned long long* bar) {
-  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-               ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
-}
-__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
-__device__ __forceinline__ void consumer_sync() { asm volatile("bar.sync 1, %0;" ::"n"(GCONSUMERS) : "memory"); }
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 __device__ __forceinline__ void dmma884(double (&c)[2], double a, double b) {
   asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};" : "+d"(c[0]), "+d"(c[1]) : "d"(a), "d"(b));
 }
 
-__global__ void __launch_bounds__(GTHREADS) gram_tile_kernel(const GramArgs g) {
+__global__ void __launch_bounds__(GTHREADS, 2) gram_tile_kernel(const GramArgs g) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   GramStage* st = reinterpret_cast<GramStage*>(smem_raw);
-  unsigned long long* full = reinterpret_cast<unsigned long long*>(smem_raw + GSTAGES * sizeof(GramStage));
-  unsigned long long* empty = full + GSTAGES;
-  unsigned* s_mask = reinterpret_cast<unsigned*>(empty + GSTAGES);  // keep mask of the chunk in each stage
+  const void** s_colptr = reinterpret_cast<const void**>(smem_raw + GSTAGES * sizeof(GramStage));  // [2*GT]: A slots then B slots
+  unsigned char* s_isint = reinterpret_cast<unsigned char*>(s_colptr + 2 * GT);                    // [2*GT]
+  unsigned char* s_intslots = s_isint + 2 * GT;                                                    // [2*GT] compact list of int32 slots
+  int* s_meta = reinterpret_cast<int*>(s_intslots + 2 * GT);                                       // [0] = #int slots, [4..6] = keep mask per stage
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int kind = blockIdx.x % g.kinds, split = blockIdx.x / g.kinds;
@@ -103,64 +97,51 @@ __global__ void __launch_bounds__(GTHREADS) gram_tile_kernel(const GramArgs g) {
     }
   }
   const bool diag = bi == bj;
+  const int n_slots = diag ? GT : 2 * GT;
 
-  // zero every stage once: padding columns (>= d), border columns 2..7 and the unused rows stay zero for good
+  // zero every stage once: padding columns (>= d), border columns 2..7 and unused rows stay zero for good
   for (int i = tid; i < static_cast<int>(GSTAGES * sizeof(GramStage) / 8); i += GTHREADS) reinterpret_cast<double*>(smem_raw)[i] = 0.0;
-  if (tid == 0) {
-    for (int s = 0; s < GSTAGES; ++s) {
-      mbar_init(&full[s], 1);
-      mbar_init(&empty[s], GCONSUMERS / 32);
-    }
-    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  if (tid < 2 * GT) {
+    const int col = (tid < GT ? bi : bj) * GT + (tid & (GT - 1));
+    const bool live = tid < n_slots && col < g.d;
+    s_colptr[tid] = live ? g.col_ptr[col] : nullptr;
+    s_isint[tid] = live ? g.col_i32[col] : 0;
   }
-  fence_proxy_async();
   __syncthreads();
+  if (tid == 0) {
+    int m = 0;
+    for (int s = 0; s < n_slots; ++s)
+      if (s_isint[s]) s_intslots[m++] = static_cast<unsigned char>(s);
+    s_meta[0] = m;
+  }
+  __syncthreads();
+  const int n_int = s_meta[0];
 
   const long long full_chunks = g.n / GKC;
   const long long my_iters = full_chunks > split ? (full_chunks - split + g.splits - 1) / g.splits : 0;
 
-  if (warp == 4) {
-    // ------------------------------------------------------------------ producer: one bulk copy per column chunk
-    unsigned bytes = 0;
-    for (int c = lane; c < GT; c += 32) {
-      const int ca = bi * GT + c, cb = bj * GT + c;
-      if (ca < g.d) bytes += g.col_i32[ca] ? GKC * 4u : GKC * 8u;
-      if (!diag && cb < g.d) bytes += g.col_i32[cb] ? GKC * 4u : GKC * 8u;
-    }
-#pragma unroll
-    for (int off = 16; off > 0; off >>= 1) bytes += __shfl_xor_sync(0xffffffffu, bytes, off);
-    if (diag) bytes += GKC * 8u;               // y
-    if (g.has_dq) bytes += GKC * 4u + GKC * 8u;  // DQ guest + price
-    for (long long it = 0; it < my_iters; ++it) {
-      const int s = static_cast<int>(it % GSTAGES);
-      const unsigned use = static_cast<unsigned>(it / GSTAGES);
-      mbar_wait(&empty[s], (use & 1u) ^ 1u);
-      const long long row = (split + it * g.splits) * GKC;
-      if (lane == 0) mbar_expect_tx(&full[s], bytes);
-      __syncwarp();
-      for (int c = lane; c < GT; c += 32) {
-        const int ca = bi * GT + c, cb = bj * GT + c;
-        if (ca < g.d) {
-          if (g.col_i32[ca]) bulk_g2s(reinterpret_cast<int*>(&st[s].a[c][0]) + GKC, static_cast<const int*>(g.col_ptr[ca]) + row, GKC * 4u, &full[s]);
-          else bulk_g2s(&st[s].a[c][0], static_cast<const double*>(g.col_ptr[ca]) + row, GKC * 8u, &full[s]);
-        }
-        if (!diag && cb < g.d) {
-          if (g.col_i32[cb]) bulk_g2s(reinterpret_cast<int*>(&st[s].b[c][0]) + GKC, static_cast<const int*>(g.col_ptr[cb]) + row, GKC * 4u, &full[s]);
-          else bulk_g2s(&st[s].b[c][0], static_cast<const double*>(g.col_ptr[cb]) + row, GKC * 8u, &full[s]);
-        }
-      }
-      if (lane == 0) {
-        if (diag) bulk_g2s(&st[s].border[0][0], g.label + row, GKC * 8u, &full[s]);
-        if (g.has_dq) {
-          bulk_g2s(&st[s].dqg[0], g.dq_guest + row, GKC * 4u, &full[s]);
-          bulk_g2s(&st[s].dqp[0], g.dq_price + row, GKC * 8u, &full[s]);
-        }
+  // every thread copies pieces idx = tid, tid + 128, ... of the stage: piece = (slot, 16-byte chunk)
+  auto issue_stage = [&](long long it) {
+    GramStage& S = st[it % GSTAGES];
+    const long long row = (split + it * g.splits) * GKC;
+    for (int idx = tid; idx < n_slots * 16; idx += GTHREADS) {
+      const int slot = idx >> 4, ch = idx & 15;
+      const void* base = s_colptr[slot];
+      if (base == nullptr) continue;
+      double* dst_row = slot < GT ? S.a[slot] : S.b[slot - GT];
+      if (!s_isint[slot]) {
+        cp_async16(dst_row + ((ch ^ ((slot & 7) << 1)) << 1), static_cast<const double*>(base) + row + ch * 2);
+      } else if (ch < 8) {  // int32 chunk (128 B) parked, unswizzled, in the upper half of its row until it is widened
+        cp_async16(reinterpret_cast<int*>(dst_row) + GKC + ch * 4, static_cast<const int*>(base) + row + ch * 4);
       }
     }
-    return;
-  }
+    if (diag && tid < 16) cp_async16(&S.border[0][0] + (tid << 1), g.label + row + tid * 2);  // y: border column 0 (col & 7 == 0: no swizzle)
+    if (g.has_dq) {
+      if (tid >= 32 && tid < 48) cp_async16(&S.dqp[(tid - 32) * 2], g.dq_price + row + (tid - 32) * 2);
+      if (tid >= 64 && tid < 72) cp_async16(&S.dqg[(tid - 64) * 4], g.dq_guest + row + (tid - 64) * 4);
+    }
+  };
 
-  // -------------------------------------------------------------------- consumers
   const int wm = warp >> 1, wn = warp & 1;
   const bool border_warp = diag && warp == 2;  // tile (1,0) of a diagonal pair lies below the diagonal
   double acc[4][4][2];
@@ -173,51 +154,48 @@ __global__ void __launch_bounds__(GTHREADS) gram_tile_kernel(const GramArgs g) {
   for (int i = 0; i < 8; ++i) accb[i][0] = accb[i][1] = 0.0;
 
   // fix-up of one staged chunk + the MMAs over it.  rows_valid < GKC only for the tail chunk.
-  auto consume = [&](GramStage& S, unsigned* mask_slot, bool convert, int rows_valid) {
-    if (convert) {  // integer columns were staged as int32 in the upper half of their slot: widen in place
-      for (int c = warp; c < GT; c += GCONSUMERS / 32) {
-        const int ca = bi * GT + c, cb = bj * GT + c;
-        if (ca < g.d && g.col_i32[ca]) {
-          const int v = reinterpret_cast<const int*>(&S.a[c][0])[GKC + lane];
-          __syncwarp();
-          S.a[c][lane] = static_cast<double>(v);
-        }
-        if (!diag && cb < g.d && g.col_i32[cb]) {
-          const int v = reinterpret_cast<const int*>(&S.b[c][0])[GKC + lane];
-          __syncwarp();
-          S.b[c][lane] = static_cast<double>(v);
-        }
+  auto consume = [&](GramStage& S, int* mask_slot, bool convert, int rows_valid) {
+    if (convert) {  // widen parked int32 chunks in place (whole warp reads before anyone writes)
+      for (int q = warp; q < n_int; q += GTHREADS / 32) {
+        const int slot = s_intslots[q];
+        double* row = slot < GT ? S.a[slot] : S.b[slot - GT];
+        const int v = reinterpret_cast<const int*>(row)[GKC + lane];
+        __syncwarp();
+        row[swz(slot, lane)] = static_cast<double>(v);
       }
     }
     if (warp == 0) {
       bool keep = lane < rows_valid;
       if (keep && g.has_dq) keep = dq_keep(S.dqg[lane], S.dqp[lane], g.t);
       const unsigned m = __ballot_sync(0xffffffffu, keep);
-      if (lane == 0) *mask_slot = m;
-      if (diag) S.border[1][lane] = keep ? 1.0 : 0.0;
+      if (lane == 0) *mask_slot = static_cast<int>(m);
+      if (diag) S.border[1][swz(1, lane)] = keep ? 1.0 : 0.0;
     }
-    consumer_sync();
-    const unsigned dropped = ~(*mask_slot);
+    __syncthreads();
+    const unsigned dropped = ~static_cast<unsigned>(*mask_slot);
     if (dropped != 0u) {  // rows the DQ rules (or the end of the data) remove contribute nothing: zero them in every column
       for (unsigned m = dropped; m != 0u; m &= m - 1u) {
         const int r = __ffs(m) - 1;
-        if (tid < GT) S.a[tid][r] = 0.0;
-        else if (!diag) S.b[tid - GT][r] = 0.0;
-        if (diag && tid == GT) S.border[0][r] = 0.0;
+        if (tid < GT) S.a[tid][swz(tid, r)] = 0.0;
+        else if (!diag) S.b[tid - GT][swz(tid - GT, r)] = 0.0;
+        if (diag && tid == GT) S.border[0][swz(0, r)] = 0.0;
       }
-      consumer_sync();
+      __syncthreads();
     }
-    const double(*A)[GKP] = S.a;
-    const double(*B)[GKP] = diag ? S.a : S.b;
+    const double(*A)[GKC] = S.a;
+    const double(*B)[GKC] = diag ? S.a : S.b;
     const int fr = lane >> 2, fk = lane & 3;
+    // fragment element (column c0 + fr, row k0 + fk): all columns of a fragment share (c & 7) == fr
+    const int sw = (fr << 1);
     if (!border_warp) {
 #pragma unroll
       for (int k0 = 0; k0 < GKC; k0 += 4) {
+        const int off = (((((k0 + fk) >> 1) ^ sw) << 1) | (fk & 1));
         double af[4], bf[4];
 #pragma unroll
-        for (int i = 0; i < 4; ++i) af[i] = A[wm * 32 + i * 8 + fr][k0 + fk];
+        for (int i = 0; i < 4; ++i) af[i] = A[wm * 32 + i * 8 + fr][off];
 #pragma unroll
-        for (int j = 0; j < 4; ++j) bf[j] = B[wn * 32 + j * 8 + fr][k0 + fk];
+        for (int j = 0; j < 4; ++j) bf[j] = B[wn * 32 + j * 8 + fr][off];
 #pragma unroll
         for (int i = 0; i < 4; ++i)
 #pragma unroll
@@ -226,47 +204,50 @@ __global__ void __launch_bounds__(GTHREADS) gram_tile_kernel(const GramArgs g) {
     } else {
 #pragma unroll
       for (int k0 = 0; k0 < GKC; k0 += 4) {
-        const double bb = S.border[fr][k0 + fk];
+        const int off = (((((k0 + fk) >> 1) ^ sw) << 1) | (fk & 1));
+        const double bb = S.border[fr][off];
 #pragma unroll
-        for (int i = 0; i < 8; ++i) dmma884(accb[i], A[i * 8 + fr][k0 + fk], bb);
+        for (int i = 0; i < 8; ++i) dmma884(accb[i], A[i * 8 + fr][off], bb);
         if (bi == 0) dmma884(corner, bb, bb);
       }
     }
   };
 
-  for (long long it = 0; it < my_iters; ++it) {
-    const int s = static_cast<int>(it % GSTAGES);
-    const unsigned use = static_cast<unsigned>(it / GSTAGES);
-    mbar_wait(&full[s], use & 1u);
-    consume(st[s], &s_mask[s], true, GKC);
-    fence_proxy_async();  // our generic-proxy writes to this stage precede the producer's next bulk copy into it
-    __syncwarp();
-    if (lane == 0) mbar_arrive(&empty[s]);
+  // ---- 3-stage cp.async pipeline: chunk it+2 is in flight while chunk it is fixed up and multiplied
+  for (int pre = 0; pre < GSTAGES - 1; ++pre) {
+    if (pre < my_iters) issue_stage(pre);
+    cp_async_commit();
   }
+  for (long long it = 0; it < my_iters; ++it) {
+    cp_async_wait<GSTAGES - 2>();  // this thread's copies of chunk `it` have landed
+    __syncthreads();               // ... and everybody's; also: everyone is done with chunk it-1, whose stage is reused next
+    if (it + GSTAGES - 1 < my_iters) issue_stage(it + GSTAGES - 1);
+    cp_async_commit();
+    consume(st[it % GSTAGES], &s_meta[4 + it % GSTAGES], n_int > 0, GKC);
+  }
+  cp_async_wait<0>();
 
-  // tail chunk (n % 32 rows): plain loads by the consumers of the CTA whose turn it is
+  // tail chunk (n % 32 rows): plain loads by the CTA whose turn it is
   const int tail_rows = static_cast<int>(g.n - full_chunks * GKC);
   if (tail_rows > 0 && static_cast<int>(full_chunks % g.splits) == split) {
-    consumer_sync();
-    GramStage& S = st[0];  // every stage has been released by now
+    __syncthreads();
+    GramStage& S = st[0];
     const long long row0 = full_chunks * GKC;
-    for (int idx = tid; idx < 2 * GT * GKC; idx += GCONSUMERS) {
-      const int r = idx % GKC, c = (idx / GKC) % GT, which = idx / (GKC * GT);
-      if (which == 1 && diag) continue;
-      const int col = (which == 0 ? bi : bj) * GT + c;
+    for (int idx = tid; idx < n_slots * GKC; idx += GTHREADS) {
+      const int r = idx % GKC, slot = idx / GKC;
       double v = 0.0;
-      if (col < g.d && r < tail_rows)
-        v = g.col_i32[col] ? static_cast<double>(static_cast<const int*>(g.col_ptr[col])[row0 + r])
-                           : static_cast<const double*>(g.col_ptr[col])[row0 + r];
-      (which == 0 ? S.a : S.b)[c][r] = v;
+      if (s_colptr[slot] != nullptr && r < tail_rows)
+        v = s_isint[slot] ? static_cast<double>(static_cast<const int*>(s_colptr[slot])[row0 + r])
+                          : static_cast<const double*>(s_colptr[slot])[row0 + r];
+      (slot < GT ? S.a[slot] : S.b[slot - GT])[swz(slot, r)] = v;
     }
     if (tid < GKC) {
-      S.border[0][tid] = (diag && tid < tail_rows) ? g.label[row0 + tid] : 0.0;
+      S.border[0][swz(0, tid)] = (diag && tid < tail_rows) ? g.label[row0 + tid] : 0.0;
       S.dqg[tid] = (g.has_dq && tid < tail_rows) ? g.dq_guest[row0 + tid] : 0;
       S.dqp[tid] = (g.has_dq && tid < tail_rows) ? g.dq_price[row0 + tid] : 0.0;
     }
-    consumer_sync();
-    consume(S, &s_mask[0], false, tail_rows);
+    __syncthreads();
+    consume(S, &s_meta[4], false, tail_rows);
   }
 
   // -------------------------------------------------------------------- partial tile -> scratch
@@ -328,7 +309,8 @@ int gram_wls_moments(dq4ml_ctx* ctx, const std::vector<const void*>& col_ptrs, c
   const int kinds = nb * (nb + 1) / 2;
   const int64_t len = 5 + 2LL * d + static_cast<int64_t>(d) * (d + 1) / 2;
   const int64_t full_chunks = n / GKC;
-  int64_t splits = (2LL * ctx->sm_count + kinds - 1) / kinds;
+  // one wave exactly: 2 CTAs fit per SM (registers and shared memory), and a 297th CTA would double the run time
+  int64_t splits = (2LL * ctx->sm_count) / kinds;
   if (splits > full_chunks) splits = full_chunks;
   if (splits < 1) splits = 1;
   const size_t table_bytes = (static_cast<size_t>(d) * 9 + 255) & ~static_cast<size_t>(255);
