@@ -120,19 +120,38 @@ __global__ void __launch_bounds__(GTHREADS, 2) gram_tile_kernel(const GramArgs g
   const long long full_chunks = g.n / GKC;
   const long long my_iters = full_chunks > split ? (full_chunks - split + g.splits - 1) / g.splits : 0;
 
-  // every thread copies pieces idx = tid, tid + 128, ... of the stage: piece = (slot, 16-byte chunk)
+  // Every thread copies the same 16 (8 on diagonal pairs) pieces of every stage: piece i = 16-byte chunk `ch` of column
+  // slot (tid >> 4) + 8 i.  Their global addresses differ between stages only by the row offset, so the per-piece base
+  // pointers live in registers for the whole kernel (loading them from shared memory per stage cost ~800 cycles per
+  // chunk in the first version: 16 dependent LDS -> branch pairs).
+  const int ch = tid & 15, slot0 = tid >> 4;
+  const char* src[16];
+  unsigned live = 0, ints = 0;
+#pragma unroll
+  for (int i = 0; i < 16; ++i) {
+    const int slot = slot0 + 8 * i;
+    const char* base = slot < n_slots ? static_cast<const char*>(s_colptr[slot]) : nullptr;
+    const bool is_int = base != nullptr && s_isint[slot] != 0;
+    src[i] = base != nullptr ? base + ch * 16 : nullptr;
+    if (base != nullptr && (!is_int || ch < 8)) live |= 1u << i;  // an int32 chunk is 128 B: only 8 pieces
+    if (is_int) ints |= 1u << i;
+  }
+  // destination of piece i inside a stage: its column's 256-byte row, chunk position XOR-swizzled (fp64) or parked
+  // unswizzled in the upper half of the row until it is widened (int32)
+  const unsigned dst_f64 = static_cast<unsigned>(slot0 * 256 + ((ch ^ ((slot0 & 7) << 1)) << 4));
+  const unsigned dst_i32 = static_cast<unsigned>(slot0 * 256 + 128 + ch * 16);
+
   auto issue_stage = [&](long long it) {
     GramStage& S = st[it % GSTAGES];
     const long long row = (split + it * g.splits) * GKC;
-    for (int idx = tid; idx < n_slots * 16; idx += GTHREADS) {
-      const int slot = idx >> 4, ch = idx & 15;
-      const void* base = s_colptr[slot];
-      if (base == nullptr) continue;
-      double* dst_row = slot < GT ? S.a[slot] : S.b[slot - GT];
-      if (!s_isint[slot]) {
-        cp_async16(dst_row + ((ch ^ ((slot & 7) << 1)) << 1), static_cast<const double*>(base) + row + ch * 2);
-      } else if (ch < 8) {  // int32 chunk (128 B) parked, unswizzled, in the upper half of its row until it is widened
-        cp_async16(reinterpret_cast<int*>(dst_row) + GKC + ch * 4, static_cast<const int*>(base) + row + ch * 4);
+    const unsigned sbase = smem_u32(&S.a[0][0]);
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+      if ((live >> i) & 1u) {
+        const bool is_int = (ints >> i) & 1u;
+        const char* p = src[i] + (is_int ? row * 4 : row * 8);
+        const unsigned dst = sbase + 2048u * i + (is_int ? dst_i32 : dst_f64);
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(p) : "memory");
       }
     }
     if (diag && tid < 16) cp_async16(&S.border[0][0] + (tid << 1), g.label + row + tid * 2);  // y: border column 0 (col & 7 == 0: no swizzle)
@@ -149,9 +168,7 @@ __global__ void __launch_bounds__(GTHREADS, 2) gram_tile_kernel(const GramArgs g
   for (int i = 0; i < 4; ++i)
 #pragma unroll
     for (int j = 0; j < 4; ++j) acc[i][j][0] = acc[i][j][1] = 0.0;
-  double accb[8][2], corner[2] = {0.0, 0.0};
-#pragma unroll
-  for (int i = 0; i < 8; ++i) accb[i][0] = accb[i][1] = 0.0;
+  // the border warp keeps its 8 border fragments in acc[i & 3][i >> 2] and the corner in acc[0][2]
 
   // fix-up of one staged chunk + the MMAs over it.  rows_valid < GKC only for the tail chunk.
   auto consume = [&](GramStage& S, int* mask_slot, bool convert, int rows_valid) {
@@ -207,8 +224,8 @@ __global__ void __launch_bounds__(GTHREADS, 2) gram_tile_kernel(const GramArgs g
         const int off = (((((k0 + fk) >> 1) ^ sw) << 1) | (fk & 1));
         const double bb = S.border[fr][off];
 #pragma unroll
-        for (int i = 0; i < 8; ++i) dmma884(accb[i], A[i * 8 + fr][off], bb);
-        if (bi == 0) dmma884(corner, bb, bb);
+        for (int i = 0; i < 8; ++i) dmma884(acc[i & 3][i >> 2], A[i * 8 + fr][off], bb);
+        if (bi == 0) dmma884(acc[0][2], bb, bb);
       }
     }
   };
@@ -264,8 +281,8 @@ __global__ void __launch_bounds__(GTHREADS, 2) gram_tile_kernel(const GramArgs g
   } else {
 #pragma unroll
     for (int i = 0; i < 8; ++i)
-      *reinterpret_cast<double2*>(&P[GT * GT + (i * 8 + fr) * 8 + fc]) = make_double2(accb[i][0], accb[i][1]);
-    *reinterpret_cast<double2*>(&P[GT * GT + GT * 8 + fr * 8 + fc]) = make_double2(corner[0], corner[1]);
+      *reinterpret_cast<double2*>(&P[GT * GT + (i * 8 + fr) * 8 + fc]) = make_double2(acc[i & 3][i >> 2][0], acc[i & 3][i >> 2][1]);
+    *reinterpret_cast<double2*>(&P[GT * GT + GT * 8 + fr * 8 + fc]) = make_double2(acc[0][2][0], acc[0][2][1]);
   }
 }
 
