@@ -209,8 +209,15 @@ def run_ours(args):
     # the timed region lasts only milliseconds: start the clock sampler first and keep the same step running untimed
     # for a while so that nvidia-smi (50 ms period) sees the GPU under this load, then go straight into the timed steps
     sampler = ClockSampler(local_rank) if rank == 0 else None
-    t_pre = time.perf_counter()
-    while time.perf_counter() - t_pre < args.preroll_seconds:
+    # every rank must run the same number of steps (each fit contains a collective): rank 0 sizes the pre-roll from
+    # its warm-up speed and tells the others
+    t0 = time.perf_counter()
+    model = lr.fit(df)
+    per_step = max(time.perf_counter() - t0, 1e-5)
+    pre_steps = torch.tensor([min(int(args.preroll_seconds / per_step), 20000)], dtype=torch.int64, device=f"cuda:{local_rank}")
+    if world > 1:
+        dist.broadcast(pre_steps, src=0)
+    for _ in range(int(pre_steps.item())):
         model = lr.fit(df)
     ctx.enable_pass_timing(True)
     l0 = ctx.launch_count

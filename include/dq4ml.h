@@ -172,7 +172,7 @@ int dq4ml_dq_filter(dq4ml_ctx* ctx, const int32_t* guest, const double* price, i
  * hosts where the GPU's memory is already owned by another allocator (an executor-wide memory pool, say), or where the
  * device-wide stall inside cudaMalloc/cudaFree is not tolerable.  It takes no dq4ml_ctx and calls no allocator of any
  * kind: the compaction kernel's look-back words and row counters live in a fixed array compiled into the library
- * (about 256 KB of every GPU that loads libdq4ml.so, held until the process exits), which caps one call at
+ * (about 128 KB of every GPU that loads libdq4ml.so, held until the process exits), which caps one call at
  * DQ4ML_NOALLOC_MAX_ROWS rows -- larger inputs are refused with DQ4ML_ERR_UNSUPPORTED.
  *   - Call it with the device that owns the buffers current (cudaSetDevice); `stream` is a cudaStream_t (NULL = the
  *     default stream).  guest/price/guest_out/price_out must be DEVICE memory (inputs 16-byte aligned, outputs sized

@@ -64,13 +64,20 @@ __global__ void __launch_bounds__(256) udf_price_corr_kernel(const double* __res
 }
 
 // ------------------------------------------------------------------------------------------ filter + compaction
-// One CTA per tile of kFilterThreads x 4 consecutive rows.  Tile t publishes its survivor count in tile_state[t] as
-// {flag:2 | value:62}; flag 1 = "aggregate of this tile", flag 2 = "inclusive prefix up to this tile".  A tile finds
-// its output offset by walking back over its predecessors' words (decoupled look-back), so the data is read once and
-// written once, and the output order is the input order (Spark's filter is order preserving within a partition).
-constexpr int kFilterThreads = 512;
-constexpr int kFilterRows = 4;
-constexpr int64_t kFilterTile = static_cast<int64_t>(kFilterThreads) * kFilterRows;
+// One CTA of 256 threads per tile of 4096 consecutive rows; warp w owns rows [512 w, 512 w + 512) of the tile and its
+// lane l the rows l, l + 32, ... of that slice (coalesced 4- and 8-byte loads).  Tile t publishes its
+// survivor count in tile_state[t] as {flag:2 | value:62}; flag 1 = "aggregate of this tile", flag 2 = "inclusive prefix
+// up to this tile".  A tile finds its output offset by walking back over its predecessors' words (decoupled
+// look-back), so the data is read once and written once, and the output order is the input order (Spark's filter is
+// order preserving within a partition).  Survivors are first compacted in shared memory, then written out coalesced.
+//
+// Round-1 history (profiles/): 2048-row tiles with direct per-thread stores ran at 0.33 of the HBM roofline with 62 %
+// of the warp stalls on the barrier behind warp 0's look-back -- with ~600 tiles in flight the walk back to the nearest
+// published prefix took ~10 L2 round trips.  Doubling the tile and halving the CTAs in flight shortens that walk, and
+// the other warps park their survivors in shared memory while warp 0 walks.
+constexpr int kFilterThreads = 256;
+constexpr int64_t kFilterTile = 4096;  // rows per tile: 16 per thread
+constexpr size_t kFilterSmem = kFilterTile * (sizeof(double) + sizeof(int));    // 48 KB of staged survivors
 constexpr unsigned long long kFlagAgg = 1ull << 62, kFlagPrefix = 2ull << 62, kValueMask = (1ull << 62) - 1;
 
 __device__ __forceinline__ unsigned long long ld_state(const unsigned long long* p) {
@@ -82,107 +89,138 @@ __device__ __forceinline__ void st_state(unsigned long long* p, unsigned long lo
   asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
 
+// One short-lived CTA per tile; blockIdx order is dispatch order, so every predecessor of a running tile has started.
+// Measured alternatives (round 1, 10^9 rows): 512 x 4-row threads with per-thread stores 0.33 of the HBM roofline;
+// 256 threads x 16 rows (128-bit loads, shuffle scans, shared-memory staging) 0.51; persistent CTAs with cp.async
+// prefetch of the next tile and a ticket counter 0.20 (every round turns into a grid-wide barrier on the slowest CTA);
+// 512 threads x 8 rows 0.43.  An ablation of the 0.51 shape without look-back and write-out still took 4.15 ms per 10^9
+// rows: the tile-local work was instruction-bound (~67 thread instructions per row: 5-step shuffle scans and 4-way
+// bank-conflicted parking).  Hence the striped row assignment below: lane l of a warp owns rows l, l + 32, ... of the
+// warp's 512-row slice, so one __ballot_sync per 32 rows replaces the scans and survivors of one ballot land on
+// consecutive shared-memory words.
 __global__ void __launch_bounds__(kFilterThreads)
     dq_filter_compact_kernel(const int* __restrict__ guest, const double* __restrict__ price, const int64_t n,
                              const DqThresholds t, int* __restrict__ guest_out, double* __restrict__ price_out,
                              unsigned long long* __restrict__ tile_state, unsigned long long* __restrict__ counters) {
-  __shared__ unsigned int s_warp_keep[kFilterThreads / 32];
-  __shared__ unsigned int s_warp_rule1[kFilterThreads / 32];
-  __shared__ unsigned long long s_tile_offset;
+  extern __shared__ __align__(16) unsigned char filter_smem[];
+  double* s_price = reinterpret_cast<double*>(filter_smem);              // survivors of the tile, in row order
+  int* s_guest = reinterpret_cast<int*>(filter_smem + kFilterTile * sizeof(double));
+  constexpr int kWarps = kFilterThreads / 32;
+  constexpr int kPerLane = kFilterTile / kFilterThreads;  // 16 rows per thread
+  __shared__ unsigned int s_tot[kWarps];
+  __shared__ unsigned int s_rule1[kWarps];
+  __shared__ unsigned long long s_part[kWarps];
+  __shared__ bool s_found[kWarps];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int64_t n_tiles = gridDim.x;
   const int64_t tile = blockIdx.x;
-  const int64_t row = tile * kFilterTile + static_cast<int64_t>(tid) * kFilterRows;
-
-  int g[kFilterRows];
-  double p[kFilterRows];
-  unsigned keep_bits = 0, rule1 = 0;
-  if (row + kFilterRows <= n) {
-    load_i32<kFilterRows, true>(guest, row, g);
-    load_f64<kFilterRows, true>(price, row, p);
+  {
+    const int64_t warp_row = tile * kFilterTile + static_cast<int64_t>(warp) * (32 * kPerLane) + lane;
+    int g[kPerLane];
+    double p[kPerLane];
+    if (warp_row - lane + 32 * kPerLane <= n) {
 #pragma unroll
-    for (int r = 0; r < kFilterRows; ++r) {
-      keep_bits |= (dq_keep(g[r], p[r], t) ? 1u : 0u) << r;
-      rule1 += dq_keep_rule1(p[r], t) ? 1u : 0u;
-    }
-  } else {
+      for (int j = 0; j < kPerLane; ++j) {
+        g[j] = __ldg(guest + warp_row + 32 * j);
+        p[j] = __ldg(price + warp_row + 32 * j);
+      }
+    } else {
 #pragma unroll
-    for (int r = 0; r < kFilterRows; ++r) {
-      if (row + r < n) {
-        g[r] = guest[row + r];
-        p[r] = price[row + r];
-        keep_bits |= (dq_keep(g[r], p[r], t) ? 1u : 0u) << r;
-        rule1 += dq_keep_rule1(p[r], t) ? 1u : 0u;
+      for (int j = 0; j < kPerLane; ++j) {
+        const bool in = warp_row + 32 * j < n;
+        g[j] = in ? guest[warp_row + 32 * j] : 0;
+        p[j] = in ? price[warp_row + 32 * j] : 0.0;  // price 0 is dropped by rule 1
       }
     }
-  }
-  const unsigned cnt = __popc(keep_bits);
-
-  // exclusive scan of cnt over the CTA (row order == thread order)
-  unsigned incl = cnt;
+    unsigned mask[kPerLane];
+    unsigned warp_total = 0, rule1 = 0;
 #pragma unroll
-  for (int off = 1; off < 32; off <<= 1) {
-    const unsigned v = __shfl_up_sync(0xffffffffu, incl, off);
-    if (lane >= off) incl += v;
-  }
-  unsigned r1sum = rule1;
-#pragma unroll
-  for (int off = 16; off > 0; off >>= 1) r1sum += __shfl_down_sync(0xffffffffu, r1sum, off);
-  if (lane == 31) s_warp_keep[warp] = incl;
-  if (lane == 0) s_warp_rule1[warp] = r1sum;
-  __syncthreads();
-  if (warp == 0) {
-    // 16 warp totals -> exclusive offsets per warp, tile aggregate, rule-1 total
-    unsigned wt = lane < kFilterThreads / 32 ? s_warp_keep[lane] : 0u;
-    unsigned r1 = lane < kFilterThreads / 32 ? s_warp_rule1[lane] : 0u;
-    unsigned wincl = wt;
-#pragma unroll
-    for (int off = 1; off < 32; off <<= 1) {
-      const unsigned v = __shfl_up_sync(0xffffffffu, wincl, off);
-      if (lane >= off) wincl += v;
+    for (int j = 0; j < kPerLane; ++j) {
+      const bool in = warp_row + 32 * j < n;
+      mask[j] = __ballot_sync(0xffffffffu, in && dq_keep(g[j], p[j], t));
+      rule1 += __popc(__ballot_sync(0xffffffffu, in && dq_keep_rule1(p[j], t)));
+      warp_total += __popc(mask[j]);
     }
-#pragma unroll
-    for (int off = 16; off > 0; off >>= 1) r1 += __shfl_down_sync(0xffffffffu, r1, off);
-    const unsigned aggregate = __shfl_sync(0xffffffffu, wincl, 31);
-    if (lane < kFilterThreads / 32) s_warp_keep[lane] = wincl - wt;  // exclusive
-    if (lane == 0 && r1 != 0u) atomicAdd(&counters[1], static_cast<unsigned long long>(r1));
+    if (lane == 0) {
+      s_tot[warp] = warp_total;
+      s_rule1[warp] = rule1;
+    }
+    __syncthreads();
 
-    // decoupled look-back
+    // every warp sums the 8 warp totals itself
+    unsigned warp_base = 0, aggregate = 0;
+#pragma unroll
+    for (int w = 0; w < kWarps; ++w) {
+      const unsigned v = s_tot[w];
+      if (w < warp) warp_base += v;
+      aggregate += v;
+    }
+    if (tid == 0) {
+      unsigned r1 = 0;
+#pragma unroll
+      for (int w = 0; w < kWarps; ++w) r1 += s_rule1[w];
+      if (r1 != 0u) atomicAdd(&counters[1], static_cast<unsigned long long>(r1));
+      // publish this tile's survivor count at once: successors can add it while we are still looking for our offset
+      st_state(&tile_state[tile], (tile == 0 ? kFlagPrefix : kFlagAgg) | aggregate);
+    }
+    // park the survivors at their tile-local position: the survivors of one ballot are consecutive words
+    {
+      const unsigned lt = (1u << lane) - 1u;
+      unsigned run = warp_base;
+#pragma unroll
+      for (int j = 0; j < kPerLane; ++j) {
+        if ((mask[j] >> lane) & 1u) {
+          const unsigned local = run + __popc(mask[j] & lt);
+          s_guest[local] = g[j];
+          s_price[local] = p[j];
+        }
+        run += __popc(mask[j]);
+      }
+    }
+
+    // Decoupled look-back by the whole CTA: thread i reads the word of tile (tile - 1 - i - 256 k) in step k, so one
+    // step covers 256 predecessors (one L2 round trip).  A warp adds the counts of its 32 tiles up to and including
+    // the nearest one that already holds a full prefix; the warps' results are chained in tile order.
     unsigned long long exclusive = 0;
-    if (tile == 0) {
-      if (lane == 0) st_state(&tile_state[0], kFlagPrefix | aggregate);
-    } else {
-      if (lane == 0) st_state(&tile_state[tile], kFlagAgg | aggregate);
-      int64_t idx = tile - 1;
+    if (tile > 0) {
+      int64_t first_idx = tile - 1;
       for (;;) {
-        const int64_t my = idx - lane;
+        const int64_t my = first_idx - tid;
         unsigned long long w = kFlagPrefix;  // tiles before 0 contribute an (empty) prefix
         if (my >= 0) {
           do { w = ld_state(&tile_state[my]); } while ((w >> 62) == 0ull);
         }
         const unsigned has_prefix = __ballot_sync(0xffffffffu, (w >> 62) == 2ull);
-        const int first = has_prefix ? __ffs(has_prefix) - 1 : 31;  // nearest predecessor that holds a full prefix
+        const int first = has_prefix ? __ffs(has_prefix) - 1 : 31;
         unsigned long long contrib = lane <= first ? (w & kValueMask) : 0ull;
 #pragma unroll
         for (int off = 16; off > 0; off >>= 1) contrib += __shfl_down_sync(0xffffffffu, contrib, off);
-        exclusive += __shfl_sync(0xffffffffu, contrib, 0);
-        if (has_prefix) break;
-        idx -= 32;
-      }
-      if (lane == 0) st_state(&tile_state[tile], kFlagPrefix | (exclusive + aggregate));
-    }
-    if (lane == 0) {
-      s_tile_offset = exclusive;
-      if (tile == static_cast<int64_t>(gridDim.x) - 1) counters[0] = exclusive + aggregate;
-    }
-  }
-  __syncthreads();
-  unsigned long long pos = s_tile_offset + s_warp_keep[warp] + (incl - cnt);
+        if (lane == 0) {
+          s_part[warp] = contrib;
+          s_found[warp] = has_prefix != 0u;
+        }
+        __syncthreads();
+        bool done = false;
 #pragma unroll
-  for (int r = 0; r < kFilterRows; ++r) {
-    if ((keep_bits >> r) & 1u) {
-      guest_out[pos] = g[r];
-      price_out[pos] = p[r];
-      ++pos;
+        for (int wv = 0; wv < kWarps; ++wv) {
+          if (!done) {
+            exclusive += s_part[wv];
+            done = s_found[wv];
+          }
+        }
+        __syncthreads();  // s_part / s_found are rewritten in the next step
+        if (done) break;
+        first_idx -= kFilterThreads;
+      }
+      if (tid == 0) st_state(&tile_state[tile], kFlagPrefix | (exclusive + aggregate));
+    } else {
+      __syncthreads();  // the parked survivors must be visible before the write-out
+    }
+    if (tid == 0 && tile == n_tiles - 1) counters[0] = exclusive + aggregate;
+
+    for (unsigned i = tid; i < aggregate; i += kFilterThreads) {
+      guest_out[exclusive + i] = s_guest[i];
+      price_out[exclusive + i] = s_price[i];
     }
   }
 }
@@ -315,12 +353,21 @@ size_t dq_filter_state_bytes(int64_t n) {
 cudaError_t launch_dq_filter(const int32_t* guest, const double* price, int64_t n, const dq4ml_dq_params& p,
                              int32_t* guest_out, double* price_out, unsigned long long* tile_state,
                              unsigned long long* counters, cudaStream_t stream, int64_t* launches) {
-  cudaError_t e = cudaMemsetAsync(counters, 0, 2 * sizeof(unsigned long long), stream);
+  cudaError_t e = cudaMemsetAsync(counters, 0, 3 * sizeof(unsigned long long), stream);  // survivors, after rule 1, tile ticket
   if (e != cudaSuccess || n <= 0) return e;
   e = cudaMemsetAsync(tile_state, 0, dq_filter_state_bytes(n), stream);
   if (e != cudaSuccess) return e;
   const int64_t tiles = (n + kFilterTile - 1) / kFilterTile;
-  dq_filter_compact_kernel<<<static_cast<unsigned>(tiles), kFilterThreads, 0, stream>>>(
+  static bool smem_opt_in[64] = {false};
+  int dev = 0;
+  if ((e = cudaGetDevice(&dev)) != cudaSuccess) return e;
+  if (dev >= 0 && dev < 64 && !smem_opt_in[dev]) {
+    e = cudaFuncSetAttribute(dq_filter_compact_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(kFilterSmem));
+    if (e != cudaSuccess) return e;
+    smem_opt_in[dev] = true;
+  }
+  const int64_t grid = tiles;
+  dq_filter_compact_kernel<<<static_cast<unsigned>(grid), kFilterThreads, kFilterSmem, stream>>>(
       guest, price, n, thresholds(p), guest_out, price_out, tile_state, counters);
   ++*launches;
   return cudaGetLastError();
@@ -362,9 +409,9 @@ cudaError_t launch_column_heads(const DeviceCols& cols, const double* label, int
 // dq4ml_dq_filter, needs a dq4ml_ctx (whose creation allocates scratch) and grows its tile-status buffer with
 // cudaMalloc; this one takes no ctx and touches no allocator at all.
 //
-// Where the scratch lives instead: the look-back words of the compaction kernel (one 64-bit word per 2048-row tile)
+// Where the scratch lives instead: the look-back words of the compaction kernel (one 64-bit word per 4096-row tile)
 // plus the two row counters sit in the file-scope device array below.  It is part of the library image, so every GPU
-// that loads libdq4ml.so carries these ~256 KB until the process exits, whether or not this entry point is ever used.
+// that loads libdq4ml.so carries these ~128 KB until the process exits, whether or not this entry point is ever used.
 // That fixed size is what bounds the call: at most DQ4ML_NOALLOC_MAX_ROWS rows per call.
 #include <mutex>
 

@@ -117,10 +117,12 @@ class Context:
         dev = f"cuda:{self.device}"
         guest = torch.empty(n, dtype=torch.int32, device=dev)
         price = torch.empty(n, dtype=torch.float64, device=dev)
-        extra = torch.empty((max(d - 1, 0), n), dtype=torch.float64, device=dev)
+        stride = (n + 15) // 16 * 16  # keeps every column 16-byte aligned whatever n is
+        store = torch.empty((max(d - 1, 0), stride), dtype=torch.float64, device=dev)
         sp = capi.SynthParams(seed_data, seed_anom, p_low, p_high, d)
         capi.check(capi.lib().dq4ml_synth_generate(self._h, C.byref(sp), row0, n, guest.data_ptr(), price.data_ptr(),
-                                                    extra.data_ptr() if d > 1 else None, n))
+                                                    store.data_ptr() if d > 1 else None, stride))
+        extra = store[:, :n]  # extra[k] is a contiguous 1-D column
         return guest, price, extra
 
     def rows_digest(self, guest, price, seed=0):

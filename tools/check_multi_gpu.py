@@ -1,0 +1,73 @@
+#!/usr/bin/env python
+"""Run under torchrun on N >= 2 GPUs: the row-sharded fit (one process per GPU, NCCL all-reduce of the result vector
+inside libdq4ml) must equal the single-GPU fit over the same global rows.
+
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29511 tools/check_multi_gpu.py
+"""
+import faulthandler
+import json
+import os
+import sys
+
+faulthandler.dump_traceback_later(100, exit=True)
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+ROOT = os.path.abspath(os.path.join(os.path.dirname(__file__), ".."))
+sys.path.insert(0, ROOT)
+import sparkdq4ml_b200 as pkg  # noqa: E402
+
+
+def frame(ctx, g, p, x, d, label="label"):
+    cols = {"guest": g, label: p}
+    names = ["guest"]
+    for k in range(d - 1):
+        cols[f"x{k + 1}"] = x[k]
+        names.append(f"x{k + 1}")
+    df = pkg.Frame(ctx, cols).with_fused_dq("guest", label)
+    return pkg.VectorAssembler().setInputCols(names).transform(df)
+
+
+def main():
+    rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+    torch.cuda.set_device(local)
+    dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local}"))
+    results = {}
+    n_global = 8_000_000 + 4321
+    cases = [("wls_d1", 1, dict(reg=1.0, alpha=1.0, solver="auto")),
+             ("owlqn_d16", 16, dict(reg=0.3, alpha=0.5, solver="l-bfgs")),
+             ("gram_d40", 40, dict(reg=0.1, alpha=0.0, solver="normal"))]
+    sharded = pkg.Context(local).bind_torch_distributed()
+    single = pkg.Context(local)  # unbound: sees only what it is given
+    for name, d, hp in cases:
+        lo, hi = pkg.shard_bounds(n_global, rank, world)
+        g, p, x = sharded.synth_generate(hi - lo, d=d, row0=lo)
+        lr = pkg.LinearRegression().setMaxIter(40).setRegParam(hp["reg"]).setElasticNetParam(hp["alpha"]).setSolver(hp["solver"])
+        m = lr.fit(frame(sharded, g, p, x, d))
+        ev = m.evaluate(frame(sharded, g, p, x, d))
+        res = {"coef": m.coefficients().tolist(), "intercept": m.intercept(), "rows": m.num_rows, "rmse": ev.rootMeanSquaredError(),
+               "hist": m.summary().objectiveHistory().tolist()}
+        # every rank must hold the identical model
+        blob = [None] * world
+        dist.all_gather_object(blob, res)
+        assert all(b == blob[0] for b in blob), f"{name}: ranks disagree"
+        if rank == 0:
+            gg, pp, xx = single.synth_generate(n_global, d=d, row0=0)
+            ref = lr.fit(frame(single, gg, pp, xx, d))
+            ref_ev = ref.evaluate(frame(single, gg, pp, xx, d))
+            assert ref.num_rows == res["rows"], (ref.num_rows, res["rows"])
+            np.testing.assert_allclose(res["coef"], ref.coefficients(), rtol=1e-8, atol=1e-11)
+            np.testing.assert_allclose(res["intercept"], ref.intercept(), rtol=1e-9)
+            np.testing.assert_allclose(res["rmse"], ref_ev.rootMeanSquaredError(), rtol=1e-9)
+            np.testing.assert_allclose(res["hist"], ref.summary().objectiveHistory(), rtol=1e-8)
+            results[name] = {"rows": res["rows"], "intercept": res["intercept"], "iterations": len(res["hist"])}
+        dist.barrier()
+    if rank == 0:
+        print(json.dumps({"multi_gpu_check": "ok", "world": world, "cases": results}))
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
