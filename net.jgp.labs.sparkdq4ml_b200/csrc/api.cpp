@@ -12,6 +12,7 @@
 #include "context.hpp"
 #include "gram.hpp"
 #include "solver.hpp"
+#include "wide.hpp"
 
 using namespace dq4ml;
 
@@ -171,19 +172,19 @@ int check_ctx(const dq4ml_ctx* ctx) {
 void collect_pass_time(dq4ml_ctx* ctx);
 
 // ---- cross-rank sum of the result vector sitting in ctx->scratch.result; leaves it in ctx->h_result ----------------
-int finish_result(dq4ml_ctx* ctx, int64_t count) {
+int finish_result(dq4ml_ctx* ctx, int64_t count, bool reduce = true) {
   if (static_cast<size_t>(count) > kResultDoubles) {
     set_error("result vector too long (%lld)", static_cast<long long>(count));
     return DQ4ML_ERR_UNSUPPORTED;
   }
-  if (ctx->nccl != nullptr) {
+  if (reduce && ctx->nccl != nullptr) {
     const int rc = nccl_allreduce_device(ctx, ctx->scratch.result, count);
     if (rc != DQ4ML_OK) return rc;
   }
   CU(cudaMemcpyAsync(ctx->h_result, ctx->scratch.result, sizeof(double) * count, cudaMemcpyDeviceToHost, ctx->stream));
   CU(cudaStreamSynchronize(ctx->stream));
   collect_pass_time(ctx);
-  if (ctx->nccl == nullptr && ctx->allreduce_cb != nullptr) {
+  if (reduce && ctx->nccl == nullptr && ctx->allreduce_cb != nullptr) {
     if (ctx->allreduce_cb(ctx->allreduce_user, ctx->h_result, count) != 0) {
       set_error("all-reduce callback failed");
       return DQ4ML_ERR_COMM;
@@ -345,10 +346,13 @@ int wls_moments_any(dq4ml_ctx* ctx, const PassInputs& in, int64_t n, double* out
 }
 
 // Summarizer, core statistics (count, mean, sample variance per column; label last) for the l-bfgs branch.
-int summarize_core(dq4ml_ctx* ctx, const PassInputs& in, int64_t n, ColumnStats* st) {
-  const int d = in.cols.n;
+// One summarizer launch over a group of <= kMaxCols feature columns (+ the label when non-null): fills count and the
+// mean / sample variance of the group's columns (group column c -> out index first + c; label -> out index label_out).
+int summarize_group(dq4ml_ctx* ctx, const DeviceCols& cols, const double* label, const DeviceDq& dq, int64_t n, int first,
+                    int label_out, ColumnStats* st) {
+  const int d = cols.n;
   const int b = stream_bucket(d > 0 ? d : 1);
-  cudaError_t e = launch_column_heads(in.cols, in.label, b, n, ctx->scratch, ctx->stream, &ctx->launches);
+  cudaError_t e = launch_column_heads(cols, label, b, n, ctx->scratch, ctx->stream, &ctx->launches);
   if (e != cudaSuccess) return cuda_fail(e, "column heads");
   std::vector<double> centres(b + 1, 0.0);
   CU(cudaMemcpyAsync(ctx->h_result, ctx->scratch.consts, sizeof(double) * (b + 1), cudaMemcpyDeviceToHost, ctx->stream));
@@ -360,31 +364,93 @@ int summarize_core(dq4ml_ctx* ctx, const PassInputs& in, int64_t n, ColumnStats*
     for (double& c : centres) c /= ctx->world > 0 ? ctx->world : 1;
     CU(cudaMemcpyAsync(ctx->scratch.consts, centres.data(), sizeof(double) * (b + 1), cudaMemcpyHostToDevice, ctx->stream));
   }
-  e = timed_stream_pass(ctx, kOpSummCore, in.cols, in.label, in.dq, n, nullptr, nullptr);
+  e = timed_stream_pass(ctx, kOpSummCore, cols, label, dq, n, nullptr, nullptr);
   if (e != cudaSuccess) return cuda_fail(e, "summarizer pass");
   const int rc = finish_result(ctx, stream_nacc(kOpSummCore, b));
   if (rc != DQ4ML_OK) return rc;
   const double* r = ctx->h_result;
   const double cnt = r[0];
   st->count = cnt;
-  st->mean.assign(d + 1, 0.0);
-  st->variance.assign(d + 1, 0.0);
-  for (int c = 0; c <= d; ++c) {
-    const int slot = c < d ? c : b;
+  auto read_out = [&](int slot, int out) {
     const double s1 = r[1 + 2 * slot], s2 = r[2 + 2 * slot];
     if (cnt > 0) {
-      st->mean[c] = centres[slot] + s1 / cnt;
+      st->mean[out] = centres[slot] + s1 / cnt;
       const double m2n = s2 - s1 * s1 / cnt;
-      st->variance[c] = cnt > 1 ? std::max(m2n / (cnt - 1.0), 0.0) : 0.0;
+      st->variance[out] = cnt > 1 ? std::max(m2n / (cnt - 1.0), 0.0) : 0.0;
     }
+  };
+  for (int c = 0; c < d; ++c) read_out(c, first + c);
+  if (label != nullptr && label_out >= 0) read_out(b, label_out);
+  return DQ4ML_OK;
+}
+
+// Summarizer, core statistics (count, mean, sample variance per column; label last) for the l-bfgs branch.  Tables
+// wider than kMaxCols go through in column groups (each column is still read exactly once; the DQ columns once per group).
+int summarize_core(dq4ml_ctx* ctx, const PassInputs& in, int64_t n, ColumnStats* st) {
+  const int d = in.width();
+  st->mean.assign(d + 1, 0.0);
+  st->variance.assign(d + 1, 0.0);
+  if (d <= kMaxCols) return summarize_group(ctx, in.cols, in.label, in.dq, n, 0, d, st);
+  for (int c0 = 0; c0 < d; c0 += kMaxCols) {
+    DeviceCols g;
+    g.n = std::min(kMaxCols, d - c0);
+    for (int j = 0; j < g.n; ++j) {
+      g.ptr[j] = in.ptr[c0 + j];
+      g.dtype[j] = in.dtype[c0 + j];
+    }
+    const bool with_label = c0 == 0;
+    const int rc = summarize_group(ctx, g, with_label ? in.label : nullptr, in.dq, n, c0, with_label ? d : -1, st);
+    if (rc != DQ4ML_OK) return rc;
   }
   return DQ4ML_OK;
 }
 
 int lsq_pass(dq4ml_ctx* ctx, const PassInputs& in, int64_t n, const double* coef, const double* fstd,
              const double* fmean, double ystd, double ymean, bool fit_intercept, double* loss_sum, double* weight_sum,
-             double* grad_sum) {
-  const int d = in.cols.n;
+             double* grad_sum, double* diff_scratch = nullptr) {
+  const int d = in.width();
+  if (d > kMaxCols) {
+    // Wide table: pass 1 writes the scaled difference r = y/yStd - (x.eff + offset) per row (and its sums), pass 2 takes
+    // gradSum_j = -sum r x_j over column groups.  The table is read twice; Spark reads it once, but keeps it in host RAM.
+    if (diff_scratch == nullptr) {
+      set_error("internal: no scratch column for the wide loss/gradient pass");
+      return DQ4ML_ERR_INVALID;
+    }
+    std::vector<double> eff(d);
+    double s = 0.0;
+    for (int j = 0; j < d; ++j) {
+      eff[j] = fstd[j] != 0.0 ? coef[j] / fstd[j] : 0.0;
+      s += eff[j] * fmean[j];
+    }
+    const double offset = fit_intercept ? ymean / ystd - s : 0.0;
+    WideSums ws;
+    int rc = wide_rows_pass(ctx, in.ptr, in.dtype, eff.data(), offset, 1.0 / ystd, in.label, in.dq, n, 1, diff_scratch, false, &ws);
+    if (rc != DQ4ML_OK) return rc;
+    std::vector<double> all(2 + d, 0.0);
+    all[0] = 0.5 * ws.ss_res;
+    all[1] = ws.n;
+    for (int c0 = 0; c0 < d; c0 += kMaxCols) {
+      DeviceCols g;
+      g.n = std::min(kMaxCols, d - c0);
+      for (int j = 0; j < g.n; ++j) {
+        g.ptr[j] = in.ptr[c0 + j];
+        g.dtype[j] = in.dtype[c0 + j];
+      }
+      cudaError_t e = timed_stream_pass(ctx, kOpGrad, g, diff_scratch, DeviceDq{}, n, nullptr, nullptr);
+      if (e != cudaSuccess) return cuda_fail(e, "gradient pass");
+      rc = finish_result(ctx, stream_nacc(kOpGrad, stream_bucket(g.n)), false);
+      if (rc != DQ4ML_OK) return rc;
+      for (int j = 0; j < g.n; ++j) all[2 + c0 + j] = -ctx->h_result[j];
+    }
+    if (multi_rank(ctx)) {
+      rc = host_allreduce(ctx, all.data(), static_cast<int64_t>(all.size()));
+      if (rc != DQ4ML_OK) return rc;
+    }
+    *loss_sum = all[0];
+    *weight_sum = all[1];
+    for (int j = 0; j < d; ++j) grad_sum[j] = fstd[j] != 0.0 ? all[2 + j] / fstd[j] : 0.0;
+    return DQ4ML_OK;
+  }
   const int b = stream_bucket(d > 0 ? d : 1);
   LsqConsts c{};
   double s = 0.0;
@@ -903,10 +969,12 @@ int dq4ml_lsq_loss_grad(dq4ml_ctx* ctx, const dq4ml_columns* features, const dou
   }
   CallScope scope(ctx);
   PassInputs in;
-  int rc = gather_inputs(ctx, features, label, n, dq, &in, 0, kMaxCols);
+  const bool wide = features->n_cols > kMaxCols;
+  int rc = gather_inputs(ctx, features, label, n, dq, &in, wide ? static_cast<size_t>(n) * 8 : 0, 4096);
   if (rc != DQ4ML_OK) return rc;
+  double* diff = wide ? static_cast<double*>(arena_take(ctx, static_cast<size_t>(n) * 8)) : nullptr;
   return lsq_pass(ctx, in, n, coef, features_std, features_mean, label_std, label_mean, fit_intercept != 0, &out[0],
-                  &out[1], out + 2);
+                  &out[1], out + 2, diff);
 }
 
 int dq4ml_linreg_fit(dq4ml_ctx* ctx, const dq4ml_columns* features, const double* label, int64_t n,
@@ -926,8 +994,10 @@ int dq4ml_linreg_fit(dq4ml_ctx* ctx, const dq4ml_columns* features, const double
   // numFeatures <= WeightedLeastSquares.MAX_NUM_FEATURES (4096); otherwise the summarizer + L-BFGS/OWL-QN branch.
   const bool wls = p.solver == DQ4ML_SOLVER_NORMAL || (p.solver == DQ4ML_SOLVER_AUTO && d <= 4096);
   PassInputs in;
-  int rc = gather_inputs(ctx, features, label, n, dq, &in, 0, wls ? 4096 : kMaxCols);
+  const bool wide_lbfgs = !wls && d > kMaxCols;  // needs one scratch column for the per-row scaled difference
+  int rc = gather_inputs(ctx, features, label, n, dq, &in, wide_lbfgs ? static_cast<size_t>(n) * 8 : 0, 1 << 20);
   if (rc != DQ4ML_OK) return rc;
+  double* diff = wide_lbfgs ? static_cast<double*>(arena_take(ctx, static_cast<size_t>(n) * 8)) : nullptr;
   try {
     auto model = std::make_unique<dq4ml_lr_model>();
     if (wls) {
@@ -944,7 +1014,7 @@ int dq4ml_linreg_fit(dq4ml_ctx* ctx, const dq4ml_columns* features, const double
                            double& loss_sum, double& weight_sum, Vec& grad_sum) {
         grad_sum.assign(d, 0.0);
         const int r = lsq_pass(ctx, in, n, coef.data(), fstd.data(), fmean.data(), ystd, ymean, p.fit_intercept,
-                               &loss_sum, &weight_sum, grad_sum.data());
+                               &loss_sum, &weight_sum, grad_sum.data(), diff);
         if (r != DQ4ML_OK) {
           pass_rc = r;
           throw SolveError{r, get_error()};
@@ -1024,9 +1094,27 @@ static int eval_common(dq4ml_ctx* ctx, const dq4ml_lr_model* m, const dq4ml_colu
   }
   CallScope scope(ctx);
   PassInputs in;
-  int rc = gather_inputs(ctx, features, label, n, dq, &in, (row_out_user != nullptr && !is_device_ptr(row_out_user)) ? static_cast<size_t>(n) * 8 : 0, kMaxCols);
+  int rc = gather_inputs(ctx, features, label, n, dq, &in, (row_out_user != nullptr && !is_device_ptr(row_out_user)) ? static_cast<size_t>(n) * 8 : 0, 4096);
   if (rc != DQ4ML_OK) return rc;
   OutBuf ob = make_out(ctx, row_out_user, static_cast<size_t>(n) * 8);
+  if (in.width() > kMaxCols) {  // wide table: the column-walking row pass
+    WideSums ws;
+    rc = wide_rows_pass(ctx, in.ptr, in.dtype, m->m.coefficients.data(), m->m.intercept, 1.0, in.label, in.dq, n, mode,
+                        static_cast<double*>(ob.dev), multi_rank(ctx), &ws);
+    if (rc != DQ4ML_OK) return rc;
+    if (ob.staged && n > 0) {
+      CU(cudaMemcpyAsync(row_out_user, ob.dev, static_cast<size_t>(n) * 8, cudaMemcpyDeviceToHost, ctx->stream));
+      CU(cudaStreamSynchronize(ctx->stream));
+    }
+    if (sums != nullptr) {
+      sums[0] = ws.n;
+      sums[1] = ws.ss_res;
+      sums[2] = ws.sum_y;
+      sums[3] = ws.sum_yy;
+      sums[4] = ws.sum_abs_res;
+    }
+    return DQ4ML_OK;
+  }
   EvalConsts c{};
   for (int j = 0; j < in.cols.n; ++j) c.coef[j] = m->m.coefficients[j];
   c.intercept = m->m.intercept;

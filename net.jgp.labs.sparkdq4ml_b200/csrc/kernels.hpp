@@ -35,7 +35,7 @@ struct Scratch {
   int sm_count;
 };
 
-enum StreamOpKind { kOpWls = 0, kOpLsq = 1, kOpSummCore = 2, kOpSummFull = 3, kOpEval = 4 };
+enum StreamOpKind { kOpWls = 0, kOpLsq = 1, kOpSummCore = 2, kOpSummFull = 3, kOpEval = 4, kOpGrad = 5 };
 
 struct LsqConsts {
   double eff[kMaxCols];

@@ -130,6 +130,24 @@ struct SummFullOp {
   }
 };
 
+// Second half of the LeastSquaresAggregator for wide tables: gradSum_j += r * x_j over a group of columns, where the
+// per-row scaled difference r was written by the wide row pass and arrives here as the "label" column.
+template <int DMAX>
+struct GradOp {
+  static constexpr int NACC = DMAX;
+  static constexpr int NCONST = 0;
+  static constexpr bool HAS_OUT = false;
+  __host__ __device__ static constexpr double identity(int) { return 0.0; }
+  __host__ __device__ static constexpr int kind(int) { return kSum; }
+
+  __device__ __forceinline__ double row(double (&acc)[NACC], const double*, const double (&x)[DMAX], double y, bool,
+                                        int) const {
+#pragma unroll
+    for (int j = 0; j < DMAX; ++j) acc[j] = fma(y, x[j], acc[j]);
+    return 0.0;
+  }
+};
+
 // LinearRegressionModel.transform + RegressionMetrics in one pass: yhat = x.beta + b; residual = y - yhat;
 // accumulators n, SSerr, sum y, sum y^2, sum |residual|.  Per-row output: prediction (mode 0) or residual (mode 1).
 template <int DMAX>

@@ -23,6 +23,7 @@ int stream_nacc(StreamOpKind op, int bucket) {
     case kOpSummCore: return 1 + 2 * (bucket + 1);
     case kOpSummFull: return 1 + 7 * bucket;
     case kOpEval: return 5;
+    case kOpGrad: return bucket;
   }
   return 0;
 }
@@ -115,6 +116,7 @@ cudaError_t launch_bucket(StreamOpKind kind, const PassArgs& a, const void* host
       if constexpr (DMAX <= 4) return launch_mode<SummFullOp<DMAX>, DMAX, ROWS>(SummFullOp<DMAX>{}, a);
       return cudaErrorInvalidValue;
     case kOpEval: return launch_mode<EvalOp<DMAX>, DMAX, ROWS>(make_eval<DMAX>(*static_cast<const EvalConsts*>(host_consts)), a);
+    case kOpGrad: return launch_one<GradOp<DMAX>, DMAX, ROWS, kDqNone>(GradOp<DMAX>{}, a);
   }
   return cudaErrorInvalidValue;
 }

@@ -1,0 +1,25 @@
+// wide.hpp -- row-streaming passes over feature tables wider than the 32 columns a register-resident streaming kernel
+// holds: prediction / residual / scaled-difference columns with their sums (wide_kernels.cu).
+#pragma once
+
+#include <vector>
+
+#include "context.hpp"
+
+namespace dq4ml {
+
+struct WideSums {
+  double n, ss_res, sum_y, sum_yy, sum_abs_res;
+};
+
+// For every row kept by the DQ predicate: pred = x . coef + c0, res = y * y_scale - pred.
+// row_out (device, nullable) receives pred (mode 0) or res (mode 1); rows the rules drop get 0.
+// sums are summed over ranks when the ctx is bound.  All data pointers are DEVICE pointers.
+int wide_rows_pass(dq4ml_ctx* ctx, const std::vector<const void*>& col_ptrs, const std::vector<int>& dtypes,
+                   const double* coef_host, double c0, double y_scale, const double* label, const DeviceDq& dq, int64_t n,
+                   int mode, double* row_out, bool reduce_over_ranks, WideSums* sums);
+
+// Grow-only device scratch shared by the wide passes (column table, coefficients, Gram partials).
+int ensure_wide_scratch(dq4ml_ctx* ctx, size_t bytes);
+
+}  // namespace dq4ml

@@ -303,3 +303,67 @@ def test_config4_shape_d256_normal_equations(pkg, ctx, params):
     np.testing.assert_allclose(model.coefficients(), ref.coefficients, rtol=1e-6, atol=1e-8)
     np.testing.assert_allclose(model.intercept(), ref.intercept, rtol=1e-7)
     assert rel_err(model.summary().objectiveHistory(), ref.objective_history) < 1e-7
+
+
+# ---------------------------------------------------------------------------------------------- wide tables beyond the Gram
+
+@pytest.mark.parametrize("d,n", [(33, 5_001), (48, 70_000), (256, 30_003)])
+def test_wide_transform_evaluate_and_lsq_vs_oracle(pkg, ctx, d, n):
+    """Tables wider than the 32 register-resident columns: column-walking predict/evaluate pass and the two-pass
+    loss/gradient, fused DQ, against the oracle."""
+    from sparkdq4ml_b200 import ml
+    guest, price, feats = wide_table(n, d)
+    rng = np.random.default_rng(d)
+    coef = rng.normal(size=d) * 0.1
+    intercept = 3.25
+    pred_ref, met_ref = passes.predict_metrics(feats, price, coef, intercept, dq=(guest, price), threads=8)
+    dfeats, dprice = to_dev(*feats), to_dev(price)[0]
+    cols = {"guest": dfeats[0], "label": dprice}
+    names = ["guest"]
+    for k in range(1, d):
+        cols[f"x{k}"] = dfeats[k]
+        names.append(f"x{k}")
+    df = pkg.VectorAssembler().setInputCols(names).transform(pkg.Frame(ctx, cols).with_fused_dq("guest", "label"))
+    model = pkg.LinearRegressionModel.from_coefficients(coef, intercept)
+    pred = model.transform(df).col("prediction").cpu().numpy()
+    keep = np.array([bool(passes.lib().orc_dq_keep(int(a), float(b))) for a, b in zip(guest, price)])
+    plain, _ = passes.predict_metrics(feats, price, coef, intercept, threads=8)  # transform ignores DQ
+    np.testing.assert_allclose(pred, plain, rtol=1e-12, atol=1e-10)
+    ev = model.evaluate(df, want_residuals=True)
+    ref = spark_ml.regression_metrics(met_ref)
+    assert ev.numInstances() == int(met_ref[0])
+    assert rel_err(ev.rootMeanSquaredError(), ref["rmse"]) < 1e-10 and rel_err(ev.r2(), ref["r2"]) < 1e-9
+    assert rel_err(ev.meanAbsoluteError(), ref["mae"]) < 1e-10
+    res = ev.residuals().cpu().numpy()
+    assert (res[~keep] == 0).all()
+    np.testing.assert_allclose(res[keep], (price - pred_ref)[keep], rtol=0, atol=1e-9 * np.abs(price).max())
+    # loss / gradient
+    summ = passes.summarizer(feats, price, dq=(guest, price), threads=8)
+    fstd, fmean = np.sqrt(summ["variance"][:d]), summ["mean"][:d]
+    ystd, ymean = np.sqrt(summ["variance"][d]), summ["mean"][d]
+    c = rng.normal(size=d)
+    rl, rw, rg = passes.lsq_loss_grad(feats, price, c, fstd, fmean, ystd, ymean, True, dq=(guest, price), threads=8)
+    gl, gw, gg = ml.lsq_loss_grad(ctx, dfeats, dprice, c, fstd, fmean, ystd, ymean, True, dq=(dfeats[0], dprice))
+    assert gw == rw and rel_err(gl, rl) < 1e-10
+    np.testing.assert_allclose(gg, rg, rtol=1e-9, atol=1e-9 * np.abs(rg).max())
+
+
+def test_wide_lbfgs_fit_d40(pkg, ctx):
+    """solver = l-bfgs on a 40-column table: grouped summarizer + two-pass loss/gradient under OWL-QN."""
+    n, d = 50_000, 40
+    guest, price, feats = wide_table(n, d)
+    params = dict(max_iter=30, reg_param=0.2, elastic_net_param=0.5, solver="l-bfgs")
+    ref = spark_ml.linear_regression_fit(feats, price, spark_ml.LRParams(**params), dq=(guest, price), threads=8)
+    dfeats, dprice = to_dev(*feats), to_dev(price)[0]
+    cols = {"guest": dfeats[0], "label": dprice}
+    names = ["guest"]
+    for k in range(1, d):
+        cols[f"x{k}"] = dfeats[k]
+        names.append(f"x{k}")
+    df = pkg.VectorAssembler().setInputCols(names).transform(pkg.Frame(ctx, cols).with_fused_dq("guest", "label"))
+    model = estimator(pkg, params).fit(df)
+    assert model.solver_used == ref.solver_used == "owlqn"
+    assert model.summary().totalIterations() == ref.total_iterations
+    assert rel_err(model.summary().objectiveHistory(), ref.objective_history) < 1e-8
+    np.testing.assert_allclose(model.coefficients(), ref.coefficients, rtol=1e-6, atol=1e-9)
+    np.testing.assert_allclose(model.intercept(), ref.intercept, rtol=1e-8)
