@@ -35,10 +35,10 @@ def frame(pkg, ctx, g, p, x, d):
     return pkg.VectorAssembler().setInputCols(names).setOutputCol("features").transform(df)
 
 
-def config3(pkg, ctx, rows, reps):
+def config3(pkg, ctx, rows, reps, row0=0, world=1, global_rows=None):
     import torch
     d = 16
-    g, p, x = ctx.synth_generate(rows, d=d)
+    g, p, x = ctx.synth_generate(rows, d=d, row0=row0)
     df = frame(pkg, ctx, g, p, x, d)
     lr = pkg.LinearRegression().setMaxIter(40).setRegParam(1.0).setElasticNetParam(0.5).setSolver("l-bfgs")
     bytes_per_row = 4 + 8 * d  # int32 guest + 15 f64 features + f64 label(price); DQ columns are guest and label
@@ -51,20 +51,22 @@ def config3(pkg, ctx, rows, reps):
         ms, passes_n = ctx.pass_timing()
         ctx.enable_pass_timing(False)
         gbs = bytes_per_row * rows * passes_n / (ms / 1e3) / 1e9
-        print(json.dumps({"config": 3, "rows": rows, "features": d, "solver": model.solver_used,
+        if ctx.rank != 0:
+            continue
+        print(json.dumps({"config": 3, "n_gpus": world, "global_rows": global_rows or rows, "rows": rows, "features": d, "solver": model.solver_used,
                           "total_iterations": model.summary().totalIterations(), "data_passes": model.data_passes,
-                          "fit_seconds": wall, "rows_per_sec_fit": rows / wall, "pass_kernel_ms_avg": ms / passes_n,
+                          "fit_seconds": wall, "rows_per_sec_fit": (global_rows or rows) / wall, "pass_kernel_ms_avg": ms / passes_n,
                           "bytes_per_row_per_pass": bytes_per_row, "pass_gbs": gbs, "pass_frac_of_measured_hbm": gbs / peak_hbm(),
                           "coefficients_head": model.coefficients()[:4].tolist(), "intercept": model.intercept()}), flush=True)
     del g, p, x
     torch.cuda.empty_cache()
 
 
-def config4(pkg, ctx, rows, reps):
+def config4(pkg, ctx, rows, reps, row0=0, world=1):
     import torch
     from sparkdq4ml_b200 import ml
     d = 256
-    g, p, x = ctx.synth_generate(rows, d=d)
+    g, p, x = ctx.synth_generate(rows, d=d, row0=row0)
     feats = [g] + [x[k] for k in range(d - 1)]
     flop_per_row = d * (d + 1) + 4 * d  # symmetric half of X^T X at 2 flop/MAC + X^T y + sums
     bytes_per_row = 4 + 8 * d
@@ -76,7 +78,9 @@ def config4(pkg, ctx, rows, reps):
         wall = time.perf_counter() - t0
         ms, passes_n = ctx.pass_timing()
         ctx.enable_pass_timing(False)
-        print(json.dumps({"config": 4, "rows": rows, "features": d, "survivors": mom[0], "gram_pass_ms": ms / passes_n,
+        if ctx.rank != 0:
+            continue
+        print(json.dumps({"config": 4, "n_gpus": world, "rows_per_gpu": rows, "features": d, "survivors_all_ranks": mom[0], "gram_pass_ms": ms / passes_n,
                           "wall_ms": wall * 1e3, "rows_per_sec_pass": rows / (ms / passes_n / 1e3),
                           "algorithmic_tflops": flop_per_row * rows / (ms / passes_n / 1e3) / 1e12,
                           "frac_of_measured_fp64_peak_37.2": flop_per_row * rows / (ms / passes_n / 1e3) / 1e12 / 37.2,
@@ -87,8 +91,9 @@ def config4(pkg, ctx, rows, reps):
     t0 = time.perf_counter()
     model = lr.fit(df)
     wall = time.perf_counter() - t0
-    print(json.dumps({"config": 4, "what": "whole fit (Gram pass + packed Cholesky on the host)", "rows": rows,
-                      "fit_seconds": wall, "rows_per_sec_fit": rows / wall, "solver": model.solver_used,
+    if ctx.rank == 0:
+        print(json.dumps({"config": 4, "n_gpus": world, "what": "whole fit (Gram pass + all-reduce + packed Cholesky on the host)", "rows_per_gpu": rows,
+                      "fit_seconds": wall, "rows_per_sec_fit": rows * world / wall, "solver": model.solver_used,
                       "coefficients_head": model.coefficients()[:4].tolist(), "intercept": model.intercept()}), flush=True)
     del g, p, x, feats
     torch.cuda.empty_cache()
@@ -129,14 +134,26 @@ def main():
     ap.add_argument("--sizes", type=str, default="10000000,100000000,1000000000,4000000000")
     a = ap.parse_args()
     import sparkdq4ml_b200 as pkg
-    ctx = pkg.Context(0)
+    world, rank, local = int(os.environ.get("WORLD_SIZE", "1")), int(os.environ.get("RANK", "0")), int(os.environ.get("LOCAL_RANK", "0"))
+    if world > 1:  # torchrun: config 3 is strong-scaled (global rows sharded), config 4 weak-scaled (rows per GPU)
+        import torch
+        import torch.distributed as dist
+        torch.cuda.set_device(local)
+        dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local}"))
+    ctx = pkg.Context(local).bind_torch_distributed()
     if a.config == 3:
-        config3(pkg, ctx, a.rows or 1_000_000_000, a.reps)
+        n_global = a.rows or 1_000_000_000
+        lo, hi = pkg.shard_bounds(n_global, rank, world)
+        config3(pkg, ctx, hi - lo, a.reps, row0=lo, world=world, global_rows=n_global)
     elif a.config == 4:
-        config4(pkg, ctx, a.rows or 62_500_000, a.reps)
+        rows = a.rows or 62_500_000
+        config4(pkg, ctx, rows, a.reps, row0=rank * rows, world=world)
     elif a.config == 5:
         config5(pkg, ctx, [int(s) for s in a.sizes.split(",")], a.reps)
     ctx.close()
+    if world > 1:
+        import torch.distributed as dist
+        dist.destroy_process_group()
 
 
 if __name__ == "__main__":
