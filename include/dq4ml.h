@@ -17,8 +17,10 @@
  *   - every function returns DQ4ML_OK (0) or a negative dq4ml_status; dq4ml_last_error() gives the text
  *     (thread-local, valid until the next failing call on the same thread).
  *   - data pointers (columns, outputs marked "host or device") may be host or CUDA device memory; the library
- *     asks the driver which (cudaPointerGetAttributes).  Host buffers are streamed through pinned staging
- *     buffers in chunks, overlapping copy and kernel.  Device columns must be 16-byte aligned.
+ *     asks the driver which (cudaPointerGetAttributes).  Host buffers are copied into a per-context device staging
+ *     arena first (pinned host memory makes that copy run at PCIe rate).  Device columns must be 32-byte aligned
+ *     (the kernels use 256-bit loads); a row range of an aligned column stays aligned when it starts on a multiple of
+ *     8 rows.
  *   - a dq4ml_ctx owns one CUDA device, one stream and its scratch buffers; use one ctx per thread (or lock).
  *   - there is no CPU fallback: entry points that need a GPU fail with DQ4ML_ERR_NO_DEVICE without one.
  *     Entry points marked [host-only] never touch the GPU.

@@ -108,8 +108,8 @@ struct Resolver {
     for (size_t i = 0; i < inputs.size(); ++i) {
       const void* p = *inputs[i].slot;
       if (is_device_ptr(p)) {
-        if ((reinterpret_cast<uintptr_t>(p) & 15u) != 0) {
-          set_error("device column %p is not 16-byte aligned", p);
+        if ((reinterpret_cast<uintptr_t>(p) & 31u) != 0) {  // 256-bit loads
+          set_error("device column %p is not 32-byte aligned", p);
           return DQ4ML_ERR_INVALID;
         }
         continue;

@@ -21,16 +21,14 @@ struct DqThresholds {
 //   r1 = price < min_price ? -1 : price        keep iff r1 > 0   (Spark SQL ordering: NaN > 0 is true)
 //   r2 = guest < min_guest && r1 > max_price ? -1 : r1           keep iff r2 > 0
 // Java's `<`/`>` are IEEE (false on NaN), so a NaN price passes through both rules and both filters.
-__device__ __forceinline__ bool dq_keep(int guest, double price, const DqThresholds& t) {
-  const double r1 = price < t.min_price ? -1.0 : price;
-  const bool k1 = (r1 != r1) || (r1 > 0.0);
-  const double r2 = (guest < t.min_guest && r1 > t.max_price) ? -1.0 : r1;
-  const bool k2 = (r2 != r2) || (r2 > 0.0);
-  return k1 && k2;
-}
+// Reduced to three fp64 compares (the fp64 pipe is shared with the accumulations of a 12 B/row pass):
+//   r1 > 0 (Spark ordering)  <=>  !(price < min_price) && !(price <= 0)   [NaN fails both tests and is kept]
+//   r2 > 0                   <=>  r1 > 0 && !(guest < min_guest && price > max_price)
 __device__ __forceinline__ bool dq_keep_rule1(double price, const DqThresholds& t) {
-  const double r1 = price < t.min_price ? -1.0 : price;
-  return (r1 != r1) || (r1 > 0.0);
+  return !(price < t.min_price) && !(price <= 0.0);
+}
+__device__ __forceinline__ bool dq_keep(int guest, double price, const DqThresholds& t) {
+  return dq_keep_rule1(price, t) && !(guest < t.min_guest && price > t.max_price);
 }
 
 // Streaming loads: read-only path, do not allocate in L1 (every byte is touched once per pass).
@@ -57,7 +55,12 @@ __device__ __forceinline__ void stg_stream_d2(void* p, double2 v) {
 // columns).  VEC: the column base is 16-byte aligned and row % ROWS == 0, so 128-bit / 64-bit vector loads are legal.
 template <int ROWS, bool VEC>
 __device__ __forceinline__ void load_f64(const double* col, int64_t row, double (&v)[ROWS]) {
-  if constexpr (VEC) {
+  if constexpr (VEC && ROWS % 4 == 0) {  // 256-bit loads (PTX ISA 8.8, sm_100+); the row offset keeps them 32-byte aligned
+#pragma unroll
+    for (int r = 0; r < ROWS; r += 4)
+      asm("ld.global.nc.L1::no_allocate.v4.f64 {%0,%1,%2,%3}, [%4];"
+          : "=d"(v[r]), "=d"(v[r + 1]), "=d"(v[r + 2]), "=d"(v[r + 3]) : "l"(col + row + r));
+  } else if constexpr (VEC) {
 #pragma unroll
     for (int r = 0; r < ROWS; r += 2) {
       const double2 t = ldg_stream_d2(col + row + r);
@@ -71,7 +74,10 @@ __device__ __forceinline__ void load_f64(const double* col, int64_t row, double 
 }
 template <int ROWS, bool VEC>
 __device__ __forceinline__ void load_i32(const int* col, int64_t row, int (&v)[ROWS]) {
-  if constexpr (VEC && ROWS == 4) {
+  if constexpr (VEC && ROWS == 8) {
+    asm("ld.global.nc.L1::no_allocate.v8.s32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]) : "l"(col + row));
+  } else if constexpr (VEC && ROWS == 4) {
     const int4 t = ldg_stream_i4(col + row);
     v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
   } else if constexpr (VEC && ROWS == 2) {

@@ -1,6 +1,7 @@
 // stream_launch.cu -- instantiates stream_reduce_kernel for every (op, column-group bucket, DQ mode) the path uses
 // and picks one at run time.  Buckets 1,2,4,8 stream 4 rows per thread per tile, buckets 16,32 stream 2 (register
 // budget); grids are sized to (CTAs resident per SM) x (SM count) so the whole pass is one wave of persistent CTAs.
+#include <cstdlib>
 #include <map>
 #include <mutex>
 
@@ -59,13 +60,16 @@ cudaError_t launch_one(const Op& op, const PassArgs& a) {
       e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, kBlock, 0);
       if (e != cudaSuccess) return e;
       if (per_sm < 1) per_sm = 1;
+      // measured (tools/k2_variants.cu, 10^8 rows of 12 B): 4 CTAs/SM stream at 6.0-6.2 TB/s, 6 CTAs/SM at 4.9-5.7
+      if (ROWS == 8 && per_sm > 4) per_sm = 4;  // measured on the bench workload: 3 -> 5.76, 4 -> 6.36, 6 -> 5.45 TB/s
+      if (const char* env = getenv("DQ4ML_STREAM_CTAS")) { const int v = atoi(env); if (v >= 1) per_sm = v; }
       blocks_per_sm[dev] = per_sm;
     } else {
       per_sm = it->second;
     }
   }
   const int64_t tile_rows = static_cast<int64_t>(kBlock) * ROWS;
-  const int64_t n_tiles = (a.n + tile_rows - 1) / tile_rows;
+  const int64_t n_tiles = (a.n + tile_rows - 1) / tile_rows;  // the partial tile is taken by CTA (full_tiles % grid) < grid
   int64_t grid = static_cast<int64_t>(per_sm) * a.scratch.sm_count;
   if (grid > n_tiles) grid = n_tiles;
   if (grid < 1) grid = 1;
@@ -105,7 +109,9 @@ EvalOp<DMAX> make_eval(const EvalConsts& c) {
 
 template <int DMAX>
 cudaError_t launch_bucket(StreamOpKind kind, const PassArgs& a, const void* host_consts) {
-  constexpr int ROWS = DMAX <= 8 ? 4 : 2;
+  // rows per thread per tile: what keeps ~100 bytes per thread in flight without spilling (tools/k2_variants.cu: 8 rows
+  // with 256-bit loads at 3 CTAs/SM stream a 12 B/row table at 6.2 TB/s, 4 rows at 6 CTAs/SM at 5.8)
+  constexpr int ROWS = DMAX <= 2 ? 8 : (DMAX <= 8 ? 4 : 2);
   switch (kind) {
     case kOpWls:
       if constexpr (DMAX <= 8) return launch_mode<WlsOp<DMAX>, DMAX, ROWS>(WlsOp<DMAX>{}, a);

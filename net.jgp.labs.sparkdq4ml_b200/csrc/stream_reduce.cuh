@@ -110,10 +110,17 @@ __global__ void __launch_bounds__(kBlock)
 #pragma unroll
   for (int k = 0; k < Op::NCONST; ++k) consts[k] = __ldg(dev_consts + k);
 
+  // Full tiles first, with no tail test inside the loop so that it can be unrolled and the loads of the next tile are
+  // in flight during the arithmetic of this one (the ragged end of the table is one extra partial tile below).
   const int64_t tile_rows = static_cast<int64_t>(kBlock) * ROWS;
-  const int64_t n_tiles = (n + tile_rows - 1) / tile_rows;
-  for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+  const int64_t full_tiles = n / tile_rows;
+#pragma unroll 2
+  for (int64_t tile = blockIdx.x; tile < full_tiles; tile += gridDim.x) {
     const int64_t row = tile * tile_rows + static_cast<int64_t>(threadIdx.x) * ROWS;
+    process_rows<Op, DMAX, ROWS, DQMODE, true>(op, acc, consts, cols, d, label, dq, row, row_out);
+  }
+  if (full_tiles * tile_rows < n && static_cast<int64_t>(blockIdx.x) == full_tiles % gridDim.x) {
+    const int64_t row = full_tiles * tile_rows + static_cast<int64_t>(threadIdx.x) * ROWS;
     if (row + ROWS <= n) {
       process_rows<Op, DMAX, ROWS, DQMODE, true>(op, acc, consts, cols, d, label, dq, row, row_out);
     } else {
