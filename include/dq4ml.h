@@ -190,6 +190,15 @@ int dq4ml_dq_filter_noalloc(void* stream, const int32_t* guest, const double* pr
                             const dq4ml_dq_params* params, int32_t* guest_out, double* price_out, int64_t* n_out,
                             int64_t* n_after_rule1);
 
+/* CSV ingest for the lab's dialect: spark.read().format("csv").option("inferSchema","true").option("header","false")
+ * .load("data/dataset-*.csv") (App:52-55) followed by the two renames (App:58-59).  Records end at CR, LF or CRLF
+ * (the lab's files use bare CR), have no header, and hold `int,decimal`; empty records are skipped.  data (len bytes)
+ * and the two outputs (room for cap records) may each be host or device memory; the decimal is converted exactly as
+ * Double.parseDouble would (correctly rounded).  n_records (HOST) receives the record count; a malformed record or
+ * cap < count is DQ4ML_ERR_INVALID. */
+int dq4ml_csv_parse(dq4ml_ctx* ctx, const char* data, int64_t len, int32_t* guest_out, double* price_out, int64_t cap,
+                    int64_t* n_records);
+
 /* ------------------------------------------------------------------------------------------------ LinearRegression */
 
 /* [host-only] */

@@ -91,6 +91,7 @@ SIGNATURES = {
                                   C.c_void_p, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]),
     "dq4ml_dq_filter_noalloc": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.POINTER(DqParams), C.c_void_p,
                                           C.c_void_p, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]),
+    "dq4ml_csv_parse": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_int64, C.POINTER(C.c_int64)]),
     "dq4ml_lr_params_default": (LrParams, []),
     "dq4ml_wls_moments_len": (C.c_int64, [C.c_int32]),
     "dq4ml_wls_moments": (C.c_int, [C.c_void_p, C.POINTER(Columns), C.c_void_p, C.c_int64, C.POINTER(DqFused), C.c_void_p]),

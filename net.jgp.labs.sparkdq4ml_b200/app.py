@@ -18,7 +18,7 @@ from .runtime import Context
 
 def parse_lab_csv(data: bytes):
     """The lab's CSV dialect (App:52-55: header=false, inferSchema=true): records split on \\r, \\n or \\r\\n,
-    `_c0` integer, `_c1` double.  Host-side ingest; the GPU parser is a "next" row of the scope table."""
+    `_c0` integer, `_c1` double.  Host-side reference of the dialect; the app itself ingests on the GPU (Context.read_csv)."""
     text = data.decode("ascii").replace("\r\n", "\n").replace("\r", "\n")
     guest, price = [], []
     for rec in text.split("\n"):
@@ -41,12 +41,8 @@ class DataQuality4MachineLearningApp:
         self.udf.register("minimumPriceRule", dqmod.MinimumPriceDataQualityUdf(), dqmod.DoubleType)
         self.udf.register("priceCorrelationRule", dqmod.PriceCorrelationDataQualityUdf(), dqmod.DoubleType)
         # load + rename (App:52-59)
-        guest, price = parse_lab_csv(csv_bytes)
-        n_loaded = guest.size
-        if to_device:
-            import torch
-            dev = f"cuda:{ctx.device}"
-            guest, price = torch.from_numpy(guest).to(dev), torch.from_numpy(price).to(dev)
+        guest, price = ctx.read_csv(csv_bytes, to_device=to_device)  # GPU ingest (dq4ml_csv_parse)
+        n_loaded = int(guest.shape[0])
         out = {"n_loaded": int(n_loaded)}
         if not fused:
             # 1) min price (App:68-78)

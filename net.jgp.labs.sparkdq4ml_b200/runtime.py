@@ -125,6 +125,30 @@ class Context:
         extra = store[:, :n]  # extra[k] is a contiguous 1-D column
         return guest, price, extra
 
+    def read_csv(self, data: bytes, to_device=True):
+        """spark.read().format("csv").option("inferSchema","true").option("header","false").load(...) for the lab's
+        two-column dialect (DataQuality4MachineLearningApp.java:52-59): returns (guest:int32, price:f64), parsed on the
+        GPU, as torch cuda tensors (or numpy arrays when to_device is False)."""
+        import torch
+
+        n_bytes = len(data)
+        cap = n_bytes // 4 + 1  # the shortest record, "1,2" + separator, is 4 bytes
+        if to_device:
+            dev = f"cuda:{self.device}"
+            guest = torch.empty(cap, dtype=torch.int32, device=dev)
+            price = torch.empty(cap, dtype=torch.float64, device=dev)
+        else:
+            guest = np.empty(cap, dtype=np.int32)
+            price = np.empty(cap, dtype=np.float64)
+        n = C.c_int64(0)
+        buf = C.create_string_buffer(data, n_bytes) if n_bytes else None
+        capi.check(capi.lib().dq4ml_csv_parse(self._h, C.cast(buf, C.c_void_p) if buf is not None else None, n_bytes,
+                                               capi.buf_ptr(guest), capi.buf_ptr(price), cap, C.byref(n)))
+        m = int(n.value)
+        if to_device:
+            return guest[:m].clone(), price[:m].clone()  # own, aligned storage of the right length
+        return guest[:m].copy(), price[:m].copy()
+
     def rows_digest(self, guest, price, seed=0):
         out = np.zeros(2, dtype=np.uint64)
         capi.check(capi.lib().dq4ml_rows_digest(self._h, capi.buf_ptr(guest), capi.buf_ptr(price), capi.buf_len(guest),
