@@ -133,14 +133,17 @@ __global__ void __launch_bounds__(kFilterThreads, 4)
       }
     }
     unsigned mask[kPerLane];
-    unsigned warp_total = 0, rule1 = 0;
+    unsigned warp_total = 0, only_rule2 = 0;  // rows that pass rule 1 but fall to rule 2 (rare): counted per thread
+    // rows past the end of the data were loaded as price 0, which rule 1 drops: no bounds test is needed here
 #pragma unroll
     for (int j = 0; j < kPerLane; ++j) {
-      const bool in = warp_row + 32 * j < n;
-      mask[j] = __ballot_sync(0xffffffffu, in && dq_keep(g[j], p[j], t));
-      rule1 += __popc(__ballot_sync(0xffffffffu, in && dq_keep_rule1(p[j], t)));
+      const bool k1 = dq_keep_rule1(p[j], t);
+      const bool k = k1 && !(g[j] < t.min_guest && p[j] > t.max_price);
+      mask[j] = __ballot_sync(0xffffffffu, k);
+      only_rule2 += (k1 && !k) ? 1u : 0u;
       warp_total += __popc(mask[j]);
     }
+    const unsigned rule1 = warp_total + __reduce_add_sync(0xffffffffu, only_rule2);
     if (lane == 0) {
       s_tot[warp] = warp_total;
       s_rule1[warp] = rule1;
