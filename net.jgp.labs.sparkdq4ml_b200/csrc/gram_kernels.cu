@@ -18,6 +18,10 @@
 //     tile lies below the diagonal, computes the border columns (X^T y, X^T 1) and the y/1 corner instead;
 //   * partial tiles go to scratch, and a second small kernel sums the row slices in a fixed order straight into the
 //     WLS moment layout (deterministic, no atomics).
+// Two further experiments did not pay (round 1, 62.5 M x 256): rotating the warp roles between co-resident CTAs and
+// skipping the sub-diagonal fragments of diagonal warp tiles (174 ms vs 168 ms: the per-chunk barrier makes the
+// heaviest warp the critical path); an 11-fragment-per-warp balanced diagonal CTA with 11/16 as many row slices
+// (181 ms: CTAs of different pairs then walk different rows at the same time and the L2 reuse between them is lost).
 // fp64 DMMA and DFMA both peak at 37.2 TFLOP/s on B200 (tools/fp64_peak.cu), so this pass is bound by the fp64 pipe,
 // not by HBM: 66 816 flop per row at d = 256 against 2 056 B.
 #include <algorithm>
