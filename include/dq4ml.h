@@ -249,6 +249,13 @@ int32_t dq4ml_linreg_model_data_passes(const dq4ml_lr_model* m);          /* agg
 int64_t dq4ml_linreg_model_num_rows(const dq4ml_lr_model* m);             /* rows that entered the fit */
 const char* dq4ml_linreg_model_solver_used(const dq4ml_lr_model* m);
 double dq4ml_linreg_predict1(const dq4ml_lr_model* m, const double* x /* d */); /* model.predict(Vector) App:150-151 */
+/* [host-only] LinearRegressionTrainingSummary.coefficientStandardErrors / tValues / pValues (beyond what the lab
+ * prints at App:132-139): k = numFeatures (+1 for the intercept, last) values each, from the diagonal of (A^T A)^-1 kept
+ * by the normal-equation Cholesky solve, the residual sum of squares and the instance count of an evaluation
+ * (metrics[1], metrics[0] of dq4ml_linreg_evaluate).  Any output may be NULL.  Returns k, or DQ4ML_ERR_UNSUPPORTED
+ * for models fitted another way (Spark: "No Std. Error of coefficients available for this LinearRegressionModel"). */
+int dq4ml_linreg_model_inference(const dq4ml_lr_model* m, double num_instances, double ss_err, int fit_intercept,
+                                 double* std_err, double* t_values, double* p_values, int32_t cap);
 void dq4ml_linreg_model_destroy(dq4ml_lr_model* m);
 /* [host-only] build a model from known coefficients (LinearRegressionModel's constructor). */
 int dq4ml_linreg_model_create(const double* coef, int32_t d, double intercept, dq4ml_lr_model** out);
@@ -258,8 +265,11 @@ int dq4ml_linreg_transform(dq4ml_ctx* ctx, const dq4ml_lr_model* m, const dq4ml_
                            double* prediction /* host or device, n */);
 
 /* LinearRegressionTrainingSummary.residuals()/rootMeanSquaredError()/r2() (App:137-139), one fused pass:
- * metrics (HOST) = [n, SSerr, sum_y, sum_yy, sum_abs_err, rmse, r2, mse, mae]; residuals (nullable, host or device,
+ * metrics (HOST, DQ4ML_METRICS_LEN = 16 doubles) = [n, SSerr, sum_y, sum_yy, sum_abs_err, rmse, r2, mse, mae,
+ * explainedVariance, degreesOfFreedom, r2adj, min residual, max residual (devianceResiduals), sum_res, sum_res_y];
+ * residuals (nullable, host or device,
  * n values, label - prediction; rows skipped by fused DQ get 0).  Summed over ranks when bound. */
+#define DQ4ML_METRICS_LEN 16
 int dq4ml_linreg_evaluate(dq4ml_ctx* ctx, const dq4ml_lr_model* m, const dq4ml_columns* features, const double* label,
                           int64_t n, const dq4ml_dq_fused* dq, int fit_intercept, double* metrics, double* residuals);
 

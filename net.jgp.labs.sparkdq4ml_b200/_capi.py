@@ -111,6 +111,8 @@ SIGNATURES = {
     "dq4ml_linreg_model_num_rows": (C.c_int64, [C.c_void_p]),
     "dq4ml_linreg_model_solver_used": (C.c_char_p, [C.c_void_p]),
     "dq4ml_linreg_predict1": (C.c_double, [C.c_void_p, C.c_void_p]),
+    "dq4ml_linreg_model_inference": (C.c_int, [C.c_void_p, C.c_double, C.c_double, C.c_int, C.c_void_p, C.c_void_p,
+                                               C.c_void_p, C.c_int32]),
     "dq4ml_linreg_model_destroy": (None, [C.c_void_p]),
     "dq4ml_linreg_model_create": (C.c_int, [C.c_void_p, C.c_int32, C.c_double, C.POINTER(C.c_void_p)]),
     "dq4ml_linreg_transform": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(Columns), C.c_int64, C.c_void_p]),

@@ -475,6 +475,32 @@ int lsq_pass(dq4ml_ctx* ctx, const PassInputs& in, int64_t n, const double* coef
   return DQ4ML_OK;
 }
 
+// Cross-rank reduction of the nine evaluation accumulators: seven sums, then min and max of the residuals (which travel
+// as a zero-padded sum so that the only collective needed is the sum all-reduce).
+int reduce_eval_sums(dq4ml_ctx* ctx, double* s) {
+  if (!multi_rank(ctx)) return DQ4ML_OK;
+  const int world = ctx->world > 0 ? ctx->world : 1;
+  std::vector<double> v(7 + 2 * static_cast<size_t>(world), 0.0);
+  std::copy(s, s + 7, v.begin());
+  v[7 + 2 * ctx->rank] = s[7];
+  v[7 + 2 * ctx->rank + 1] = s[8];
+  // +-inf (a rank without surviving rows) cannot ride a sum next to zeros of other ranks: send finite stand-ins
+  const double big = 1.7e308;
+  if (!(v[7 + 2 * ctx->rank] < big)) v[7 + 2 * ctx->rank] = big;
+  if (!(v[7 + 2 * ctx->rank + 1] > -big)) v[7 + 2 * ctx->rank + 1] = -big;
+  const int rc = host_allreduce(ctx, v.data(), static_cast<int64_t>(v.size()));
+  if (rc != DQ4ML_OK) return rc;
+  std::copy(v.begin(), v.begin() + 7, s);
+  double mn = big, mx = -big;
+  for (int r = 0; r < world; ++r) {
+    mn = std::min(mn, v[7 + 2 * r]);
+    mx = std::max(mx, v[7 + 2 * r + 1]);
+  }
+  s[7] = mn;
+  s[8] = mx;
+  return DQ4ML_OK;
+}
+
 LrParams to_params(const dq4ml_lr_params* p) {
   LrParams q;
   if (p != nullptr) {
@@ -1066,6 +1092,35 @@ double dq4ml_linreg_predict1(const dq4ml_lr_model* m, const double* x) {
   return s + m->m.intercept;
 }
 
+int dq4ml_linreg_model_inference(const dq4ml_lr_model* m, double num_instances, double ss_err, int fit_intercept,
+                                 double* std_err, double* t_values, double* p_values, int32_t cap) {
+  if (m == nullptr) {
+    set_error("null model");
+    return DQ4ML_ERR_INVALID;
+  }
+  const int k = static_cast<int>(m->m.diag_inv_atwa.size());
+  const int d = static_cast<int>(m->m.coefficients.size());
+  if (k == 0 || k != d + (fit_intercept ? 1 : 0)) {
+    set_error("No Std. Error of coefficients available for this LinearRegressionModel (normal-equation Cholesky fits only)");
+    return DQ4ML_ERR_UNSUPPORTED;
+  }
+  if (cap < k) {
+    set_error("inference: room for %d values, need %d", cap, k);
+    return DQ4ML_ERR_INVALID;
+  }
+  const double dof = num_instances - d - (fit_intercept ? 1.0 : 0.0);
+  const double sigma2 = ss_err / dof;  // rss / degreesOfFreedom
+  for (int i = 0; i < k; ++i) {
+    const double se = std::sqrt(m->m.diag_inv_atwa[i] * sigma2);
+    const double est = i < d ? m->m.coefficients[i] : m->m.intercept;
+    const double t = est / se;
+    if (std_err != nullptr) std_err[i] = se;
+    if (t_values != nullptr) t_values[i] = t;
+    if (p_values != nullptr) p_values[i] = student_t_two_sided_p(t, dof);
+  }
+  return k;
+}
+
 void dq4ml_linreg_model_destroy(dq4ml_lr_model* m) { delete m; }
 
 int dq4ml_linreg_model_create(const double* coef, int32_t d, double intercept, dq4ml_lr_model** out) {
@@ -1100,18 +1155,16 @@ static int eval_common(dq4ml_ctx* ctx, const dq4ml_lr_model* m, const dq4ml_colu
   if (in.width() > kMaxCols) {  // wide table: the column-walking row pass
     WideSums ws;
     rc = wide_rows_pass(ctx, in.ptr, in.dtype, m->m.coefficients.data(), m->m.intercept, 1.0, in.label, in.dq, n, mode,
-                        static_cast<double*>(ob.dev), multi_rank(ctx), &ws);
+                        static_cast<double*>(ob.dev), false, &ws);
     if (rc != DQ4ML_OK) return rc;
     if (ob.staged && n > 0) {
       CU(cudaMemcpyAsync(row_out_user, ob.dev, static_cast<size_t>(n) * 8, cudaMemcpyDeviceToHost, ctx->stream));
       CU(cudaStreamSynchronize(ctx->stream));
     }
     if (sums != nullptr) {
-      sums[0] = ws.n;
-      sums[1] = ws.ss_res;
-      sums[2] = ws.sum_y;
-      sums[3] = ws.sum_yy;
-      sums[4] = ws.sum_abs_res;
+      const double loc[9] = {ws.n, ws.ss_res, ws.sum_y, ws.sum_yy, ws.sum_abs_res, ws.sum_res, ws.sum_res_y, ws.min_res, ws.max_res};
+      std::copy(loc, loc + 9, sums);
+      return reduce_eval_sums(ctx, sums);
     }
     return DQ4ML_OK;
   }
@@ -1123,9 +1176,12 @@ static int eval_common(dq4ml_ctx* ctx, const dq4ml_lr_model* m, const dq4ml_colu
                                      ctx->stream, &ctx->launches);
   if (e != cudaSuccess) return cuda_fail(e, "predict/evaluate pass");
   if (ob.staged && n > 0) CU(cudaMemcpyAsync(row_out_user, ob.dev, static_cast<size_t>(n) * 8, cudaMemcpyDeviceToHost, ctx->stream));
-  rc = finish_result(ctx, 5);
+  rc = finish_result(ctx, 9, false);
   if (rc != DQ4ML_OK) return rc;
-  if (sums != nullptr) std::copy(ctx->h_result, ctx->h_result + 5, sums);
+  if (sums != nullptr) {
+    std::copy(ctx->h_result, ctx->h_result + 9, sums);
+    return reduce_eval_sums(ctx, sums);
+  }
   return DQ4ML_OK;
 }
 
@@ -1154,17 +1210,31 @@ int dq4ml_linreg_evaluate(dq4ml_ctx* ctx, const dq4ml_lr_model* m, const dq4ml_c
     set_error("evaluate: null label / metrics");
     return DQ4ML_ERR_INVALID;
   }
-  double s[5];
+  double s[9];
   const int rc = eval_common(ctx, m, features, label, n, dq, 1, residuals, s);
   if (rc != DQ4ML_OK) return rc;
-  const double cnt = s[0], ss_err = s[1], sy = s[2], syy = s[3], sabs = s[4];
+  const double cnt = s[0], ss_err = s[1], sy = s[2], syy = s[3], sabs = s[4], sr = s[5], sry = s[6];
   for (int k = 0; k < 5; ++k) metrics[k] = s[k];
   const double mse = cnt > 0 ? ss_err / cnt : 0.0;
-  const double ss_tot = fit_intercept ? syy - (cnt > 0 ? sy * sy / cnt : 0.0) : syy;
+  const double y_bar = cnt > 0 ? sy / cnt : 0.0;
+  const double ss_tot = fit_intercept ? syy - sy * y_bar : syy;
+  const double r2 = 1.0 - ss_err / ss_tot;
   metrics[5] = std::sqrt(mse);          // rootMeanSquaredError
-  metrics[6] = 1.0 - ss_err / ss_tot;   // r2
-  metrics[7] = mse;
-  metrics[8] = cnt > 0 ? sabs / cnt : 0.0;
+  metrics[6] = r2;                      // r2
+  metrics[7] = mse;                     // meanSquaredError
+  metrics[8] = cnt > 0 ? sabs / cnt : 0.0;  // meanAbsoluteError
+  // RegressionMetrics.explainedVariance = SSreg / n with SSreg = sum (prediction - mean(label))^2, prediction = y - r
+  const double sum_pred = sy - sr, sum_pred2 = syy - 2.0 * sry + ss_err;
+  metrics[9] = cnt > 0 ? (sum_pred2 - 2.0 * y_bar * sum_pred + cnt * y_bar * y_bar) / cnt : 0.0;
+  // LinearRegressionSummary.degreesOfFreedom / r2adj
+  const double k_int = fit_intercept ? 1.0 : 0.0;
+  const double dof = cnt - static_cast<double>(m->m.coefficients.size()) - k_int;
+  metrics[10] = dof;
+  metrics[11] = 1.0 - (1.0 - r2) * (cnt - k_int) / dof;
+  metrics[12] = cnt > 0 ? s[7] : 0.0;   // devianceResiduals: min and max residual
+  metrics[13] = cnt > 0 ? s[8] : 0.0;
+  metrics[14] = sr;
+  metrics[15] = sry;
   return DQ4ML_OK;
 }
 

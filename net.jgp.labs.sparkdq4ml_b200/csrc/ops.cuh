@@ -148,18 +148,21 @@ struct GradOp {
   }
 };
 
-// LinearRegressionModel.transform + RegressionMetrics in one pass: yhat = x.beta + b; residual = y - yhat;
-// accumulators n, SSerr, sum y, sum y^2, sum |residual|.  Per-row output: prediction (mode 0) or residual (mode 1).
+// LinearRegressionModel.transform + RegressionMetrics / LinearRegressionSummary sums in one pass: yhat = x.beta + b;
+// residual r = y - yhat; accumulators n, sum r^2, sum y, sum y^2, sum |r|, sum r, sum r*y, min r, max r (the last four
+// feed explainedVariance and devianceResiduals).  Per-row output: prediction (mode 0) or residual (mode 1).
 template <int DMAX>
 struct EvalOp {
-  static constexpr int NACC = 5;
+  static constexpr int NACC = 9;
   static constexpr int NCONST = 0;
   static constexpr bool HAS_OUT = true;
   double coef[DMAX];
   double intercept;
   int mode;
-  __host__ __device__ static constexpr double identity(int) { return 0.0; }
-  __host__ __device__ static constexpr int kind(int) { return kSum; }
+  __host__ __device__ static constexpr int kind(int k) { return k == 7 ? kMin : (k == 8 ? kMax : kSum); }
+  __host__ __device__ static constexpr double identity(int k) {
+    return k == 7 ? __builtin_huge_val() : (k == 8 ? -__builtin_huge_val() : 0.0);
+  }
 
   __device__ __forceinline__ double row(double (&acc)[NACC], const double*, const double (&x)[DMAX], double y,
                                         bool keep, int) const {
@@ -174,6 +177,10 @@ struct EvalOp {
     acc[2] += y;
     acc[3] = fma(y, y, acc[3]);
     acc[4] += fabs(res);
+    acc[5] += res;
+    acc[6] = fma(res, y, acc[6]);
+    acc[7] = combine(kMin, acc[7], keep ? res : __builtin_huge_val());
+    acc[8] = combine(kMax, acc[8], keep ? res : -__builtin_huge_val());
     return mode == 0 ? yhat : res;
   }
 };

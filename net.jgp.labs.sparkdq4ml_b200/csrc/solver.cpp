@@ -338,6 +338,82 @@ int packed_cholesky_solve(Vec& ap, Vec& b) {
   return 0;
 }
 
+bool packed_spd_inverse_diag(Vec ap, int k, Vec* diag) {
+  auto at = [&](int i, int j) -> double& { return ap[static_cast<size_t>(i) + static_cast<size_t>(j) * (j + 1) / 2]; };
+  // A = U^T U (as in packed_cholesky_solve), then V = U^-1 (upper triangular) and (A^-1)_ii = sum_{j >= i} V_ij^2
+  for (int j = 0; j < k; ++j) {
+    double d = at(j, j);
+    for (int i = 0; i < j; ++i) {
+      double t = at(i, j);
+      for (int l = 0; l < i; ++l) t -= at(l, i) * at(l, j);
+      t /= at(i, i);
+      at(i, j) = t;
+      d -= t * t;
+    }
+    if (!(d > 0.0)) return false;
+    at(j, j) = std::sqrt(d);
+  }
+  diag->assign(k, 0.0);
+  Vec col(k);
+  for (int j = 0; j < k; ++j) {  // column j of V solves U v = e_j by back substitution; only rows <= j are non-zero
+    for (int i = j; i >= 0; --i) {
+      double t = i == j ? 1.0 : 0.0;
+      for (int l = i + 1; l <= j; ++l) t -= at(i, l) * col[l];
+      col[i] = t / at(i, i);
+    }
+    for (int i = 0; i <= j; ++i) (*diag)[i] += col[i] * col[i];
+  }
+  return true;
+}
+
+namespace {
+
+// Regularised incomplete beta function I_x(a, b) by Lentz's continued fraction (Numerical Recipes 6.4).
+double beta_cf(double a, double b, double x) {
+  const double tiny = 1e-300, eps = 1e-16;
+  const double qab = a + b, qap = a + 1.0, qam = a - 1.0;
+  double c = 1.0, d = 1.0 - qab * x / qap;
+  if (std::fabs(d) < tiny) d = tiny;
+  d = 1.0 / d;
+  double h = d;
+  for (int m = 1; m <= 10000; ++m) {
+    const int m2 = 2 * m;
+    double aa = m * (b - m) * x / ((qam + m2) * (a + m2));
+    d = 1.0 + aa * d;
+    if (std::fabs(d) < tiny) d = tiny;
+    c = 1.0 + aa / c;
+    if (std::fabs(c) < tiny) c = tiny;
+    d = 1.0 / d;
+    h *= d * c;
+    aa = -(a + m) * (qab + m) * x / ((a + m2) * (qap + m2));
+    d = 1.0 + aa * d;
+    if (std::fabs(d) < tiny) d = tiny;
+    c = 1.0 + aa / c;
+    if (std::fabs(c) < tiny) c = tiny;
+    d = 1.0 / d;
+    const double del = d * c;
+    h *= del;
+    if (std::fabs(del - 1.0) < eps) break;
+  }
+  return h;
+}
+
+double reg_inc_beta(double a, double b, double x) {
+  if (x <= 0.0) return 0.0;
+  if (x >= 1.0) return 1.0;
+  const double ln_front = std::lgamma(a + b) - std::lgamma(a) - std::lgamma(b) + a * std::log(x) + b * std::log1p(-x);
+  if (x < (a + 1.0) / (a + b + 2.0)) return std::exp(ln_front) * beta_cf(a, b, x) / a;
+  return 1.0 - std::exp(ln_front) * beta_cf(b, a, 1.0 - x) / b;
+}
+
+}  // namespace
+
+double student_t_two_sided_p(double t, double dof) {
+  if (std::isnan(t) || !(dof > 0.0)) return std::numeric_limits<double>::quiet_NaN();
+  if (std::isinf(t)) return 0.0;
+  return reg_inc_beta(0.5 * dof, 0.5, dof / (dof + t * t));  // = 2 (1 - cdf(|t|))
+}
+
 namespace {
 
 // y = A x for packed upper column-major symmetric A of order k.
@@ -478,6 +554,16 @@ LrModel wls_fit_from_moments(const double* mom, int d, const LrParams& p) {
     } else {
       model.objective_history = {0.0};
       model.solver_used = "wls-cholesky";
+      // CholeskySolver also returns aaInv; WeightedLeastSquares keeps its diagonal, rescaled to original units:
+      // inv_ii / (wSum * aStd_i^2) for features, inv_kk / wSum for the intercept.  O(k^3 / 3) on the host.
+      Vec inv_diag;
+      if (k <= 2048 && packed_spd_inverse_diag(make_ata(), k, &inv_diag)) {
+        model.diag_inv_atwa.resize(k);
+        for (int i = 0; i < k; ++i) {
+          const double mult = (p.fit_intercept && i == k - 1) ? 1.0 : a_std[i] * a_std[i];
+          model.diag_inv_atwa[i] = inv_diag[i] / (w_sum * mult);
+        }
+      }
     }
   }
   model.coefficients.assign(sol.begin(), sol.begin() + d);

@@ -33,7 +33,16 @@ struct LrModel {
   std::string solver_used;
   int data_passes = 0;
   int64_t num_rows = 0;
+  // WeightedLeastSquaresModel.diagInvAtWA: diagonal of (A^T W A)^-1 in original units (features, then the intercept);
+  // filled on the Cholesky path only, like Spark.  Empty = "No Std. Error of coefficients available".
+  Vec diag_inv_atwa;
 };
+
+// Diagonal of the inverse of a packed upper SPD matrix (LAPACK dpptri, diagonal only).  Returns false if not SPD.
+bool packed_spd_inverse_diag(Vec ap, int k, Vec* diag);
+
+// Two-sided p-value of a Student-t statistic: 2 (1 - cdf_dof(|t|)), as LinearRegressionSummary.pValues.
+double student_t_two_sided_p(double t, double dof);
 
 struct SolveError {
   int code;  // dq4ml_status

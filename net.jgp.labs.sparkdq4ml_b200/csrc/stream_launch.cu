@@ -23,7 +23,7 @@ int stream_nacc(StreamOpKind op, int bucket) {
     case kOpLsq: return 2 + bucket;
     case kOpSummCore: return 1 + 2 * (bucket + 1);
     case kOpSummFull: return 1 + 7 * bucket;
-    case kOpEval: return 5;
+    case kOpEval: return 9;
     case kOpGrad: return bucket;
   }
   return 0;

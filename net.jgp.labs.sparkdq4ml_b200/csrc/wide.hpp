@@ -9,7 +9,7 @@
 namespace dq4ml {
 
 struct WideSums {
-  double n, ss_res, sum_y, sum_yy, sum_abs_res;
+  double n, ss_res, sum_y, sum_yy, sum_abs_res, sum_res, sum_res_y, min_res, max_res;
 };
 
 // For every row kept by the DQ predicate: pred = x . coef + c0, res = y * y_scale - pred.

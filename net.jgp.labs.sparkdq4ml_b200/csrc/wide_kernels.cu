@@ -29,10 +29,11 @@ struct WideArgs {
   double* result;
 };
 
-constexpr int kWideAcc = 5;
+constexpr int kWideAcc = 9;
+__device__ __forceinline__ int wide_kind(int k) { return k == 7 ? kMin : (k == 8 ? kMax : kSum); }
 
 __global__ void __launch_bounds__(kBlock) wide_rows_kernel(const WideArgs a) {
-  double acc[kWideAcc] = {0.0, 0.0, 0.0, 0.0, 0.0};
+  double acc[kWideAcc] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0, __builtin_huge_val(), -__builtin_huge_val()};
   const long long tile_rows = 2LL * kBlock;
   const long long n_tiles = (a.n + tile_rows - 1) / tile_rows;
   for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
@@ -91,6 +92,10 @@ __global__ void __launch_bounds__(kBlock) wide_rows_kernel(const WideArgs a) {
     acc[2] += ys0 + ys1;
     acc[3] = fma(ys0, ys0, fma(ys1, ys1, acc[3]));
     acc[4] += fabs(r0) + fabs(r1);
+    acc[5] += r0 + r1;
+    acc[6] = fma(r0, ys0, fma(r1, ys1, acc[6]));
+    acc[7] = combine(kMin, acc[7], combine(kMin, k0 ? r0 : __builtin_huge_val(), k1 ? r1 : __builtin_huge_val()));
+    acc[8] = combine(kMax, acc[8], combine(kMax, k0 ? r0 : -__builtin_huge_val(), k1 ? r1 : -__builtin_huge_val()));
     if (a.row_out != nullptr) {
       const double o0 = a.mode == 0 ? pred0 : r0, o1 = a.mode == 0 ? pred1 : r1;
       if (pair) stg_stream_d2(a.row_out + row, make_double2(o0, o1));
@@ -101,7 +106,7 @@ __global__ void __launch_bounds__(kBlock) wide_rows_kernel(const WideArgs a) {
   __shared__ double s_red[kBlock / 32];
   __shared__ bool s_last;
   for (int k = 0; k < kWideAcc; ++k) {
-    const double v = block_reduce(acc[k], kSum, s_red);
+    const double v = block_reduce(acc[k], wide_kind(k), s_red);
     if (threadIdx.x == 0) a.partials[static_cast<size_t>(blockIdx.x) * kWideAcc + k] = v;
   }
   __threadfence();
@@ -111,9 +116,10 @@ __global__ void __launch_bounds__(kBlock) wide_rows_kernel(const WideArgs a) {
   if (!s_last) return;
   __threadfence();
   for (int k = 0; k < kWideAcc; ++k) {
-    double v = 0.0;
-    for (unsigned b = threadIdx.x; b < gridDim.x; b += kBlock) v += __ldcg(a.partials + static_cast<size_t>(b) * kWideAcc + k);
-    v = block_reduce(v, kSum, s_red);
+    const int kind = wide_kind(k);
+    double v = kind == kMin ? __builtin_huge_val() : (kind == kMax ? -__builtin_huge_val() : 0.0);
+    for (unsigned b = threadIdx.x; b < gridDim.x; b += kBlock) v = combine(kind, v, __ldcg(a.partials + static_cast<size_t>(b) * kWideAcc + k));
+    v = block_reduce(v, kind, s_red);
     if (threadIdx.x == 0) a.result[k] = v;
   }
   if (threadIdx.x == 0) *a.ticket = 0u;
@@ -215,6 +221,10 @@ int wide_rows_pass(dq4ml_ctx* ctx, const std::vector<const void*>& col_ptrs, con
     sums->sum_y = ctx->h_result[2];
     sums->sum_yy = ctx->h_result[3];
     sums->sum_abs_res = ctx->h_result[4];
+    sums->sum_res = ctx->h_result[5];
+    sums->sum_res_y = ctx->h_result[6];
+    sums->min_res = ctx->h_result[7];
+    sums->max_res = ctx->h_result[8];
   }
   return DQ4ML_OK;
 }

@@ -287,7 +287,7 @@ class LinearRegressionSummary:
                 res = torch.empty(df.n, dtype=torch.float64, device=label.device)
             else:
                 res = np.empty(df.n, dtype=np.float64)
-        met = np.zeros(9, dtype=np.float64)
+        met = np.zeros(16, dtype=np.float64)  # DQ4ML_METRICS_LEN
         capi.check(capi.lib().dq4ml_linreg_evaluate(df.ctx.handle, model._h, C.byref(tab), capi.buf_ptr(label), df.n,
                                                      C.byref(dqs) if dqs is not None else None,
                                                      int(model._est._fit_intercept), met.ctypes.data, capi.buf_ptr(res)))
@@ -320,6 +320,38 @@ class LinearRegressionSummary:
 
     def meanAbsoluteError(self):
         return float(self._m()[8])
+
+    def explainedVariance(self):
+        return float(self._m()[9])
+
+    def degreesOfFreedom(self):
+        return int(self._m()[10])
+
+    def r2adj(self):
+        return float(self._m()[11])
+
+    def _inference(self):
+        m = self._m()
+        k = self._model.numFeatures() + (1 if self._model._est._fit_intercept else 0)
+        se, tv, pv = (np.zeros(k, dtype=np.float64) for _ in range(3))
+        capi.check(capi.lib().dq4ml_linreg_model_inference(self._model._h, float(m[0]), float(m[1]),
+                                                            int(self._model._est._fit_intercept), se.ctypes.data,
+                                                            tv.ctypes.data, pv.ctypes.data, k))
+        return se, tv, pv
+
+    def coefficientStandardErrors(self):
+        """Standard errors of the coefficients (intercept last); normal-equation Cholesky fits only, like Spark."""
+        return self._inference()[0]
+
+    def tValues(self):
+        return self._inference()[1]
+
+    def pValues(self):
+        return self._inference()[2]
+
+    def devianceResiduals(self):
+        """[min, max] of the residuals (weights are 1), as Spark's LinearRegressionSummary.devianceResiduals."""
+        return [float(self._m()[12]), float(self._m()[13])]
 
 
 class LinearRegressionTrainingSummary(LinearRegressionSummary):

@@ -367,3 +367,42 @@ def test_wide_lbfgs_fit_d40(pkg, ctx):
     assert rel_err(model.summary().objectiveHistory(), ref.objective_history) < 1e-8
     np.testing.assert_allclose(model.coefficients(), ref.coefficients, rtol=1e-6, atol=1e-9)
     np.testing.assert_allclose(model.intercept(), ref.intercept, rtol=1e-8)
+
+
+@pytest.mark.parametrize("d", [3, 40])
+def test_training_summary_surface_vs_numpy(pkg, ctx, d):
+    """The rest of LinearRegressionTrainingSummary (explainedVariance, r2adj, degreesOfFreedom, devianceResiduals,
+    standard errors, t- and p-values) on an OLS fit with fused DQ, against numpy/scipy on the surviving rows."""
+    from scipy import stats
+    n = 80_000
+    guest, price, feats = wide_table(n, d)
+    keep = np.array([bool(passes.lib().orc_dq_keep(int(a), float(b))) for a, b in zip(guest, price)])
+    X = np.stack([np.asarray(f, dtype=np.float64)[keep] for f in feats], axis=1)
+    y = price[keep]
+    dfeats, dprice = to_dev(*feats), to_dev(price)[0]
+    cols = {"guest": dfeats[0], "label": dprice}
+    names = ["guest"]
+    for k in range(1, d):
+        cols[f"x{k}"] = dfeats[k]
+        names.append(f"x{k}")
+    df = pkg.VectorAssembler().setInputCols(names).transform(pkg.Frame(ctx, cols).with_fused_dq("guest", "label"))
+    model = pkg.LinearRegression().setSolver("normal").fit(df)
+    s = model.summary()
+    m = len(y)
+    Xa = np.hstack([X, np.ones((m, 1))])
+    beta = np.linalg.lstsq(Xa, y, rcond=None)[0]
+    pred = Xa @ beta
+    res = y - pred
+    np.testing.assert_allclose(np.append(model.coefficients(), model.intercept()), beta, rtol=1e-7, atol=1e-9)
+    assert s.numInstances() == m and s.degreesOfFreedom() == m - d - 1
+    r2 = 1 - (res @ res) / ((y - y.mean()) @ (y - y.mean()))
+    assert rel_err(s.r2(), r2) < 1e-9
+    assert rel_err(s.r2adj(), 1 - (1 - r2) * (m - 1) / (m - d - 1)) < 1e-9
+    assert rel_err(s.explainedVariance(), ((pred - y.mean()) ** 2).mean()) < 1e-8
+    assert rel_err(s.meanAbsoluteError(), np.abs(res).mean()) < 1e-8
+    np.testing.assert_allclose(s.devianceResiduals(), [res.min(), res.max()], rtol=1e-6, atol=1e-7)
+    dof = m - d - 1
+    se_ref = np.sqrt(np.diag(np.linalg.inv(Xa.T @ Xa)) * (res @ res) / dof)
+    np.testing.assert_allclose(s.coefficientStandardErrors(), se_ref, rtol=1e-6)
+    np.testing.assert_allclose(s.tValues(), beta / se_ref, rtol=1e-6)
+    np.testing.assert_allclose(s.pValues(), 2 * stats.t.sf(np.abs(beta / se_ref), dof), rtol=1e-5, atol=1e-300)

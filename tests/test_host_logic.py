@@ -174,3 +174,35 @@ def test_lab_csv_parser_matches_oracle(pkg, lab_csv):
         g, p = pkg.parse_lab_csv(lab_csv(name))
         go, po = passes.csv_parse(lab_csv(name))
         assert g.tolist() == go.tolist() and p.tobytes() == po.tobytes()
+
+
+def test_inference_statistics_match_numpy_scipy(pkg):
+    """coefficientStandardErrors / tValues / pValues (host-only entry point) against the textbook OLS formulas."""
+    from scipy import stats
+    from sparkdq4ml_b200 import ml
+    rng = np.random.default_rng(5)
+    n, d = 500, 5
+    X = rng.normal(size=(n, d)) * rng.uniform(0.5, 4.0, size=d) + rng.uniform(-2, 2, size=d)
+    y = X @ np.array([1.5, 0.0, -2.0, 0.02, 0.7]) + 4.0 + rng.normal(size=n) * 1.3
+    feats = [np.ascontiguousarray(X[:, j]) for j in range(d)]
+    mom = passes.wls_moments(feats, y)
+    model = ml.wls_solve(mom, d, pkg.LinearRegression())  # regParam 0 -> Cholesky
+    assert model.solver_used == "wls-cholesky"
+    Xa = np.hstack([X, np.ones((n, 1))])
+    beta = np.linalg.solve(Xa.T @ Xa, Xa.T @ y)
+    np.testing.assert_allclose(np.append(model.coefficients(), model.intercept()), beta, rtol=1e-9, atol=1e-11)
+    res = y - Xa @ beta
+    dof = n - d - 1
+    se_ref = np.sqrt(np.diag(np.linalg.inv(Xa.T @ Xa)) * (res @ res) / dof)
+    t_ref = beta / se_ref
+    p_ref = 2.0 * stats.t.sf(np.abs(t_ref), dof)
+    se, tv, pv = (np.zeros(d + 1) for _ in range(3))
+    k = pkg.capi.lib().dq4ml_linreg_model_inference(model._h, float(n), float(res @ res), 1, se.ctypes.data, tv.ctypes.data,
+                                                    pv.ctypes.data, d + 1)
+    assert k == d + 1
+    np.testing.assert_allclose(se, se_ref, rtol=1e-8)
+    np.testing.assert_allclose(tv, t_ref, rtol=1e-8)
+    np.testing.assert_allclose(pv, p_ref, rtol=1e-7, atol=1e-300)
+    # models fitted another way have no standard errors, like Spark
+    lasso = ml.wls_solve(mom, d, pkg.LinearRegression().setRegParam(0.1).setElasticNetParam(1.0))
+    assert pkg.capi.lib().dq4ml_linreg_model_inference(lasso._h, float(n), 1.0, 1, None, None, None, d + 1) == pkg.capi.ERR_UNSUPPORTED
