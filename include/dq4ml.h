@@ -239,6 +239,14 @@ int dq4ml_lsq_loss_grad(dq4ml_ctx* ctx, const dq4ml_columns* features, const dou
 int dq4ml_linreg_fit(dq4ml_ctx* ctx, const dq4ml_columns* features, const double* label, int64_t n,
                      const dq4ml_lr_params* params, const dq4ml_dq_fused* dq, dq4ml_lr_model** out);
 
+/* LinearRegression.setWeightCol(...).fit(dataset): the same fit with instance weights (the lab never sets weightCol,
+ * App:111-126 leaves it at Spark's default; SURVEY.md 8f lists it as the next parameter).  weight: f64[n], host or
+ * device, every value >= 0 (Spark: require(w >= 0.0)); NULL = dq4ml_linreg_fit.  Normal-equation branch: the Gram
+ * kernel scales each row by sqrt(w) (any width).  l-bfgs branch: weighted summarizer (zero-weight rows are not counted,
+ * variance denominator wSum - sum(w^2)/wSum) and weighted LeastSquaresAggregator, at most 31 feature columns. */
+int dq4ml_linreg_fit_weighted(dq4ml_ctx* ctx, const dq4ml_columns* features, const double* label, const double* weight,
+                              int64_t n, const dq4ml_lr_params* params, const dq4ml_dq_fused* dq, dq4ml_lr_model** out);
+
 /* [host-only] LinearRegressionModel / LinearRegressionTrainingSummary getters (App:132-146). */
 int32_t dq4ml_linreg_model_num_features(const dq4ml_lr_model* m);
 int dq4ml_linreg_model_coefficients(const dq4ml_lr_model* m, double* coef /* d */);
@@ -272,6 +280,13 @@ int dq4ml_linreg_transform(dq4ml_ctx* ctx, const dq4ml_lr_model* m, const dq4ml_
 #define DQ4ML_METRICS_LEN 16
 int dq4ml_linreg_evaluate(dq4ml_ctx* ctx, const dq4ml_lr_model* m, const dq4ml_columns* features, const double* label,
                           int64_t n, const dq4ml_dq_fused* dq, int fit_intercept, double* metrics, double* residuals);
+
+/* LinearRegressionSummary under a weight column (Spark 2.4.4 keeps RegressionMetrics unweighted; only these differ):
+ * out3 (HOST) = [sum w r^2 (the rss of coefficientStandardErrors), min sqrt(w) r, max sqrt(w) r (devianceResiduals)]
+ * over the residual column r that dq4ml_linreg_evaluate wrote (host or device) and the weight column.  Rows the fused
+ * DQ rules skip do not take part.  Summed / folded over ranks when bound. */
+int dq4ml_weighted_residual_stats(dq4ml_ctx* ctx, const double* residuals, const double* weight, int64_t n,
+                                  const dq4ml_dq_fused* dq, double* out3);
 
 /* ------------------------------------------------------------------------------------------------ synthetic data */
 

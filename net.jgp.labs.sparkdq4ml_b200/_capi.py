@@ -102,6 +102,10 @@ SIGNATURES = {
                                       C.c_void_p, C.c_void_p, C.c_double, C.c_double, C.c_int, C.c_void_p]),
     "dq4ml_linreg_fit": (C.c_int, [C.c_void_p, C.POINTER(Columns), C.c_void_p, C.c_int64, C.POINTER(LrParams),
                                    C.POINTER(DqFused), C.POINTER(C.c_void_p)]),
+    "dq4ml_linreg_fit_weighted": (C.c_int, [C.c_void_p, C.POINTER(Columns), C.c_void_p, C.c_void_p, C.c_int64,
+                                            C.POINTER(LrParams), C.POINTER(DqFused), C.POINTER(C.c_void_p)]),
+    "dq4ml_weighted_residual_stats": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.POINTER(DqFused),
+                                                C.c_void_p]),
     "dq4ml_linreg_model_num_features": (C.c_int32, [C.c_void_p]),
     "dq4ml_linreg_model_coefficients": (C.c_int, [C.c_void_p, C.c_void_p]),
     "dq4ml_linreg_model_intercept": (C.c_double, [C.c_void_p]),

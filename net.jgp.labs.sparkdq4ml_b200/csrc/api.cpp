@@ -222,12 +222,15 @@ struct PassInputs {
   std::vector<int> dtype;
   DeviceCols cols;               // the same table in the fixed-size form the streaming kernels take (width <= kMaxCols)
   const double* label = nullptr;
+  const double* weight = nullptr;  // instance weights (weightCol); nullptr = every weight 1
+  DeviceCols wcols;                // [weight, features...] for the weighted streaming ops (width + 1 <= kMaxCols)
   DeviceDq dq;
   int width() const { return static_cast<int>(ptr.size()); }
 };
 
 int gather_inputs(dq4ml_ctx* ctx, const dq4ml_columns* features, const double* label, int64_t n,
-                  const dq4ml_dq_fused* dq, PassInputs* out, size_t out_bytes, int max_cols) {
+                  const dq4ml_dq_fused* dq, PassInputs* out, size_t out_bytes, int max_cols,
+                  const double* weight = nullptr) {
   if (features == nullptr || n < 0 || features->n_cols < 0 || (features->n_cols > 0 && features->cols == nullptr)) {
     set_error("bad feature table / row count");
     return DQ4ML_ERR_INVALID;
@@ -249,6 +252,7 @@ int gather_inputs(dq4ml_ctx* ctx, const dq4ml_columns* features, const double* l
     out->dtype[j] = c.dtype;
   }
   out->label = label;
+  out->weight = weight;
   if (dq != nullptr) {
     if ((dq->guest == nullptr || dq->price == nullptr) && n > 0) {
       set_error("fused DQ needs both guest and price columns");
@@ -264,6 +268,7 @@ int gather_inputs(dq4ml_ctx* ctx, const dq4ml_columns* features, const double* l
     const void* dummy = ctx->scratch.consts;
     for (int j = 0; j < d; ++j) out->ptr[j] = dummy;
     out->label = static_cast<const double*>(dummy);
+    if (weight != nullptr) out->weight = static_cast<const double*>(dummy);
     if (dq != nullptr) {
       out->dq.guest = static_cast<const int32_t*>(dummy);
       out->dq.price = static_cast<const double*>(dummy);
@@ -273,6 +278,7 @@ int gather_inputs(dq4ml_ctx* ctx, const dq4ml_columns* features, const double* l
     Resolver rs(ctx);
     for (int j = 0; j < d; ++j) rs.input(&out->ptr[j], static_cast<size_t>(n) * (out->dtype[j] == DQ4ML_I32 ? 4 : 8));
     rs.input(reinterpret_cast<const void**>(&out->label), static_cast<size_t>(n) * 8);
+    rs.input(reinterpret_cast<const void**>(&out->weight), static_cast<size_t>(n) * 8);
     rs.input(reinterpret_cast<const void**>(&out->dq.guest), static_cast<size_t>(n) * 4);
     rs.input(reinterpret_cast<const void**>(&out->dq.price), static_cast<size_t>(n) * 8);
     rs.reserve_output(out_bytes);
@@ -283,6 +289,16 @@ int gather_inputs(dq4ml_ctx* ctx, const dq4ml_columns* features, const double* l
   for (int j = 0; j < out->cols.n; ++j) {
     out->cols.ptr[j] = out->ptr[j];
     out->cols.dtype[j] = out->dtype[j];
+  }
+  out->wcols.n = 0;
+  if (out->weight != nullptr && d + 1 <= kMaxCols) {
+    out->wcols.n = d + 1;
+    out->wcols.ptr[0] = out->weight;
+    out->wcols.dtype[0] = DQ4ML_F64;
+    for (int j = 0; j < d; ++j) {
+      out->wcols.ptr[1 + j] = out->ptr[j];
+      out->wcols.dtype[1 + j] = out->dtype[j];
+    }
   }
   return DQ4ML_OK;
 }
@@ -341,8 +357,68 @@ int wls_moments_any(dq4ml_ctx* ctx, const PassInputs& in, int64_t n, double* out
     set_error("label column is required");
     return DQ4ML_ERR_INVALID;
   }
-  if (in.width() <= 8) return wls_moments_small(ctx, in, n, out);
-  return gram_wls_moments(ctx, in.ptr, in.dtype, in.label, in.dq, n, out);
+  if (in.width() <= 8 && in.weight == nullptr) return wls_moments_small(ctx, in, n, out);
+  const int rc = gram_wls_moments(ctx, in.ptr, in.dtype, in.label, in.weight, in.dq, n, out);
+  // WeightedLeastSquares.Aggregator.add: require(w >= 0.0).  A negative weight turns sqrt(w) into NaN in wSum.
+  if (rc == DQ4ML_OK && in.weight != nullptr && !(out[1] == out[1])) {
+    set_error("instance weight must be >= 0 and not NaN");
+    return DQ4ML_ERR_INVALID;
+  }
+  return rc;
+}
+
+int weighted_width_check(const PassInputs& in) {
+  if (in.weight != nullptr && in.wcols.n == 0) {
+    set_error("weightCol with the l-bfgs branch handles at most %d feature columns (got %d)", kMaxCols - 1, in.width());
+    return DQ4ML_ERR_UNSUPPORTED;
+  }
+  return DQ4ML_OK;
+}
+
+// Weighted summarizer for the l-bfgs branch: count (rows with w != 0), weighted mean and the unbiased weighted variance
+// MultivariateOnlineSummarizer.variance returns, sum(w (v - mean)^2) / (W - sum(w^2) / W).
+int summarize_core_weighted(dq4ml_ctx* ctx, const PassInputs& in, int64_t n, ColumnStats* st) {
+  int rc = weighted_width_check(in);
+  if (rc != DQ4ML_OK) return rc;
+  const int d = in.width();
+  st->mean.assign(d + 1, 0.0);
+  st->variance.assign(d + 1, 0.0);
+  const int b = stream_bucket(d + 1);
+  cudaError_t e = launch_column_heads(in.wcols, in.label, b, n, ctx->scratch, ctx->stream, &ctx->launches);
+  if (e != cudaSuccess) return cuda_fail(e, "column heads");
+  std::vector<double> centres(b + 1, 0.0);
+  CU(cudaMemcpyAsync(ctx->h_result, ctx->scratch.consts, sizeof(double) * (b + 1), cudaMemcpyDeviceToHost, ctx->stream));
+  CU(cudaStreamSynchronize(ctx->stream));
+  std::copy(ctx->h_result, ctx->h_result + b + 1, centres.begin());
+  if (multi_rank(ctx)) {
+    rc = host_allreduce(ctx, centres.data(), b + 1);
+    if (rc != DQ4ML_OK) return rc;
+    for (double& c : centres) c /= ctx->world > 0 ? ctx->world : 1;
+    CU(cudaMemcpyAsync(ctx->scratch.consts, centres.data(), sizeof(double) * (b + 1), cudaMemcpyHostToDevice, ctx->stream));
+  }
+  e = timed_stream_pass(ctx, kOpSummCoreW, in.wcols, in.label, in.dq, n, nullptr, nullptr);
+  if (e != cudaSuccess) return cuda_fail(e, "weighted summarizer pass");
+  rc = finish_result(ctx, stream_nacc(kOpSummCoreW, b));
+  if (rc != DQ4ML_OK) return rc;
+  const double* r = ctx->h_result;
+  const double w_sum = r[1], ww_sum = r[2];
+  if (!(w_sum == w_sum) || w_sum < 0.0) {
+    set_error("instance weight must be >= 0 and not NaN");
+    return DQ4ML_ERR_INVALID;
+  }
+  st->count = r[0];
+  const double denom = w_sum > 0.0 ? w_sum - ww_sum / w_sum : 0.0;
+  auto read_out = [&](int slot, int out) {
+    const double s1 = r[1 + 2 * slot], s2 = r[2 + 2 * slot];
+    if (w_sum > 0.0) {
+      st->mean[out] = centres[slot] + s1 / w_sum;
+      const double m2n = s2 - s1 * s1 / w_sum;
+      st->variance[out] = denom > 0.0 ? std::max(m2n / denom, 0.0) : 0.0;
+    }
+  };
+  for (int c = 0; c < d; ++c) read_out(1 + c, c);
+  read_out(b, d);
+  return DQ4ML_OK;
 }
 
 // Summarizer, core statistics (count, mean, sample variance per column; label last) for the l-bfgs branch.
@@ -409,6 +485,28 @@ int lsq_pass(dq4ml_ctx* ctx, const PassInputs& in, int64_t n, const double* coef
              const double* fmean, double ystd, double ymean, bool fit_intercept, double* loss_sum, double* weight_sum,
              double* grad_sum, double* diff_scratch = nullptr) {
   const int d = in.width();
+  if (in.weight != nullptr) {  // weight in column 0, features in 1..d
+    int rc = weighted_width_check(in);
+    if (rc != DQ4ML_OK) return rc;
+    const int b = stream_bucket(d + 1);
+    LsqConsts c{};
+    double s = 0.0;
+    for (int j = 0; j < d; ++j) {
+      c.eff[1 + j] = fstd[j] != 0.0 ? coef[j] / fstd[j] : 0.0;
+      s += c.eff[1 + j] * fmean[j];
+    }
+    c.offset = fit_intercept ? ymean / ystd - s : 0.0;
+    c.inv_ystd = 1.0 / ystd;
+    cudaError_t e = timed_stream_pass(ctx, kOpLsqW, in.wcols, in.label, in.dq, n, &c, nullptr);
+    if (e != cudaSuccess) return cuda_fail(e, "weighted loss/gradient pass");
+    rc = finish_result(ctx, stream_nacc(kOpLsqW, b));
+    if (rc != DQ4ML_OK) return rc;
+    const double* r = ctx->h_result;
+    *loss_sum = r[0];
+    *weight_sum = r[1];
+    for (int j = 0; j < d; ++j) grad_sum[j] = fstd[j] != 0.0 ? r[3 + j] / fstd[j] : 0.0;
+    return DQ4ML_OK;
+  }
   if (d > kMaxCols) {
     // Wide table: pass 1 writes the scaled difference r = y/yStd - (x.eff + offset) per row (and its sums), pass 2 takes
     // gradSum_j = -sum r x_j over column groups.  The table is read twice; Spark reads it once, but keeps it in host RAM.
@@ -1005,6 +1103,11 @@ int dq4ml_lsq_loss_grad(dq4ml_ctx* ctx, const dq4ml_columns* features, const dou
 
 int dq4ml_linreg_fit(dq4ml_ctx* ctx, const dq4ml_columns* features, const double* label, int64_t n,
                      const dq4ml_lr_params* params, const dq4ml_dq_fused* dq, dq4ml_lr_model** out) {
+  return dq4ml_linreg_fit_weighted(ctx, features, label, nullptr, n, params, dq, out);
+}
+
+int dq4ml_linreg_fit_weighted(dq4ml_ctx* ctx, const dq4ml_columns* features, const double* label, const double* weight,
+                              int64_t n, const dq4ml_lr_params* params, const dq4ml_dq_fused* dq, dq4ml_lr_model** out) {
   if (check_ctx(ctx) != DQ4ML_OK) return DQ4ML_ERR_INVALID;
   if (out == nullptr || (label == nullptr && n > 0) || features == nullptr) {
     set_error("linreg_fit: null argument");
@@ -1021,7 +1124,7 @@ int dq4ml_linreg_fit(dq4ml_ctx* ctx, const dq4ml_columns* features, const double
   const bool wls = p.solver == DQ4ML_SOLVER_NORMAL || (p.solver == DQ4ML_SOLVER_AUTO && d <= 4096);
   PassInputs in;
   const bool wide_lbfgs = !wls && d > kMaxCols;  // needs one scratch column for the per-row scaled difference
-  int rc = gather_inputs(ctx, features, label, n, dq, &in, wide_lbfgs ? static_cast<size_t>(n) * 8 : 0, 1 << 20);
+  int rc = gather_inputs(ctx, features, label, n, dq, &in, wide_lbfgs ? static_cast<size_t>(n) * 8 : 0, 1 << 20, weight);
   if (rc != DQ4ML_OK) return rc;
   double* diff = wide_lbfgs ? static_cast<double*>(arena_take(ctx, static_cast<size_t>(n) * 8)) : nullptr;
   try {
@@ -1033,7 +1136,7 @@ int dq4ml_linreg_fit(dq4ml_ctx* ctx, const dq4ml_columns* features, const double
       model->m = wls_fit_from_moments(mom.data(), d, p);
     } else {
       ColumnStats st;
-      rc = summarize_core(ctx, in, n, &st);
+      rc = in.weight != nullptr ? summarize_core_weighted(ctx, in, n, &st) : summarize_core(ctx, in, n, &st);
       if (rc != DQ4ML_OK) return rc;
       int pass_rc = DQ4ML_OK;
       LsqPassFn pass = [&](const Vec& coef, const Vec& fstd, const Vec& fmean, double ystd, double ymean,
@@ -1235,6 +1338,37 @@ int dq4ml_linreg_evaluate(dq4ml_ctx* ctx, const dq4ml_lr_model* m, const dq4ml_c
   metrics[13] = cnt > 0 ? s[8] : 0.0;
   metrics[14] = sr;
   metrics[15] = sry;
+  return DQ4ML_OK;
+}
+
+int dq4ml_weighted_residual_stats(dq4ml_ctx* ctx, const double* residuals, const double* weight, int64_t n,
+                                  const dq4ml_dq_fused* dq, double* out3) {
+  if (check_ctx(ctx) != DQ4ML_OK) return DQ4ML_ERR_INVALID;
+  if (out3 == nullptr || ((residuals == nullptr || weight == nullptr) && n > 0)) {
+    set_error("weighted_residual_stats: null argument");
+    return DQ4ML_ERR_INVALID;
+  }
+  CallScope scope(ctx);
+  dq4ml_column col{residuals, DQ4ML_F64};
+  dq4ml_columns table{&col, 1};
+  PassInputs in;
+  int rc = gather_inputs(ctx, &table, nullptr, n, dq, &in, 0, 1, weight);
+  if (rc != DQ4ML_OK) return rc;
+  cudaError_t e = launch_stream_pass(kOpWResid, in.wcols, nullptr, in.dq, n, nullptr, nullptr, ctx->scratch, ctx->stream,
+                                     &ctx->launches);
+  if (e != cudaSuccess) return cuda_fail(e, "weighted residual pass");
+  rc = finish_result(ctx, 3, false);
+  if (rc != DQ4ML_OK) return rc;
+  // the cross-rank fold reuses the evaluate path: slots 0..6 are sums, 7 / 8 the min / max
+  double s[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+  s[0] = ctx->h_result[0];
+  s[7] = ctx->h_result[1];
+  s[8] = ctx->h_result[2];
+  rc = reduce_eval_sums(ctx, s);
+  if (rc != DQ4ML_OK) return rc;
+  out3[0] = s[0];
+  out3[1] = s[7];
+  out3[2] = s[8];
   return DQ4ML_OK;
 }
 

@@ -46,7 +46,8 @@ constexpr int GPART = GT * GT + GT * 8 + 64;  // doubles per CTA partial: tile, 
 struct __align__(16) GramStage {
   double a[GT][GKC];       // column block bi
   double b[GT][GKC];       // column block bj (unused on diagonal pairs)
-  double border[8][GKC];   // column 0 = y, column 1 = ones/keep mask, 2..7 stay zero
+  double border[8][GKC];   // column 0 = sqrt(w) y, 1 = sqrt(w) keep, 2 = w keep, 3 = keep (w = 1 unweighted); 4..7 stay zero
+  double wt[GKC];          // weight chunk, replaced by sqrt(w) * keep during the fix-up (weighted fits only)
   double dqp[GKC];         // DQ price chunk
   int dqg[GKC];            // DQ guest chunk
 };
@@ -61,6 +62,7 @@ struct GramArgs {
   const unsigned char* col_i32;  // device array [d]: 1 = int32 column
   int d, nb, kinds, splits;
   const double* label;
+  const double* weight;  // instance weights (weightCol), nullptr = all 1
   const int* dq_guest;
   const double* dq_price;
   DqThresholds t;
@@ -163,6 +165,7 @@ __global__ void __launch_bounds__(GTHREADS, 2) gram_tile_kernel(const GramArgs g
       if (tid >= 32 && tid < 48) cp_async16(&S.dqp[(tid - 32) * 2], g.dq_price + row + (tid - 32) * 2);
       if (tid >= 64 && tid < 72) cp_async16(&S.dqg[(tid - 64) * 4], g.dq_guest + row + (tid - 64) * 4);
     }
+    if (g.weight != nullptr && tid >= 96 && tid < 112) cp_async16(&S.wt[(tid - 96) * 2], g.weight + row + (tid - 96) * 2);
   };
 
   const int wm = warp >> 1, wn = warp & 1;
@@ -190,7 +193,16 @@ __global__ void __launch_bounds__(GTHREADS, 2) gram_tile_kernel(const GramArgs g
       if (keep && g.has_dq) keep = dq_keep(S.dqg[lane], S.dqp[lane], g.t);
       const unsigned m = __ballot_sync(0xffffffffu, keep);
       if (lane == 0) *mask_slot = static_cast<int>(m);
-      if (diag) S.border[1][swz(1, lane)] = keep ? 1.0 : 0.0;
+      // WeightedLeastSquares.Aggregator: wSum += w, wwSum += w^2, bSum += w y, aSum += w x, aaSum += w x x^T.  Every row of
+      // the chunk is scaled by sqrt(w) below, so Z^T Z carries the weights; count and wwSum ride in two more border columns.
+      const double w = keep ? (g.weight != nullptr ? S.wt[lane] : 1.0) : 0.0;
+      const double sw = g.weight != nullptr ? sqrt(w) : w;  // w is 0 or 1 without a weight column
+      if (g.weight != nullptr) S.wt[lane] = sw;
+      if (diag) {
+        S.border[1][swz(1, lane)] = sw;
+        S.border[2][swz(2, lane)] = w;
+        S.border[3][swz(3, lane)] = keep ? 1.0 : 0.0;
+      }
     }
     __syncthreads();
     const unsigned dropped = ~static_cast<unsigned>(*mask_slot);
@@ -201,6 +213,20 @@ __global__ void __launch_bounds__(GTHREADS, 2) gram_tile_kernel(const GramArgs g
         else if (!diag) S.b[tid - GT][swz(tid - GT, r)] = 0.0;
         if (diag && tid == GT) S.border[0][swz(0, r)] = 0.0;
       }
+      __syncthreads();
+    }
+    if (g.weight != nullptr) {  // scale every row of both panels and of y by sqrt(w): the same 16-byte pieces this thread staged
+      const int pch = tid & 15, slot_base = tid >> 4;
+      const int lch = pch ^ ((slot_base & 7) << 1);  // logical chunk held at physical position pch: rows 2 lch, 2 lch + 1
+      const double s0 = S.wt[2 * lch], s1 = S.wt[2 * lch + 1];
+      for (int slot = slot_base; slot < n_slots; slot += 8) {
+        double2* q = reinterpret_cast<double2*>((slot < GT ? S.a[slot] : S.b[slot - GT]) + 2 * pch);
+        double2 v = *q;
+        v.x *= s0;
+        v.y *= s1;
+        *q = v;
+      }
+      if (diag && tid < GKC) S.border[0][swz(0, tid)] *= S.wt[tid];
       __syncthreads();
     }
     const double(*A)[GKC] = S.a;
@@ -266,6 +292,7 @@ __global__ void __launch_bounds__(GTHREADS, 2) gram_tile_kernel(const GramArgs g
       S.border[0][swz(0, tid)] = (diag && tid < tail_rows) ? g.label[row0 + tid] : 0.0;
       S.dqg[tid] = (g.has_dq && tid < tail_rows) ? g.dq_guest[row0 + tid] : 0;
       S.dqp[tid] = (g.has_dq && tid < tail_rows) ? g.dq_price[row0 + tid] : 0.0;
+      if (g.weight != nullptr) S.wt[tid] = tid < tail_rows ? g.weight[row0 + tid] : 0.0;
     }
     __syncthreads();
     consume(S, &s_meta[4], false, tail_rows);
@@ -299,7 +326,8 @@ __global__ void __launch_bounds__(256) gram_reduce_kernel(const double* __restri
   int bi, bj, off;
   if (e < 5) {
     bi = bj = 0;
-    off = GT * GT + GT * 8 + (e < 3 ? 1 * 8 + 1 : (e == 3 ? 0 * 8 + 1 : 0));  // corner: [1][1] = count, [0][1] = sum y, [0][0] = sum y^2
+    // corner = [sqrt(w) y, sqrt(w), w, keep]^T [same]: [3][3] = count, [1][1] = wSum, [2][2] = wwSum, [0][1] = bSum, [0][0] = bbSum
+    off = GT * GT + GT * 8 + (e == 0 ? 3 * 8 + 3 : (e == 1 ? 1 * 8 + 1 : (e == 2 ? 2 * 8 + 2 : (e == 3 ? 0 * 8 + 1 : 0))));
   } else if (e < 5 + 2LL * d) {
     const int j = static_cast<int>((e - 5) % d);
     const bool ab = (e - 5) >= d;
@@ -324,7 +352,7 @@ __global__ void __launch_bounds__(256) gram_reduce_kernel(const double* __restri
 }  // namespace
 
 int gram_wls_moments(dq4ml_ctx* ctx, const std::vector<const void*>& col_ptrs, const std::vector<int>& dtypes,
-                     const double* label, const DeviceDq& dq, int64_t n, double* out) {
+                     const double* label, const double* weight, const DeviceDq& dq, int64_t n, double* out) {
   const int d = static_cast<int>(col_ptrs.size());
   const int nb = (d + GT - 1) / GT;
   const int kinds = nb * (nb + 1) / 2;
@@ -377,6 +405,7 @@ int gram_wls_moments(dq4ml_ctx* ctx, const std::vector<const void*>& col_ptrs, c
   g.kinds = kinds;
   g.splits = static_cast<int>(splits);
   g.label = label;
+  g.weight = weight;
   g.dq_guest = dq.guest;
   g.dq_price = dq.price;
   g.t.min_price = dq.params.min_price;

@@ -35,7 +35,11 @@ struct Scratch {
   int sm_count;
 };
 
-enum StreamOpKind { kOpWls = 0, kOpLsq = 1, kOpSummCore = 2, kOpSummFull = 3, kOpEval = 4, kOpGrad = 5 };
+enum StreamOpKind {
+  kOpWls = 0, kOpLsq = 1, kOpSummCore = 2, kOpSummFull = 3, kOpEval = 4, kOpGrad = 5,
+  // weighted variants: column 0 of the table is the instance weight, the features follow (so at most kMaxCols - 1 of them)
+  kOpSummCoreW = 6, kOpLsqW = 7, kOpWResid = 8
+};
 
 struct LsqConsts {
   double eff[kMaxCols];

@@ -148,6 +148,96 @@ struct GradOp {
   }
 };
 
+// ---- instance weights (LinearRegression.setWeightCol) ---------------------------------------------------------------
+// The weighted ops take the weight as column 0 of the table and the features as columns 1..d, so that the weight rides
+// the same vector loads as everything else and the unweighted kernels keep their register budget.  x[0] arrives as 0
+// for dropped rows, which removes them from every weighted sum.
+
+// MultivariateOnlineSummarizer.add(sample, weight): a zero-weight row is skipped entirely (not even counted); mean =
+// sum(w v) / W and variance = sum(w (v - mean)^2) / (W - sum(w^2) / W), read out on the host from the shifted sums.
+// acc: count, W, sum w^2, then (S1, S2) for feature columns 1..DMAX-1, then for the label.  Centres: slot j of the
+// table, label at slot DMAX (slot 0, the weight's own head mean, is unused).
+template <int DMAX>
+struct SummCoreWOp {
+  static constexpr int NACC = 3 + 2 * DMAX;
+  static constexpr int NCONST = DMAX + 1;
+  static constexpr bool HAS_OUT = false;
+  __host__ __device__ static constexpr double identity(int) { return 0.0; }
+  __host__ __device__ static constexpr int kind(int) { return kSum; }
+
+  __device__ __forceinline__ double row(double (&acc)[NACC], const double* c, const double (&x)[DMAX], double y,
+                                        bool keep, int) const {
+    const double w = x[0];
+    const bool on = keep && w != 0.0;
+    acc[0] += on ? 1.0 : 0.0;
+    acc[1] += w >= 0.0 ? w : __longlong_as_double(0x7ff8000000000000LL);  // require(weight >= 0.0): a bad weight poisons W
+    acc[2] = fma(w, w, acc[2]);
+#pragma unroll
+    for (int j = 1; j < DMAX; ++j) {
+      const double t = on ? x[j] - c[j] : 0.0;
+      const double wt = w * t;
+      acc[1 + 2 * j] += wt;
+      acc[2 + 2 * j] = fma(wt, t, acc[2 + 2 * j]);
+    }
+    const double t = on ? y - c[DMAX] : 0.0;
+    const double wt = w * t;
+    acc[1 + 2 * DMAX] += wt;
+    acc[2 + 2 * DMAX] = fma(wt, t, acc[2 + 2 * DMAX]);
+    return 0.0;
+  }
+};
+
+// LeastSquaresAggregator.add with weights: lossSum += w diff^2 / 2, weightSum += w, gradSum_j += w diff x_j (eff[0] is
+// 0 so the weight column stays out of the margin; accumulator 2 is unused).
+template <int DMAX>
+struct LsqWOp {
+  static constexpr int NACC = 2 + DMAX;
+  static constexpr int NCONST = 0;
+  static constexpr bool HAS_OUT = false;
+  double eff[DMAX];
+  double offset;
+  double inv_ystd;
+  __host__ __device__ static constexpr double identity(int) { return 0.0; }
+  __host__ __device__ static constexpr int kind(int) { return kSum; }
+
+  __device__ __forceinline__ double row(double (&acc)[NACC], const double*, const double (&x)[DMAX], double y,
+                                        bool keep, int) const {
+    double dotp = 0.0;
+#pragma unroll
+    for (int j = 1; j < DMAX; ++j) dotp = fma(x[j], eff[j], dotp);
+    double diff = dotp - y * inv_ystd + offset;
+    diff = keep ? diff : 0.0;
+    const double wd = x[0] * diff;
+    acc[0] = fma(0.5 * wd, diff, acc[0]);
+    acc[1] += x[0];
+#pragma unroll
+    for (int j = 1; j < DMAX; ++j) acc[2 + j] = fma(wd, x[j], acc[2 + j]);
+    return 0.0;
+  }
+};
+
+// LinearRegressionSummary under a weight column: coefficientStandardErrors take rss = sum(w (label - prediction)^2) and
+// devianceResiduals the extremes of sqrt(w) (label - prediction).  Table: column 0 = weight, column 1 = residual.
+template <int DMAX>
+struct WResidOp {
+  static constexpr int NACC = 3;
+  static constexpr int NCONST = 0;
+  static constexpr bool HAS_OUT = false;
+  __host__ __device__ static constexpr int kind(int k) { return k == 1 ? kMin : (k == 2 ? kMax : kSum); }
+  __host__ __device__ static constexpr double identity(int k) {
+    return k == 1 ? __builtin_huge_val() : (k == 2 ? -__builtin_huge_val() : 0.0);
+  }
+  __device__ __forceinline__ double row(double (&acc)[NACC], const double*, const double (&x)[DMAX], double, bool keep,
+                                        int) const {
+    const double w = x[0], r = DMAX > 1 ? x[DMAX > 1 ? 1 : 0] : 0.0;
+    acc[0] = fma(w * r, r, acc[0]);
+    const double s = sqrt(w) * r;
+    acc[1] = combine(kMin, acc[1], keep ? s : __builtin_huge_val());
+    acc[2] = combine(kMax, acc[2], keep ? s : -__builtin_huge_val());
+    return 0.0;
+  }
+};
+
 // LinearRegressionModel.transform + RegressionMetrics / LinearRegressionSummary sums in one pass: yhat = x.beta + b;
 // residual r = y - yhat; accumulators n, sum r^2, sum y, sum y^2, sum |r|, sum r, sum r*y, min r, max r (the last four
 // feed explainedVariance and devianceResiduals).  Per-row output: prediction (mode 0) or residual (mode 1).

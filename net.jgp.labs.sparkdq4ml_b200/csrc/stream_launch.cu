@@ -25,6 +25,9 @@ int stream_nacc(StreamOpKind op, int bucket) {
     case kOpSummFull: return 1 + 7 * bucket;
     case kOpEval: return 9;
     case kOpGrad: return bucket;
+    case kOpSummCoreW: return 3 + 2 * bucket;
+    case kOpLsqW: return 2 + bucket;
+    case kOpWResid: return 3;
   }
   return 0;
 }
@@ -90,9 +93,16 @@ cudaError_t launch_mode(const Op& op, const PassArgs& a) {
   }
 }
 
-template <int DMAX>
-LsqOp<DMAX> make_lsq(const LsqConsts& c) {
-  LsqOp<DMAX> op;
+// the weighted ops never see the lab layout (column 0 is the weight), so two DQ modes are enough
+template <class Op, int DMAX, int ROWS>
+cudaError_t launch_mode2(const Op& op, const PassArgs& a) {
+  if (a.dq_mode == kDqNone) return launch_one<Op, DMAX, ROWS, kDqNone>(op, a);
+  return launch_one<Op, DMAX, ROWS, kDqSeparate>(op, a);
+}
+
+template <class L, int DMAX>
+L make_lsq(const LsqConsts& c) {
+  L op;
   for (int j = 0; j < DMAX; ++j) op.eff[j] = c.eff[j];
   op.offset = c.offset;
   op.inv_ystd = c.inv_ystd;
@@ -116,13 +126,22 @@ cudaError_t launch_bucket(StreamOpKind kind, const PassArgs& a, const void* host
     case kOpWls:
       if constexpr (DMAX <= 8) return launch_mode<WlsOp<DMAX>, DMAX, ROWS>(WlsOp<DMAX>{}, a);
       return cudaErrorInvalidValue;
-    case kOpLsq: return launch_mode<LsqOp<DMAX>, DMAX, ROWS>(make_lsq<DMAX>(*static_cast<const LsqConsts*>(host_consts)), a);
+    case kOpLsq: return launch_mode<LsqOp<DMAX>, DMAX, ROWS>(make_lsq<LsqOp<DMAX>, DMAX>(*static_cast<const LsqConsts*>(host_consts)), a);
     case kOpSummCore: return launch_mode<SummCoreOp<DMAX>, DMAX, ROWS>(SummCoreOp<DMAX>{}, a);
     case kOpSummFull:
       if constexpr (DMAX <= 4) return launch_mode<SummFullOp<DMAX>, DMAX, ROWS>(SummFullOp<DMAX>{}, a);
       return cudaErrorInvalidValue;
     case kOpEval: return launch_mode<EvalOp<DMAX>, DMAX, ROWS>(make_eval<DMAX>(*static_cast<const EvalConsts*>(host_consts)), a);
     case kOpGrad: return launch_one<GradOp<DMAX>, DMAX, ROWS, kDqNone>(GradOp<DMAX>{}, a);
+    case kOpSummCoreW:
+      if constexpr (DMAX >= 2) return launch_mode2<SummCoreWOp<DMAX>, DMAX, ROWS>(SummCoreWOp<DMAX>{}, a);
+      return cudaErrorInvalidValue;
+    case kOpLsqW:
+      if constexpr (DMAX >= 2) return launch_mode2<LsqWOp<DMAX>, DMAX, ROWS>(make_lsq<LsqWOp<DMAX>, DMAX>(*static_cast<const LsqConsts*>(host_consts)), a);
+      return cudaErrorInvalidValue;
+    case kOpWResid:
+      if constexpr (DMAX == 2) return launch_mode2<WResidOp<DMAX>, DMAX, ROWS>(WResidOp<DMAX>{}, a);
+      return cudaErrorInvalidValue;
   }
   return cudaErrorInvalidValue;
 }
@@ -149,8 +168,8 @@ cudaError_t launch_stream_pass(StreamOpKind op, const DeviceCols& cols, const do
   a.dq.t.min_guest = dq.params.min_guest;
   if (dq.guest == nullptr) {
     a.dq_mode = kDqNone;
-  } else if (cols.n > 0 && cols.dtype[0] == DQ4ML_I32 && cols.ptr[0] == dq.guest && label != nullptr &&
-             label == dq.price) {
+  } else if (op < kOpSummCoreW && cols.n > 0 && cols.dtype[0] == DQ4ML_I32 && cols.ptr[0] == dq.guest &&
+             label != nullptr && label == dq.price) {
     a.dq_mode = kDqLab;
   } else {
     a.dq_mode = kDqSeparate;

@@ -102,6 +102,15 @@ class LinearRegression:
         self._max_iter, self._reg_param, self._elastic_net, self._tol = 100, 0.0, 0.0, 1e-6
         self._fit_intercept, self._standardization, self._solver = True, True, "auto"
         self._features_col, self._label_col, self._prediction_col = "features", "label", "prediction"
+        self._weight_col = None
+
+    def setWeightCol(self, v):
+        """Instance weights (Spark: unset / empty = every weight 1.0; the lab never sets it)."""
+        self._weight_col = v if v else None
+        return self
+
+    def getWeightCol(self):
+        return self._weight_col or ""
 
     def setMaxIter(self, v):
         self._max_iter = int(v)
@@ -172,8 +181,10 @@ class LinearRegression:
         dqs, keep2 = df._dq_struct()
         params = self._c_params()
         handle = C.c_void_p()
-        capi.check(capi.lib().dq4ml_linreg_fit(df.ctx.handle, C.byref(tab), capi.buf_ptr(label), df.n, C.byref(params),
-                                                C.byref(dqs) if dqs is not None else None, C.byref(handle)))
+        weight = df.columns[self._weight_col] if self._weight_col else None
+        capi.check(capi.lib().dq4ml_linreg_fit_weighted(df.ctx.handle, C.byref(tab), capi.buf_ptr(label),
+                                                         capi.buf_ptr(weight), df.n, C.byref(params),
+                                                         C.byref(dqs) if dqs is not None else None, C.byref(handle)))
         model = LinearRegressionModel(handle, self)
         model._training = df
         return model
@@ -272,6 +283,7 @@ class LinearRegressionSummary:
         self._model, self._df = model, df
         self._metrics = None
         self._residuals = None
+        self._weighted = None
         self._want_residuals = want_residuals
 
     def _run(self, with_residuals):
@@ -294,6 +306,24 @@ class LinearRegressionSummary:
         self._metrics = met
         if with_residuals:
             self._residuals = res
+
+    def _w(self):
+        """[sum w r^2, min sqrt(w) r, max sqrt(w) r] when the estimator has a weight column, else None.  Spark 2.4.4
+        keeps RegressionMetrics (rmse, r2, ...) unweighted; only the standard errors and devianceResiduals use weights."""
+        wc = self._model._est._weight_col
+        if not wc:
+            return None
+        if self._weighted is None:
+            df = self._df
+            res = self.residuals()
+            dqs, keep2 = df._dq_struct()
+            out = np.zeros(3, dtype=np.float64)
+            capi.check(capi.lib().dq4ml_weighted_residual_stats(df.ctx.handle, capi.buf_ptr(res),
+                                                                 capi.buf_ptr(df.columns[wc]), df.n,
+                                                                 C.byref(dqs) if dqs is not None else None,
+                                                                 out.ctypes.data))
+            self._weighted = out
+        return self._weighted
 
     def _m(self):
         if self._metrics is None:
@@ -332,9 +362,11 @@ class LinearRegressionSummary:
 
     def _inference(self):
         m = self._m()
+        w = self._w()
+        rss = float(m[1]) if w is None else float(w[0])
         k = self._model.numFeatures() + (1 if self._model._est._fit_intercept else 0)
         se, tv, pv = (np.zeros(k, dtype=np.float64) for _ in range(3))
-        capi.check(capi.lib().dq4ml_linreg_model_inference(self._model._h, float(m[0]), float(m[1]),
+        capi.check(capi.lib().dq4ml_linreg_model_inference(self._model._h, float(m[0]), rss,
                                                             int(self._model._est._fit_intercept), se.ctypes.data,
                                                             tv.ctypes.data, pv.ctypes.data, k))
         return se, tv, pv
@@ -350,7 +382,10 @@ class LinearRegressionSummary:
         return self._inference()[2]
 
     def devianceResiduals(self):
-        """[min, max] of the residuals (weights are 1), as Spark's LinearRegressionSummary.devianceResiduals."""
+        """[min, max] of sqrt(weight) * residual, as Spark's LinearRegressionSummary.devianceResiduals."""
+        w = self._w()
+        if w is not None:
+            return [float(w[1]), float(w[2])] if self.numInstances() > 0 else [0.0, 0.0]
         return [float(self._m()[12]), float(self._m()[13])]
 
 

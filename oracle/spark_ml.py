@@ -530,9 +530,73 @@ def wls_fit_from_moments(mom, d, p: LRParams, solver_type="auto"):
 
 # ----------------------------------------------------------------------------- LinearRegression.train, l-bfgs branch
 
-def lbfgs_path_fit(features, label, p: LRParams, dq=None, threads=1):
+# ---- instance weights (LinearRegression.setWeightCol): numpy restatements, small inputs only --------------------------
+# The lab never sets weightCol and Spark's sources are not under /root/reference (Maven dependency spark-mllib_2.11
+# 2.4.4): these follow the published algorithm of ml.optim.WeightedLeastSquares.Aggregator.add,
+# mllib.stat.MultivariateOnlineSummarizer.add(sample, weight) / .mean / .variance and
+# ml.optim.aggregator.LeastSquaresAggregator.add.  PARITY UNPINNED, like the rest of the oracle.
+
+def _dq_keep_mask(dq, n):
+    if dq is None:
+        return np.ones(n, dtype=bool)
+    g = np.asarray(dq[0], dtype=np.int32)
+    pr = np.asarray(dq[1], dtype=np.float64)
+    with np.errstate(invalid="ignore"):
+        return ~(pr < 20.0) & ~(pr <= 0.0) & ~((g < 14) & (pr > 90.0))
+
+
+def _weighted_table(features, label, weight, dq):
+    y = np.asarray(label, dtype=np.float64)
+    w = np.asarray(weight, dtype=np.float64)
+    if np.any(~(w >= 0.0)):
+        raise ValueError("instance weight must be >= 0")  # require(w >= 0.0) in Aggregator.add
+    keep = _dq_keep_mask(dq, y.size)
+    x = np.stack([np.asarray(f, dtype=np.float64)[keep] for f in features], axis=1) if len(features) else np.zeros((int(keep.sum()), 0))
+    return x, y[keep], w[keep]
+
+
+def wls_moments_weighted(features, label, weight, dq=None):
+    """WeightedLeastSquares.Aggregator.add over every kept row (zero-weight rows still count), public moment layout."""
+    x, y, w = _weighted_table(features, label, weight, dq)
+    d = x.shape[1]
+    aa = (x * w[:, None]).T @ x
+    packed = [aa[i, j] for j in range(d) for i in range(j + 1)]
+    return np.array([float(y.size), w.sum(), (w * w).sum(), (w * y).sum(), (w * y * y).sum()]
+                    + list((x * w[:, None]).sum(axis=0)) + list((x * (w * y)[:, None]).sum(axis=0)) + packed)
+
+
+def summarizer_weighted(features, label, weight, dq=None):
+    """MultivariateOnlineSummarizer with weights: rows with w == 0 are skipped; variance = sum w (v - mean)^2 /
+    (W - sum w^2 / W) when that denominator is positive, else 0."""
+    x, y, w = _weighted_table(features, label, weight, dq)
+    on = w != 0.0
+    x, y, w = x[on], y[on], w[on]
+    cols = np.concatenate([x, y[:, None]], axis=1)
+    w_sum, ww_sum = w.sum(), (w * w).sum()
+    mean = (cols * w[:, None]).sum(axis=0) / w_sum if w_sum > 0 else np.zeros(cols.shape[1])
+    denom = w_sum - ww_sum / w_sum if w_sum > 0 else 0.0
+    m2n = (w[:, None] * (cols - mean) ** 2).sum(axis=0)
+    var = np.maximum(m2n / denom, 0.0) if denom > 0 else np.zeros(cols.shape[1])
+    return {"count": float(w.size), "mean": mean, "variance": var, "weight_sum": w_sum}
+
+
+def lsq_loss_grad_weighted(features, label, weight, coef, fstd, fmean, ystd, ymean, fit_intercept=True, dq=None):
+    """LeastSquaresAggregator.add: diff = x.(c/sigma) - y/sigma_y + offset; lossSum += w diff^2/2; gradSum_j += w diff x_j/sigma_j."""
+    x, y, w = _weighted_table(features, label, weight, dq)
+    fstd = np.asarray(fstd, dtype=np.float64)
+    eff = np.where(fstd != 0.0, np.asarray(coef, dtype=np.float64) / np.where(fstd != 0.0, fstd, 1.0), 0.0)
+    offset = (ymean / ystd - float(eff @ np.asarray(fmean))) if fit_intercept else 0.0
+    diff = x @ eff - y / ystd + offset
+    grad = np.where(fstd != 0.0, ((w * diff)[:, None] * x).sum(axis=0) / np.where(fstd != 0.0, fstd, 1.0), 0.0)
+    return 0.5 * float((w * diff * diff).sum()), float(w.sum()), grad
+
+
+def lbfgs_path_fit(features, label, p: LRParams, dq=None, threads=1, weight=None):
     d = len(features)
-    summ = passes.summarizer(features, label, dq=dq, threads=threads)
+    if weight is None:
+        summ = passes.summarizer(features, label, dq=dq, threads=threads)
+    else:
+        summ = summarizer_weighted(features, label, weight, dq=dq)
     n_pass = 1
     y_mean = float(summ["mean"][d])
     raw_y_std = math.sqrt(float(summ["variance"][d]))
@@ -550,8 +614,12 @@ def lbfgs_path_fit(features, label, p: LRParams, dq=None, threads=1):
     evals = [0]
 
     def cost(c):
-        loss_sum, w_sum, grad_sum = passes.lsq_loss_grad(features, label, c, f_std, f_mean, y_std, y_mean,
-                                                         p.fit_intercept, dq=dq, threads=threads)
+        if weight is None:
+            loss_sum, w_sum, grad_sum = passes.lsq_loss_grad(features, label, c, f_std, f_mean, y_std, y_mean,
+                                                             p.fit_intercept, dq=dq, threads=threads)
+        else:
+            loss_sum, w_sum, grad_sum = lsq_loss_grad_weighted(features, label, weight, c, f_std, f_mean, y_std, y_mean,
+                                                               p.fit_intercept, dq=dq)
         evals[0] += 1
         loss = loss_sum / w_sum
         grad = grad_sum / w_sum
@@ -586,13 +654,16 @@ def lbfgs_path_fit(features, label, p: LRParams, dq=None, threads=1):
     return LRModel(raw, float(intercept), list(hist), len(hist), used, n_pass + n_eval)
 
 
-def linear_regression_fit(features, label, p: LRParams, dq=None, threads=1):
+def linear_regression_fit(features, label, p: LRParams, dq=None, threads=1, weight=None):
     """ml.regression.LinearRegression.train: solver selection (auto & d <= 4096 -> WLS, else l-bfgs)."""
     d = len(features)
     if (p.solver == "auto" and d <= 4096) or p.solver == "normal":
-        mom = passes.wls_moments(features, label, dq=dq, threads=threads)
+        if weight is None:
+            mom = passes.wls_moments(features, label, dq=dq, threads=threads)
+        else:
+            mom = wls_moments_weighted(features, label, weight, dq=dq)
         return wls_fit_from_moments(mom, d, p, "auto")
-    return lbfgs_path_fit(features, label, p, dq=dq, threads=threads)
+    return lbfgs_path_fit(features, label, p, dq=dq, threads=threads, weight=weight)
 
 
 def regression_metrics(metrics_out, fit_intercept=True):

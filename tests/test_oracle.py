@@ -141,3 +141,28 @@ def test_threaded_passes_agree_with_sequential_fold():
     keep = np.array([bool(passes.lib().orc_dq_keep(int(x), float(y))) for x, y in zip(guest, price)])
     assert rel_err(s1["mean"][-1], price[keep].mean()) < 1e-12
     assert rel_err(s1["variance"][1], extra[0][keep].var(ddof=1)) < 1e-11
+
+
+@pytest.mark.parametrize("solver,reg,en", [("normal", 0.0, 0.0), ("normal", 0.3, 0.5), ("l-bfgs", 0.0, 0.0)])
+def test_weighted_restatement_equals_replicated_rows(solver, reg, en):
+    """setWeightCol: integer weights must act like repeated rows -- exactly for the normal-equation
+    branch (population moments) and for the unregularised l-bfgs branch (the optimum does not depend on the scaling)."""
+    rng = np.random.default_rng(1)
+    n = 400
+    g = rng.integers(1, 40, n).astype(np.int32)
+    x2 = rng.normal(size=n)
+    y = 20 + 5 * g + 3 * x2 + rng.normal(size=n)
+    w = rng.integers(0, 4, n).astype(np.float64)
+    idx = np.repeat(np.arange(n), w.astype(np.int64))
+    p = spark_ml.LRParams(max_iter=100, reg_param=reg, elastic_net_param=en, tol=1e-10, fit_intercept=True,
+                          standardization=True, solver=solver)
+    mw = spark_ml.linear_regression_fit([g, x2], y, p, weight=w, dq=(g, y))
+    mr = spark_ml.linear_regression_fit([g[idx], x2[idx]], y[idx], p, dq=(g[idx], y[idx]))
+    np.testing.assert_allclose(mw.coefficients, mr.coefficients, rtol=2e-7)
+    assert abs(mw.intercept - mr.intercept) < 2e-6
+    s = spark_ml.summarizer_weighted([g, x2], y, w)
+    on = w != 0
+    assert s["count"] == on.sum()
+    np.testing.assert_allclose(s["mean"][2], np.average(y[on], weights=w[on]), rtol=1e-13)
+    with pytest.raises(ValueError):
+        spark_ml.wls_moments_weighted([g], y, -w - 1.0)
