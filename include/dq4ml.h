@@ -116,6 +116,17 @@ void* dq4ml_ctx_stream(dq4ml_ctx* ctx);
 /* Number of kernels this ctx has launched so far (bench.py's gpu_launches). */
 int64_t dq4ml_ctx_launch_count(dq4ml_ctx* ctx);
 
+/* Which kernel serves the normal-equation (WeightedLeastSquares.Aggregator) pass of lr.fit (App:126).  No counterpart
+ * in the reference (Spark always accumulates in fp64 on the CPU).
+ *   DQ4ML_GRAM_FP64   (default) fp64 throughout: streaming kernel for d <= 8, mma.sync DMMA Gram kernel above; 1e-9 parity.
+ *   DQ4ML_GRAM_TF32X3 tcgen05 tensor cores with accumulators in TMEM, for 1 <= d <= 256: centred values split into two
+ *                     TF32 parts (3 products per term), fp32 accumulation over spans of 1024 rows, fp64 across spans
+ *                     and for every column sum.  Tolerance of the tier: 1e-5 relative on coefficients / intercept.
+ *                     Wider tables fall back to the fp64 kernel. */
+#define DQ4ML_GRAM_FP64 0
+#define DQ4ML_GRAM_TF32X3 1
+int dq4ml_ctx_set_gram_tier(dq4ml_ctx* ctx, int tier);
+
 /* Measurement hook (no counterpart in the reference): when enabled, every aggregation-pass kernel (WLS moments,
  * summarizer, loss/gradient) is bracketed by CUDA events on the ctx stream; dq4ml_ctx_pass_timing returns the summed
  * kernel time and the number of passes since it was enabled. */

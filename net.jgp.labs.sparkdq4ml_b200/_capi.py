@@ -102,6 +102,7 @@ SIGNATURES = {
                                       C.c_void_p, C.c_void_p, C.c_double, C.c_double, C.c_int, C.c_void_p]),
     "dq4ml_linreg_fit": (C.c_int, [C.c_void_p, C.POINTER(Columns), C.c_void_p, C.c_int64, C.POINTER(LrParams),
                                    C.POINTER(DqFused), C.POINTER(C.c_void_p)]),
+    "dq4ml_ctx_set_gram_tier": (C.c_int, [C.c_void_p, C.c_int]),
     "dq4ml_linreg_fit_weighted": (C.c_int, [C.c_void_p, C.POINTER(Columns), C.c_void_p, C.c_void_p, C.c_int64,
                                             C.POINTER(LrParams), C.POINTER(DqFused), C.POINTER(C.c_void_p)]),
     "dq4ml_weighted_residual_stats": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.POINTER(DqFused),

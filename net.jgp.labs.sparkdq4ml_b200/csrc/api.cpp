@@ -357,8 +357,10 @@ int wls_moments_any(dq4ml_ctx* ctx, const PassInputs& in, int64_t n, double* out
     set_error("label column is required");
     return DQ4ML_ERR_INVALID;
   }
-  if (in.width() <= 8 && in.weight == nullptr) return wls_moments_small(ctx, in, n, out);
-  const int rc = gram_wls_moments(ctx, in.ptr, in.dtype, in.label, in.weight, in.dq, n, out);
+  const bool tf32 = ctx->gram_tier == DQ4ML_GRAM_TF32X3 && gram_tf32_supported(in.width()) && n > 0;
+  if (in.width() <= 8 && in.weight == nullptr && !tf32) return wls_moments_small(ctx, in, n, out);
+  const int rc = tf32 ? gram_tf32_wls_moments(ctx, in.ptr, in.dtype, in.label, in.weight, in.dq, n, out)
+                      : gram_wls_moments(ctx, in.ptr, in.dtype, in.label, in.weight, in.dq, n, out);
   // WeightedLeastSquares.Aggregator.add: require(w >= 0.0).  A negative weight turns sqrt(w) into NaN in wSum.
   if (rc == DQ4ML_OK && in.weight != nullptr && !(out[1] == out[1])) {
     set_error("instance weight must be >= 0 and not NaN");
@@ -719,6 +721,16 @@ int dq4ml_ctx_synchronize(dq4ml_ctx* ctx) {
 
 void* dq4ml_ctx_stream(dq4ml_ctx* ctx) { return ctx != nullptr ? ctx->stream : nullptr; }
 int64_t dq4ml_ctx_launch_count(dq4ml_ctx* ctx) { return ctx != nullptr ? ctx->launches : 0; }
+
+int dq4ml_ctx_set_gram_tier(dq4ml_ctx* ctx, int tier) {
+  if (check_ctx(ctx) != DQ4ML_OK) return DQ4ML_ERR_INVALID;
+  if (tier != DQ4ML_GRAM_FP64 && tier != DQ4ML_GRAM_TF32X3) {
+    set_error("unknown Gram tier %d", tier);
+    return DQ4ML_ERR_INVALID;
+  }
+  ctx->gram_tier = tier;
+  return DQ4ML_OK;
+}
 
 int dq4ml_ctx_enable_pass_timing(dq4ml_ctx* ctx, int enable) {
   if (check_ctx(ctx) != DQ4ML_OK) return DQ4ML_ERR_INVALID;

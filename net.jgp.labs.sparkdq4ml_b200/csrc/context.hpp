@@ -40,6 +40,7 @@ struct dq4ml_ctx {
   size_t gram_cap = 0;
   double* gram_host = nullptr;   // pinned copy of the packed result
   size_t gram_host_cap = 0;
+  int gram_tier = DQ4ML_GRAM_FP64;  // which kernel serves the normal-equation pass (dq4ml_ctx_set_gram_tier)
   int64_t launches = 0;
   // optional CUDA-event timing of the aggregation-pass kernels (bench.py's roofline leg)
   bool pass_timing = false;

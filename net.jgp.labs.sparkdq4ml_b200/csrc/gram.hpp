@@ -12,4 +12,10 @@ namespace dq4ml {
 int gram_wls_moments(dq4ml_ctx* ctx, const std::vector<const void*>& col_ptrs, const std::vector<int>& dtypes,
                      const double* label, const double* weight, const DeviceDq& dq, int64_t n, double* out);
 
+// The tcgen05 / TMEM tier of the same pass (gram_tf32_kernels.cu): 3xTF32 split products, fp32 accumulation in TMEM over
+// bounded row spans, fp64 across spans.  Same arguments and output layout; 1 <= d <= 256; relaxed tolerance (1e-5).
+bool gram_tf32_supported(int d);
+int gram_tf32_wls_moments(dq4ml_ctx* ctx, const std::vector<const void*>& col_ptrs, const std::vector<int>& dtypes,
+                          const double* label, const double* weight, const DeviceDq& dq, int64_t n, double* out);
+
 }  // namespace dq4ml

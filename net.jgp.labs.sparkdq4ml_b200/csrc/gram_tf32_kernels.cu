@@ -1,0 +1,642 @@
+// gram_tf32_kernels.cu -- the tensor-core tier of the normal-equation pass: Z^T Z on tcgen05 (5th-gen tensor cores,
+// accumulators in TMEM) with a 3xTF32 split, for 9 <= d <= 256 feature columns.
+//
+// What it computes is the same WeightedLeastSquares.Aggregator result as gram_kernels.cu (lr.fit, App:126, solver
+// normal/auto), at a relaxed tolerance: every centred, weighted value z = sqrt(w) (x - c) is split into hi = tf32(z)
+// and lo = tf32(z - hi); hi.hi + hi.lo + lo.hi reproduces the product to ~2^-21, fp32 accumulation happens in TMEM over
+// at most `drain_rows` rows and is then added into an fp64 tile in L2-resident scratch.  The centring (c = mean of the
+// column head) makes the tensor-core part carry covariances rather than raw second moments, so its rounding error is
+// relative to sigma_i sigma_j, which is what the regression needs; the raw moments are rebuilt in fp64 from the exact
+// column sums.  Stated tolerance of the tier: 1e-5 relative on coefficients / intercept (north_star: "1e-5 where fp32
+// accumulation is used and justified"); the fp64 DMMA kernel stays the default.
+//
+// Shape of the kernel (one persistent CTA per SM, 256 threads, all of TMEM):
+//   - rows are taken in chunks of 16; a 3-stage cp.async pipeline stages the raw fp64 / int32 column pieces;
+//   - thread t owns feature column t: it centres / weights / masks its 16 values, accumulates sum w(x-c) and
+//     sum w(x-c)y in fp64, and writes the hi and lo operands in the canonical no-swizzle K-major UMMA layout
+//     (8 x 16-byte core matrices);
+//   - one thread issues the MMAs of the chunk: per 8 rows and per split term, M128 x N256 for the feature block row 0
+//     (blocks (0,0) and (0,1)) and M128 x N128 for block (1,1); completion is tracked with tcgen05.commit -> mbarrier,
+//     which is also what frees the operand buffer for the conversion two chunks later;
+//   - every drain_rows rows the 128 x 384 fp32 accumulators are read with tcgen05.ld and added to the CTA's fp64 tile.
+// A second, small kernel pair folds the per-CTA tiles and rebuilds the public moment layout.
+#include <algorithm>
+#include <cstdio>
+#include <cstdlib>
+#include <vector>
+
+#include "context.hpp"
+#include "device_utils.cuh"
+#include "gram.hpp"
+
+namespace dq4ml {
+namespace {
+
+constexpr int TF = 256;                     // feature slots per CTA = threads per CTA
+constexpr int TKC = 16;                     // rows per chunk
+constexpr int TSTAGES = 4;                  // staging stages (raw columns)
+constexpr int TCONV = 512;                  // loader / converter threads: two per feature slot
+constexpr int TTHREADS = TCONV + 64;        // + the MMA warp + the row warp
+constexpr int TOPS = 2;                     // operand stages (hi/lo tf32)
+constexpr int TSTRIDE = TKC * 8 + 16;       // bytes per feature in a staging stage: +16 keeps 128-bit reads conflict-free
+constexpr int TLBO = 128;                   // bytes between the two 16-byte K chunks of one MMA (core matrix = 8 x 16 B)
+constexpr int TSBO = (TKC / 4) * 128;       // bytes between groups of 8 feature rows
+constexpr int TOPB = TF * TKC * 4;          // bytes of one operand buffer (hi or lo)
+constexpr int TROWB = 512;                  // per staging stage: y[16], dq price[16], weight[16], dq guest[16]
+constexpr int kStagingOff = 0;
+constexpr int kOpsOff = kStagingOff + TSTAGES * TF * TSTRIDE;
+constexpr int kRowsOff = kOpsOff + TOPS * 2 * TOPB;
+constexpr int kScaleOff = kRowsOff + TSTAGES * TROWB;  // s[16], s*y[16]
+constexpr int kBarOff = kScaleOff + 2 * (2 * TKC + 2) * 8;  // two sets of row factors (s[16], s*y[16], flag), then 7 mbarriers + the TMEM base address
+constexpr int kTf32Smem = kBarOff + 64;
+constexpr int SCOLS = 384;                  // fp64 tile columns per CTA: block (0,0) | (0,1) | (1,1)
+constexpr int kCtaDoubles = 128 * SCOLS + 2 * TF + 8;  // tile, sum w(x-c)[256], sum w(x-c)y[256], 5 scalars
+
+struct Tf32Args {
+  const void* const* col_ptr;
+  const unsigned char* col_i32;
+  const double* centres;  // [d]
+  int d;
+  const double* label;
+  const double* weight;
+  const int* dq_guest;
+  const double* dq_price;
+  DqThresholds t;
+  int has_dq;
+  long long n;
+  int drain_chunks;
+  int swap_offsets;  // debug: exchange LBO and SBO in the descriptors
+  int experiment;    // debug: bit 0 = converters skip the conversion, bit 1 = no MMAs are issued, bit 2 = no loads
+  double* partials;  // [grid][kCtaDoubles], zeroed by the launcher
+};
+
+__device__ __forceinline__ unsigned s_u32(const void* p) { return static_cast<unsigned>(__cvta_generic_to_shared(p)); }
+__device__ __forceinline__ void cpa16(unsigned dst, const void* src) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cpa_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cpa_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+__device__ __forceinline__ void mbar_init(unsigned bar, unsigned count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(unsigned bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned bar, unsigned parity) {
+  unsigned ok = 0;
+  for (unsigned spin = 0; ok == 0; ++spin) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(bar), "r"(parity)
+        : "memory");
+    if (spin > (1u << 24)) __trap();  // a lost completion must not hang the GPU
+  }
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_commit(unsigned bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void tc_mma_tf32(unsigned tmem_d, unsigned long long da, unsigned long long db, unsigned idesc,
+                                            unsigned accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\ttcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem_d),
+      "l"(da), "l"(db), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// 32 lanes x 32 consecutive fp32 columns: thread l receives lane (addr.lane + l), columns addr.col .. +31
+__device__ __forceinline__ void tc_ld32(unsigned taddr, unsigned (&r)[32]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,"
+      "%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]), "=r"(r[9]),
+        "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]), "=r"(r[17]), "=r"(r[18]),
+        "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]),
+        "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+      : "r"(taddr)
+      : "memory");
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+// Shared-memory matrix descriptor, K-major, no swizzle: 8-row x 16-byte core matrices; `lbo` = byte distance between the
+// two K chunks of one MMA, `sbo` = byte distance between 8-row groups (cute::UMMA::SmemDescriptor, version 1).
+__device__ __forceinline__ unsigned long long umma_desc(unsigned saddr, unsigned lbo, unsigned sbo) {
+  unsigned long long d = static_cast<unsigned long long>((saddr >> 4) & 0x3fffu);
+  d |= static_cast<unsigned long long>((lbo >> 4) & 0x3fffu) << 16;
+  d |= static_cast<unsigned long long>((sbo >> 4) & 0x3fffu) << 32;
+  d |= 1ull << 46;
+  return d;
+}
+// Instruction descriptor (cute::UMMA::InstrDescriptor): D fp32, A/B tf32, both K-major, M = 128.
+__host__ __device__ constexpr unsigned umma_idesc_tf32(int n) {
+  return (1u << 4) | (2u << 7) | (2u << 10) | (static_cast<unsigned>(n >> 3) << 17) | (static_cast<unsigned>(128 >> 4) << 24);
+}
+
+__device__ __forceinline__ float to_tf32(float f) {
+  unsigned b;
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(b) : "f"(f));
+  return __uint_as_float(b);
+}
+
+#define TICK(slot)                                   \
+  do {                                               \
+    if (prof) {                                      \
+      const long long now_ = clock64();              \
+      tacc[slot] += now_ - tlast;                    \
+      tlast = now_;                                  \
+    }                                                \
+  } while (0)
+
+__global__ void __launch_bounds__(TTHREADS, 1) gram_tf32_kernel(const Tf32Args g) {
+  const bool prof = (g.experiment & 8) != 0 && blockIdx.x == 0 && (threadIdx.x & 31) == 0;
+  long long tacc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  long long tlast = clock64();
+  extern __shared__ __align__(128) unsigned char smem[];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const unsigned sbase = s_u32(smem);
+  const unsigned bar_free0 = sbase + kBarOff, bar_ready0 = bar_free0 + 16, bar_scale0 = bar_free0 + 32, bar_drain = bar_free0 + 48;
+  unsigned* tmem_slot = reinterpret_cast<unsigned*>(smem + kBarOff + 56);
+  const int nb = g.d > 128 ? 2 : 1;
+
+  // operand buffers start as zeros: feature slots >= d are never written again
+  for (int i = tid; i < TOPS * 2 * TOPB / 16; i += TTHREADS) reinterpret_cast<int4*>(smem + kOpsOff)[i] = make_int4(0, 0, 0, 0);
+  if (tid == 0) {
+    mbar_init(bar_free0, 1);          // operand buffer o may be overwritten: arrived by tcgen05.commit
+    mbar_init(bar_free0 + 8, 1);
+    mbar_init(bar_ready0, TCONV / 32);  // operand buffer o is written: arrived once per converter warp
+    mbar_init(bar_ready0 + 8, TCONV / 32);
+    mbar_init(bar_scale0, 1);           // row factors of a chunk are written: arrived by the row warp
+    mbar_init(bar_scale0 + 8, 1);
+    mbar_init(bar_drain, 1);          // every MMA issued so far has completed
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 0) {  // all 512 TMEM columns: this kernel is alone on its SM (shared memory sees to that)
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(s_u32(tmem_slot)), "r"(512u) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // the zeros above, for the tensor core's reads
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const unsigned tmem = *tmem_slot;
+
+  const long long total_chunks = (g.n + TKC - 1) / TKC, full_chunks = g.n / TKC;
+  const long long my_iters =
+      total_chunks > blockIdx.x ? (total_chunks - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+  double* P = g.partials + static_cast<size_t>(blockIdx.x) * kCtaDoubles;
+
+  if (warp == TCONV / 32) {
+    // ================================================= MMA warp: one thread feeds the tensor core ====================
+    if (lane == 0) {
+      const unsigned lbo = g.swap_offsets ? TSBO : TLBO, sbo = g.swap_offsets ? TLBO : TSBO;
+      const unsigned idesc_row0 = umma_idesc_tf32(nb == 2 ? 256 : 128), idesc_blk = umma_idesc_tf32(128);
+      int since_drain = 0;
+      for (long long it = 0; it < my_iters; ++it) {
+        const int o = static_cast<int>(it & 1);
+        TICK(0);
+        mbar_wait(bar_ready0 + 8 * o, static_cast<unsigned>((it >> 1) & 1));
+        TICK(1);
+        tc_fence_after();
+        const unsigned hi = sbase + kOpsOff + o * (2 * TOPB), lo = hi + TOPB;
+#pragma unroll
+        for (int ks = 0; ks < ((g.experiment & 2) ? 0 : TKC / 8); ++ks) {
+          const unsigned koff = ks * 2 * TLBO;
+#pragma unroll
+          for (int term = 0; term < 3; ++term) {  // hi.hi, hi.lo, lo.hi
+            const unsigned a = (term == 2 ? lo : hi) + koff, b = (term == 1 ? lo : hi) + koff;
+            const unsigned acc = (since_drain == 0 && ks == 0 && term == 0) ? 0u : 1u;
+            tc_mma_tf32(tmem, umma_desc(a, lbo, sbo), umma_desc(b, lbo, sbo), idesc_row0, acc);
+            if (nb == 2)
+              tc_mma_tf32(tmem + 256, umma_desc(a + 16 * TSBO, lbo, sbo), umma_desc(b + 16 * TSBO, lbo, sbo), idesc_blk, acc);
+          }
+        }
+        tc_commit(bar_free0 + 8 * o);
+        if (++since_drain == g.drain_chunks || it == my_iters - 1) {
+          tc_commit(bar_drain);
+          since_drain = 0;
+        }
+        TICK(2);
+      }
+      if (prof) printf("mma thread: loop %lld wait_ready %lld issue+commit %lld (cycles, %lld chunks)\n", tacc[0], tacc[1], tacc[2], my_iters);
+    }
+  } else if (warp == TCONV / 32 + 1) {
+    // ================================================= row warp: keep mask, weight, label factors of every chunk ========
+    double cnt = 0.0, wsum = 0.0, wwsum = 0.0, bsum = 0.0, bbsum = 0.0;
+    for (long long it = 0; it < my_iters; ++it) {
+      TICK(0);
+      asm volatile("bar.sync 1, %0;" ::"n"(TCONV + 32) : "memory");  // chunk `it` has landed
+      TICK(1);
+      const int st = static_cast<int>(it % TSTAGES);
+      const unsigned char* rowb = smem + kRowsOff + st * TROWB;
+      double* scale = reinterpret_cast<double*>(smem + kScaleOff) + (it & 1) * (2 * TKC + 2);
+      bool plain = true;
+      if (lane < TKC) {
+        const long long row = (blockIdx.x + it * static_cast<long long>(gridDim.x)) * TKC + lane;
+        bool keep = row < g.n;
+        if (keep && g.has_dq)
+          keep = dq_keep(reinterpret_cast<const int*>(rowb + 384)[lane], reinterpret_cast<const double*>(rowb + 128)[lane], g.t);
+        const double w = keep ? (g.weight != nullptr ? reinterpret_cast<const double*>(rowb + 256)[lane] : 1.0) : 0.0;
+        const double s = g.weight != nullptr ? sqrt(w) : w;
+        const double y = keep ? reinterpret_cast<const double*>(rowb)[lane] : 0.0;
+        scale[lane] = s;
+        scale[TKC + lane] = keep ? s * y : 0.0;
+        plain = s == 1.0;
+        cnt += keep ? 1.0 : 0.0;
+        wsum += s * s;  // = w, and NaN for a negative weight (require(w >= 0))
+        wwsum = fma(w, w, wwsum);
+        bsum = fma(w, y, bsum);
+        bbsum = fma(w * y, y, bbsum);
+      }
+      const bool all_plain = __all_sync(0xffffffffu, plain);
+      if (lane == 0) reinterpret_cast<int*>(scale + 2 * TKC)[0] = all_plain ? 1 : 0;  // every factor is 1: the converters skip the scaling
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bar_scale0 + 8 * static_cast<unsigned>(it & 1));
+      TICK(2);
+    }
+    if (prof) printf("row warp: loop %lld barrier %lld work %lld\n", tacc[0], tacc[1], tacc[2]);
+#pragma unroll
+    for (int off = 8; off > 0; off >>= 1) {
+      cnt += __shfl_down_sync(0xffffffffu, cnt, off);
+      wsum += __shfl_down_sync(0xffffffffu, wsum, off);
+      wwsum += __shfl_down_sync(0xffffffffu, wwsum, off);
+      bsum += __shfl_down_sync(0xffffffffu, bsum, off);
+      bbsum += __shfl_down_sync(0xffffffffu, bbsum, off);
+    }
+    if (lane == 0) {
+      double* sc = P + 128 * SCOLS + 2 * TF;
+      sc[0] = cnt; sc[1] = wsum; sc[2] = wwsum; sc[3] = bsum; sc[4] = bbsum;
+    }
+  } else {
+    // ================================================= loader / converter warps ========================================
+    // converter: two threads per feature, 8 rows of every chunk each (lanes 0..15 / 16..31 of a warp share 16 features)
+    const int feat = warp * 16 + (lane & 15), half = lane >> 4;
+    const bool active = feat < g.d;
+    const bool own_int = active && g.col_i32[feat] != 0;
+    const double centre = active ? g.centres[feat] : 0.0;
+    // loader: 16-byte piece `ch` of the column slots (tid >> 3) + 64 i, so that 8 neighbouring threads fetch one 128-byte line
+    const int ch = tid & 7, slot0 = tid >> 3;
+    const char* src[4];
+    unsigned live = 0, ints = 0;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int slot = slot0 + 64 * i;
+      const bool on = slot < g.d;
+      const char* base = on ? static_cast<const char*>(g.col_ptr[slot]) : nullptr;
+      const bool is_int = on && g.col_i32[slot] != 0;
+      src[i] = base != nullptr ? base + ch * 16 : nullptr;
+      if (base != nullptr && (!is_int || ch < 4)) live |= 1u << i;
+      if (is_int) ints |= 1u << i;
+    }
+    const unsigned piece_dst = static_cast<unsigned>(slot0 * TSTRIDE + ch * 16);
+
+    auto issue_tail = [&](long long row, int st) {  // the ragged last chunk: guarded plain loads, same raw formats
+      unsigned char* rowb = smem + kRowsOff + st * TROWB;
+      const int valid = static_cast<int>(g.n - row);
+      if (tid < g.d) {
+        const bool is_int = g.col_i32[tid] != 0;
+        unsigned char* dst = smem + kStagingOff + st * (TF * TSTRIDE) + tid * TSTRIDE;
+        for (int k = 0; k < TKC; ++k) {
+          if (is_int) reinterpret_cast<int*>(dst)[k] = k < valid ? static_cast<const int*>(g.col_ptr[tid])[row + k] : 0;
+          else reinterpret_cast<double*>(dst)[k] = k < valid ? static_cast<const double*>(g.col_ptr[tid])[row + k] : 0.0;
+        }
+      }
+      if (tid < TKC) {
+        const bool in = tid < valid;
+        reinterpret_cast<double*>(rowb)[tid] = in ? g.label[row + tid] : 0.0;
+        reinterpret_cast<double*>(rowb + 128)[tid] = (in && g.has_dq) ? g.dq_price[row + tid] : 0.0;
+        reinterpret_cast<double*>(rowb + 256)[tid] = (in && g.weight != nullptr) ? g.weight[row + tid] : 0.0;
+        reinterpret_cast<int*>(rowb + 384)[tid] = (in && g.has_dq) ? g.dq_guest[row + tid] : 0;
+      }
+    };
+    auto issue_stage = [&](long long it) {
+      const long long chunk = blockIdx.x + it * static_cast<long long>(gridDim.x);
+      const long long row = chunk * TKC;
+      const int st = static_cast<int>(it % TSTAGES);
+      if (chunk >= full_chunks) {
+        issue_tail(row, st);
+        return;
+      }
+      const unsigned stg = sbase + kStagingOff + st * (TF * TSTRIDE) + piece_dst;
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        if (((live >> i) & 1u) && !(g.experiment & 4)) cpa16(stg + 64 * i * TSTRIDE, src[i] + (((ints >> i) & 1u) ? row * 4 : row * 8));
+      }
+      const unsigned rb = sbase + kRowsOff + st * TROWB;
+      if (tid < 8) cpa16(rb + tid * 16, g.label + row + tid * 2);
+      else if (tid < 16) { if (g.has_dq) cpa16(rb + 128 + (tid - 8) * 16, g.dq_price + row + (tid - 8) * 2); }
+      else if (tid < 24) { if (g.weight != nullptr) cpa16(rb + 256 + (tid - 16) * 16, g.weight + row + (tid - 16) * 2); }
+      else if (tid < 28) { if (g.has_dq) cpa16(rb + 384 + (tid - 24) * 16, g.dq_guest + row + (tid - 24) * 4); }
+    };
+
+    // TMEM accumulators -> the CTA's fp64 tile, stored column-major (P[col * 128 + row]) so that the 32 lanes of a warp,
+    // which hold 32 consecutive rows of one column, read-modify-write 256 contiguous bytes.  Column groups that lie
+    // entirely below the diagonal of a diagonal block are skipped.
+    auto drain = [&]() {
+      tc_fence_after();
+      const int quad = warp & 3, part = warp >> 2;
+      const int groups = nb == 2 ? SCOLS / 32 : 4;
+      const int row = quad * 32 + lane;
+      for (int cg = part; cg < groups; cg += TCONV / 128) {
+        if (cg < 4 && cg < quad) continue;            // block (0,0), below the diagonal
+        if (cg >= 8 && cg - 8 < quad) continue;       // block (1,1), below the diagonal
+        unsigned r[32];
+        tc_ld32(tmem + (static_cast<unsigned>(quad * 32) << 16) + static_cast<unsigned>(cg * 32), r);
+        double* dst = P + static_cast<size_t>(cg * 32) * 128 + row;
+#pragma unroll
+        for (int k = 0; k < 32; ++k) dst[k * 128] += static_cast<double>(__uint_as_float(r[k]));
+      }
+      tc_fence_before();
+    };
+
+    // one value -> the two tf32 operands.  hi = fp32(z) rounded to tf32 (so the tensor core, which ignores the 13 low
+    // mantissa bits, sees exactly hi; rounding rather than truncating keeps the sign of lo random, which keeps the
+    // truncation of lo by the tensor core from adding up); lo = fp32(z - hi).
+    auto split = [](double z, float& h, float& l) {
+      const unsigned hb = (__float_as_uint(__double2float_rn(z)) + 0x1000u) & 0xffffe000u;  // round to tf32 (half up in magnitude)
+      h = __uint_as_float(hb);
+      // hb as a double, by exponent re-bias (no conversion instruction): exact for normal numbers, and values below
+      // 2^-126 do not matter here
+      const unsigned mag = hb & 0x7fffffffu;
+      const int hw = mag != 0u ? static_cast<int>((hb & 0x80000000u) | ((mag >> 3) + 0x38000000u)) : static_cast<int>(hb);
+      l = __double2float_rn(z - __hiloint2double(hw, 0));
+    };
+
+    for (int s = 0; s < TSTAGES - 1; ++s) {
+      if (s < my_iters) issue_stage(s);
+      cpa_commit();
+    }
+
+    double a1 = 0.0, ab = 0.0;  // sum w (x - c), sum w (x - c) y over this thread's rows of its feature
+    int since_drain = 0;
+    unsigned drains = 0;
+    const unsigned char* sp0 = smem + kStagingOff + feat * TSTRIDE + half * (own_int ? 32 : 64);
+    unsigned char* op0 = smem + kOpsOff + (feat >> 3) * TSBO + (feat & 7) * 16 + half * 2 * TLBO;
+
+    for (long long it = 0; it < my_iters; ++it) {
+      TICK(0);
+      cpa_wait<TSTAGES - 2>();
+      TICK(1);
+      asm volatile("bar.sync 1, %0;" ::"n"(TCONV + 32) : "memory");  // chunk `it` has landed; the stage chunk it+3 goes into is free
+      TICK(2);
+      if (it + TSTAGES - 1 < my_iters) issue_stage(it + TSTAGES - 1);
+      cpa_commit();
+      TICK(3);
+
+      const int st = static_cast<int>(it % TSTAGES);
+      const int o = static_cast<int>(it & 1);
+      const double* scale = reinterpret_cast<const double*>(smem + kScaleOff) + o * (2 * TKC + 2) + half * 8;
+      mbar_wait(bar_scale0 + 8 * o, static_cast<unsigned>((it >> 1) & 1));                     // the row warp has written this chunk's factors
+      TICK(4);
+      if (it >= 2) mbar_wait(bar_free0 + 8 * o, static_cast<unsigned>(((it >> 1) - 1) & 1));  // the MMAs of chunk it-2 have read this buffer
+
+      TICK(5);
+      if (active && !(g.experiment & 1)) {
+        const unsigned char* sp = sp0 + st * (TF * TSTRIDE);
+        unsigned char* ohi = op0 + o * (2 * TOPB);
+        unsigned char* olo = ohi + TOPB;
+        const bool plain = reinterpret_cast<const int*>(scale - half * 8 + 2 * TKC)[0] != 0;
+#pragma unroll
+        for (int q = 0; q < 2; ++q) {
+          double x[4];
+          if (own_int) {
+            const int4 v = *reinterpret_cast<const int4*>(sp + q * 16);
+            x[0] = v.x; x[1] = v.y; x[2] = v.z; x[3] = v.w;
+          } else {
+            const double2 u = *reinterpret_cast<const double2*>(sp + q * 32), v = *reinterpret_cast<const double2*>(sp + q * 32 + 16);
+            x[0] = u.x; x[1] = u.y; x[2] = v.x; x[3] = v.y;
+          }
+          float h[4], l[4];
+          if (plain) {  // no dropped row, no weights in this chunk
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+              const double z = x[k] - centre;
+              a1 += z;
+              ab = fma(scale[TKC + 4 * q + k], z, ab);
+              split(z, h[k], l[k]);
+            }
+          } else {
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+              const double s = scale[4 * q + k];
+              const double z = s != 0.0 ? s * (x[k] - centre) : 0.0;  // dropped rows may hold NaN / Inf payload
+              a1 = fma(s, z, a1);
+              ab = fma(scale[TKC + 4 * q + k], z, ab);
+              split(z, h[k], l[k]);
+            }
+          }
+          *reinterpret_cast<float4*>(ohi + q * TLBO) = make_float4(h[0], h[1], h[2], h[3]);
+          *reinterpret_cast<float4*>(olo + q * TLBO) = make_float4(l[0], l[1], l[2], l[3]);
+        }
+      }
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic-proxy stores -> visible to the tensor core's reads
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bar_ready0 + 8 * o);  // one arrival per warp
+      TICK(6);
+
+      if (++since_drain == g.drain_chunks || it == my_iters - 1) {
+        mbar_wait(bar_drain, drains & 1u);
+        ++drains;
+        drain();
+        since_drain = 0;
+      }
+      TICK(7);
+    }
+    if (prof && (warp == 0 || warp == 9)) printf("converter warp %d: loop %lld cpwait %lld barrier %lld issue %lld wait_scale %lld wait_free %lld convert+arrive %lld drain %lld\n", warp, tacc[0], tacc[1], tacc[2], tacc[3], tacc[4], tacc[5], tacc[6], tacc[7]);
+    cpa_wait<0>();
+    if (active) {  // the two halves of a feature add up in either order to the same value
+      atomicAdd(&P[128 * SCOLS + feat], a1);
+      atomicAdd(&P[128 * SCOLS + TF + feat], ab);
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(512u) : "memory");
+}
+
+// centre of column j = mean of its first min(n, 256) values (0 when that is not finite): one warp per column
+__global__ void tf32_centres_kernel(const void* const* col_ptr, const unsigned char* col_i32, int d, long long n,
+                                    double* centres) {
+  const int j = blockIdx.x, lane = threadIdx.x;
+  if (j >= d) return;
+  const long long m = n < 256 ? n : 256;
+  double s = 0.0;
+  for (long long r = lane; r < m; r += 32)
+    s += col_i32[j] ? static_cast<double>(static_cast<const int*>(col_ptr[j])[r]) : static_cast<const double*>(col_ptr[j])[r];
+#pragma unroll
+  for (int off = 16; off > 0; off >>= 1) s += __shfl_down_sync(0xffffffffu, s, off);
+  if (lane == 0) {
+    const double c = m > 0 ? s / static_cast<double>(m) : 0.0;
+    centres[j] = (c - c == 0.0) ? c : 0.0;
+  }
+}
+
+// scalars and the two border vectors, folded over the CTAs in a fixed order; tot = [5 scalars, sum w (x_j - c_j) per j]
+__global__ void tf32_border_reduce_kernel(const double* __restrict__ partials, int grid, int d,
+                                          const double* __restrict__ centres, double* __restrict__ tot,
+                                          double* __restrict__ out) {
+  const int e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= 5 + 2 * d) return;
+  auto fold = [&](int off) {
+    double s = 0.0;
+    for (int b = 0; b < grid; ++b) s += partials[static_cast<size_t>(b) * kCtaDoubles + 128 * SCOLS + off];
+    return s;
+  };
+  if (e < 5) {
+    const double v = fold(2 * TF + e);
+    tot[e] = v;
+    out[e] = v;
+  } else if (e < 5 + d) {
+    const int j = e - 5;
+    const double a = fold(j), w = fold(2 * TF + 1);
+    tot[5 + j] = a;
+    out[e] = fma(centres[j], w, a);  // sum w x_j
+  } else {
+    const int j = e - 5 - d;
+    const double v = fold(TF + j), by = fold(2 * TF + 3);
+    out[e] = fma(centres[j], by, v);  // sum w x_j y
+  }
+}
+
+// packed upper triangle: sum w x_i x_j = T_ij + c_j A'_i + c_i A'_j + c_i c_j W, with T the tensor-core tile and A' the
+// centred column sums
+__global__ void tf32_pack_kernel(const double* __restrict__ partials, int grid, int d, const double* __restrict__ centres,
+                                 const double* __restrict__ tot, double* __restrict__ out) {
+  const long long q = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  const long long tri = static_cast<long long>(d) * (d + 1) / 2;
+  if (q >= tri) return;
+  long long j = static_cast<long long>((sqrt(8.0 * static_cast<double>(q) + 1.0) - 1.0) * 0.5);
+  while (j * (j + 1) / 2 > q) --j;
+  while ((j + 1) * (j + 2) / 2 <= q) ++j;
+  const long long i = q - j * (j + 1) / 2;  // i <= j
+  const size_t off = i < 128 ? static_cast<size_t>(j) * 128 + i : static_cast<size_t>(256 + (j - 128)) * 128 + (i - 128);  // column-major tile
+  double t = 0.0;
+  for (int b = 0; b < grid; ++b) t += partials[static_cast<size_t>(b) * kCtaDoubles + off];
+  const double ci = centres[i], cj = centres[j];
+  out[5 + 2 * d + q] = t + cj * tot[5 + i] + ci * tot[5 + j] + ci * cj * tot[1];
+}
+
+}  // namespace
+
+bool gram_tf32_supported(int d) { return d >= 1 && d <= TF; }
+
+int gram_tf32_wls_moments(dq4ml_ctx* ctx, const std::vector<const void*>& col_ptrs, const std::vector<int>& dtypes,
+                          const double* label, const double* weight, const DeviceDq& dq, int64_t n, double* out) {
+  const int d = static_cast<int>(col_ptrs.size());
+  if (!gram_tf32_supported(d)) {
+    set_error("the tf32 Gram tier handles 1..%d feature columns (got %d)", TF, d);
+    return DQ4ML_ERR_UNSUPPORTED;
+  }
+  const int64_t len = 5 + 2LL * d + static_cast<int64_t>(d) * (d + 1) / 2;
+  const int64_t chunks = (n + TKC - 1) / TKC;
+  int grid = ctx->sm_count;
+  if (grid > chunks) grid = static_cast<int>(chunks);
+  if (grid < 1) grid = 1;
+  const size_t table_bytes = (static_cast<size_t>(d) * 9 + 255) & ~static_cast<size_t>(255);
+  const size_t centre_bytes = TF * sizeof(double);
+  const size_t tot_bytes = (5 + TF + 3) * sizeof(double);
+  const size_t part_bytes = static_cast<size_t>(grid) * kCtaDoubles * sizeof(double);
+  const size_t out_bytes = static_cast<size_t>(len) * sizeof(double);
+  const size_t need = table_bytes + centre_bytes + tot_bytes + part_bytes + out_bytes + 512;
+  auto fail = [](cudaError_t e, const char* what) {
+    set_error("%s: %s", what, cudaGetErrorString(e));
+    return DQ4ML_ERR_CUDA;
+  };
+  cudaError_t e;
+  if (need > ctx->gram_cap) {
+    if ((e = cudaStreamSynchronize(ctx->stream)) != cudaSuccess) return fail(e, "sync");
+    if (ctx->gram_scratch != nullptr) cudaFree(ctx->gram_scratch);
+    ctx->gram_scratch = nullptr;
+    ctx->gram_cap = 0;
+    if ((e = cudaMalloc(reinterpret_cast<void**>(&ctx->gram_scratch), need)) != cudaSuccess) return fail(e, "gram scratch");
+    ctx->gram_cap = need;
+  }
+  if (out_bytes > ctx->gram_host_cap) {
+    if (ctx->gram_host != nullptr) cudaFreeHost(ctx->gram_host);
+    ctx->gram_host = nullptr;
+    ctx->gram_host_cap = 0;
+    if ((e = cudaMallocHost(reinterpret_cast<void**>(&ctx->gram_host), out_bytes)) != cudaSuccess) return fail(e, "gram pinned result");
+    ctx->gram_host_cap = out_bytes;
+  }
+  char* base = ctx->gram_scratch;
+  const void** d_ptrs = reinterpret_cast<const void**>(base);
+  unsigned char* d_i32 = reinterpret_cast<unsigned char*>(base + static_cast<size_t>(d) * 8);
+  double* d_centres = reinterpret_cast<double*>(base + table_bytes);
+  double* d_tot = reinterpret_cast<double*>(base + table_bytes + centre_bytes);
+  double* d_part = reinterpret_cast<double*>(base + table_bytes + centre_bytes + tot_bytes);
+  double* d_out = reinterpret_cast<double*>(base + table_bytes + centre_bytes + tot_bytes + part_bytes);
+  std::vector<unsigned char> flags(d);
+  for (int j = 0; j < d; ++j) flags[j] = dtypes[j] == DQ4ML_I32 ? 1 : 0;
+  if ((e = cudaMemcpyAsync(d_ptrs, col_ptrs.data(), static_cast<size_t>(d) * 8, cudaMemcpyHostToDevice, ctx->stream)) != cudaSuccess) return fail(e, "column table upload");
+  if ((e = cudaMemcpyAsync(d_i32, flags.data(), static_cast<size_t>(d), cudaMemcpyHostToDevice, ctx->stream)) != cudaSuccess) return fail(e, "column table upload");
+  if ((e = cudaStreamSynchronize(ctx->stream)) != cudaSuccess) return fail(e, "sync");  // the host vectors go out of scope
+
+  Tf32Args g;
+  g.col_ptr = d_ptrs;
+  g.col_i32 = d_i32;
+  g.centres = d_centres;
+  g.d = d;
+  g.label = label;
+  g.weight = weight;
+  g.dq_guest = dq.guest;
+  g.dq_price = dq.price;
+  g.t.min_price = dq.params.min_price;
+  g.t.max_price = dq.params.max_price;
+  g.t.min_guest = dq.params.min_guest;
+  g.has_dq = dq.guest != nullptr ? 1 : 0;
+  g.n = n;
+  int drain_rows = 1024;  // fp32 accumulation span; see the header comment
+  if (const char* env = getenv("DQ4ML_TF32_DRAIN_ROWS")) { const int v = atoi(env); if (v >= TKC) drain_rows = v; }
+  g.drain_chunks = drain_rows / TKC;
+  g.swap_offsets = getenv("DQ4ML_TF32_SWAP_OFFSETS") != nullptr ? 1 : 0;
+  g.experiment = getenv("DQ4ML_TF32_EXPERIMENT") != nullptr ? atoi(getenv("DQ4ML_TF32_EXPERIMENT")) : 0;
+  g.partials = d_part;
+  static bool attr_set[64] = {false};
+  if (ctx->device < 64 && !attr_set[ctx->device]) {
+    if ((e = cudaFuncSetAttribute(gram_tf32_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kTf32Smem)) != cudaSuccess)
+      return fail(e, "tf32 gram smem attribute");
+    attr_set[ctx->device] = true;
+  }
+  if (ctx->pass_timing) cudaEventRecord(ctx->pass_ev0, ctx->stream);
+  tf32_centres_kernel<<<d, 32, 0, ctx->stream>>>(d_ptrs, d_i32, d, n, d_centres);
+  if ((e = cudaGetLastError()) != cudaSuccess) return fail(e, "tf32 centres kernel");
+  if ((e = cudaMemsetAsync(d_part, 0, part_bytes, ctx->stream)) != cudaSuccess) return fail(e, "tf32 tile clear");
+  gram_tf32_kernel<<<grid, TTHREADS, kTf32Smem, ctx->stream>>>(g);
+  if ((e = cudaGetLastError()) != cudaSuccess) return fail(e, "tf32 gram kernel");
+  tf32_border_reduce_kernel<<<(5 + 2 * d + 127) / 128, 128, 0, ctx->stream>>>(d_part, grid, d, d_centres, d_tot, d_out);
+  if ((e = cudaGetLastError()) != cudaSuccess) return fail(e, "tf32 border reduce kernel");
+  const long long tri = static_cast<long long>(d) * (d + 1) / 2;
+  tf32_pack_kernel<<<static_cast<unsigned>((tri + 255) / 256), 256, 0, ctx->stream>>>(d_part, grid, d, d_centres, d_tot, d_out);
+  if ((e = cudaGetLastError()) != cudaSuccess) return fail(e, "tf32 pack kernel");
+  ctx->launches += 4;
+  if (ctx->pass_timing) {
+    cudaEventRecord(ctx->pass_ev1, ctx->stream);
+    ctx->pass_event_pending = true;
+  }
+  if (ctx->nccl != nullptr) {
+    const int rc = nccl_allreduce_device(ctx, d_out, len);
+    if (rc != DQ4ML_OK) return rc;
+  }
+  if ((e = cudaMemcpyAsync(ctx->gram_host, d_out, out_bytes, cudaMemcpyDeviceToHost, ctx->stream)) != cudaSuccess) return fail(e, "gram D2H");
+  if ((e = cudaStreamSynchronize(ctx->stream)) != cudaSuccess) return fail(e, "tf32 gram pass");
+  if (ctx->pass_event_pending) {
+    ctx->pass_event_pending = false;
+    float ms = 0.f;
+    if (cudaEventElapsedTime(&ms, ctx->pass_ev0, ctx->pass_ev1) == cudaSuccess) {
+      ctx->pass_ms_total += ms;
+      ++ctx->pass_count;
+    }
+  }
+  if (ctx->nccl == nullptr && ctx->allreduce_cb != nullptr) {
+    if (ctx->allreduce_cb(ctx->allreduce_user, ctx->gram_host, len) != 0) {
+      set_error("all-reduce callback failed");
+      return DQ4ML_ERR_COMM;
+    }
+  }
+  std::copy(ctx->gram_host, ctx->gram_host + len, out);
+  return DQ4ML_OK;
+}
+
+}  // namespace dq4ml

@@ -52,6 +52,13 @@ class Context:
     def launch_count(self) -> int:
         return int(capi.lib().dq4ml_ctx_launch_count(self._h))
 
+    def set_gram_tier(self, tier="fp64"):
+        """"fp64" (default, 1e-9 parity) or "tf32x3" (tcgen05 tensor cores, TMEM accumulators, 1e-5 tolerance, d <= 256)."""
+        tiers = {"fp64": 0, "tf32x3": 1}
+        if tier not in tiers:
+            raise ValueError(f"tier must be one of {sorted(tiers)}")
+        capi.check(capi.lib().dq4ml_ctx_set_gram_tier(self._h, tiers[tier]))
+
     def enable_pass_timing(self, on=True):
         capi.check(capi.lib().dq4ml_ctx_enable_pass_timing(self._h, int(bool(on))))
 

@@ -62,10 +62,11 @@ def config3(pkg, ctx, rows, reps, row0=0, world=1, global_rows=None):
     torch.cuda.empty_cache()
 
 
-def config4(pkg, ctx, rows, reps, row0=0, world=1):
+def config4(pkg, ctx, rows, reps, row0=0, world=1, tier="fp64"):
     import torch
     from sparkdq4ml_b200 import ml
     d = 256
+    ctx.set_gram_tier(tier)
     g, p, x = ctx.synth_generate(rows, d=d, row0=row0)
     feats = [g] + [x[k] for k in range(d - 1)]
     flop_per_row = d * (d + 1) + 4 * d  # symmetric half of X^T X at 2 flop/MAC + X^T y + sums
@@ -80,7 +81,7 @@ def config4(pkg, ctx, rows, reps, row0=0, world=1):
         ctx.enable_pass_timing(False)
         if ctx.rank != 0:
             continue
-        print(json.dumps({"config": 4, "n_gpus": world, "rows_per_gpu": rows, "features": d, "survivors_all_ranks": mom[0], "gram_pass_ms": ms / passes_n,
+        print(json.dumps({"config": 4, "gram_tier": tier, "n_gpus": world, "rows_per_gpu": rows, "features": d, "survivors_all_ranks": mom[0], "gram_pass_ms": ms / passes_n,
                           "wall_ms": wall * 1e3, "rows_per_sec_pass": rows / (ms / passes_n / 1e3),
                           "algorithmic_tflops": flop_per_row * rows / (ms / passes_n / 1e3) / 1e12,
                           "frac_of_measured_fp64_peak_37.2": flop_per_row * rows / (ms / passes_n / 1e3) / 1e12 / 37.2,
@@ -92,7 +93,7 @@ def config4(pkg, ctx, rows, reps, row0=0, world=1):
     model = lr.fit(df)
     wall = time.perf_counter() - t0
     if ctx.rank == 0:
-        print(json.dumps({"config": 4, "n_gpus": world, "what": "whole fit (Gram pass + all-reduce + packed Cholesky on the host)", "rows_per_gpu": rows,
+        print(json.dumps({"config": 4, "gram_tier": tier, "n_gpus": world, "what": "whole fit (Gram pass + all-reduce + packed Cholesky on the host)", "rows_per_gpu": rows,
                       "fit_seconds": wall, "rows_per_sec_fit": rows * world / wall, "solver": model.solver_used,
                       "coefficients_head": model.coefficients()[:4].tolist(), "intercept": model.intercept()}), flush=True)
     del g, p, x, feats
@@ -131,6 +132,7 @@ def main():
     ap.add_argument("--config", type=int, required=True)
     ap.add_argument("--rows", type=int, default=0)
     ap.add_argument("--reps", type=int, default=3)
+    ap.add_argument("--gram-tier", type=str, default="fp64", choices=["fp64", "tf32x3"])
     ap.add_argument("--sizes", type=str, default="10000000,100000000,1000000000,4000000000")
     a = ap.parse_args()
     import sparkdq4ml_b200 as pkg
@@ -147,7 +149,7 @@ def main():
         config3(pkg, ctx, hi - lo, a.reps, row0=lo, world=world, global_rows=n_global)
     elif a.config == 4:
         rows = a.rows or 62_500_000
-        config4(pkg, ctx, rows, a.reps, row0=rank * rows, world=world)
+        config4(pkg, ctx, rows, a.reps, row0=rank * rows, world=world, tier=a.gram_tier)
     elif a.config == 5:
         config5(pkg, ctx, [int(s) for s in a.sizes.split(",")], a.reps)
     ctx.close()
