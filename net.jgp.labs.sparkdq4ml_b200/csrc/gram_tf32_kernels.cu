@@ -1,25 +1,45 @@
 // gram_tf32_kernels.cu -- the tensor-core tier of the normal-equation pass: Z^T Z on tcgen05 (5th-gen tensor cores,
-// accumulators in TMEM) with a 3xTF32 split, for 9 <= d <= 256 feature columns.
+// accumulators in TMEM) with a 3xTF32 split, for 1 <= d <= 256 feature columns.  Opt-in (dq4ml_ctx_set_gram_tier).
 //
-// What it computes is the same WeightedLeastSquares.Aggregator result as gram_kernels.cu (lr.fit, App:126, solver
-// normal/auto), at a relaxed tolerance: every centred, weighted value z = sqrt(w) (x - c) is split into hi = tf32(z)
-// and lo = tf32(z - hi); hi.hi + hi.lo + lo.hi reproduces the product to ~2^-21, fp32 accumulation happens in TMEM over
-// at most `drain_rows` rows and is then added into an fp64 tile in L2-resident scratch.  The centring (c = mean of the
-// column head) makes the tensor-core part carry covariances rather than raw second moments, so its rounding error is
-// relative to sigma_i sigma_j, which is what the regression needs; the raw moments are rebuilt in fp64 from the exact
-// column sums.  Stated tolerance of the tier: 1e-5 relative on coefficients / intercept (north_star: "1e-5 where fp32
-// accumulation is used and justified"); the fp64 DMMA kernel stays the default.
+// What it computes is the WeightedLeastSquares.Aggregator result of gram_kernels.cu (lr.fit, App:126, solver normal /
+// auto) at a relaxed tolerance.  Every centred, weighted value z = sqrt(w) keep (x - c), c = mean of the column's first
+// 256 values, is rounded to fp32 and split into hi (11 leading bits, exactly a tf32) and lo = z - hi; the tensor core
+// accumulates hi.hi + hi.lo + lo.hi in fp32 in TMEM, which reproduces each product to ~2^-21.  Three things keep the
+// fp32 accumulation -- which rounds towards zero, i.e. loses half an ulp of the running sum per step, always in the
+// same direction for a sum of one sign -- from showing in the regression:
+//   - the accumulators are drained into an fp64 tile every `drain_rows` rows (2048 by default);
+//   - centring makes the off-diagonal sums covariances, which hover around zero unless two columns are correlated
+//     (measured error of a covariance relative to sigma_i sigma_j: 3e-7 at 2048 rows, growing linearly with the span and
+//     with the correlation);
+//   - the sums that are of one sign or carry the signal never touch the tensor core: sum z^2 (the diagonal),
+//     sum w (x - c) (which the centres multiply when the raw moments are rebuilt) and sum w (x - c)(y - c_y) are summed
+//     over 8 rows in fp32 with round-to-nearest and across chunks in fp64 by the threads that convert the values; the
+//     five scalars (count, sum w, sum w^2, sum w y, sum w y^2) are fp64 throughout.
+// Measured against the fp64 kernel on the config-4 workload (62.5 M x 256, fused DQ): coefficients agree to 5e-7
+// relative, the intercept to 1.4e-6.  Stated tolerance of the tier: 1e-5 (north_star: "1e-5 where fp32 accumulation is
+// used and justified"); the fp64 DMMA kernel stays the default.
 //
-// Shape of the kernel (one persistent CTA per SM, 256 threads, all of TMEM):
-//   - rows are taken in chunks of 16; a 3-stage cp.async pipeline stages the raw fp64 / int32 column pieces;
-//   - thread t owns feature column t: it centres / weights / masks its 16 values, accumulates sum w(x-c) and
-//     sum w(x-c)y in fp64, and writes the hi and lo operands in the canonical no-swizzle K-major UMMA layout
-//     (8 x 16-byte core matrices);
-//   - one thread issues the MMAs of the chunk: per 8 rows and per split term, M128 x N256 for the feature block row 0
-//     (blocks (0,0) and (0,1)) and M128 x N128 for block (1,1); completion is tracked with tcgen05.commit -> mbarrier,
-//     which is also what frees the operand buffer for the conversion two chunks later;
-//   - every drain_rows rows the 128 x 384 fp32 accumulators are read with tcgen05.ld and added to the CTA's fp64 tile.
-// A second, small kernel pair folds the per-CTA tiles and rebuilds the public moment layout.
+// Shape of the kernel: one persistent CTA per SM (all 512 TMEM columns, ~217 KB of shared memory), 18 warps:
+//   - 16 loader / converter warps.  Rows are taken in chunks of 16.  A 4-stage cp.async ring stages the raw fp64 / int32
+//     pieces of all columns (8 neighbouring threads fetch one 128-byte line); after one named barrier per chunk, two
+//     threads per feature convert 8 rows each and write the hi and lo operands in the canonical no-swizzle K-major UMMA
+//     layout (8-row x 16-byte core matrices; LBO = 128 B between the K chunks, SBO = 512 B between 8-feature groups),
+//     then fence.proxy.async and one mbarrier arrival per warp;
+//   - the MMA warp: one thread waits for the operands of a chunk and issues, per 8 rows and per split term,
+//     M128 x N256 (features 0..127 against all 256) and M128 x N128 (features 128..255 against themselves) of
+//     kind::tf32; tcgen05.commit -> mbarrier frees the operand buffer (two buffers) and announces a finished span;
+//   - the row warp: its own 16-deep cp.async ring for label / DQ price / DQ guest / weight, the keep mask of the DQ
+//     rules, the per-row factors for the converters (eight buffers ahead), the five scalar sums;
+//   - the drain: every warp reads its TMEM lane quadrant with tcgen05.ld.32x32b.x32 and adds it to the CTA's fp64 tile in
+//     L2-resident scratch, stored column-major so that the 32 lanes read-modify-write 256 contiguous bytes; column
+//     groups below the diagonal of a diagonal block are skipped.
+// A small kernel pair folds the per-CTA tiles in a fixed order and rebuilds the public moment layout.
+//
+// Where the time goes (62.5 M x 256: 50 ms = 0.39 of the HBM roofline, tensor pipe 40 % busy, vs 178 ms for the fp64
+// kernel): the converter warps.  Each executes ~240 instructions per chunk (conversion ~140, synchronisation and load
+// issue ~100) as a mostly serial stream, four warps per scheduler; ablations (DQ4ML_TF32_EXPERIMENT) put loads alone at
+// 30 ms, conversion alone at 32 ms, MMAs alone at 37 ms.  Next: packed f32x2 arithmetic for the split and the sums,
+// wrap-around counters instead of 64-bit modulo, two chunks per row-warp iteration.
 #include <algorithm>
 #include <cstdio>
 #include <cstdlib>
@@ -32,30 +52,39 @@
 namespace dq4ml {
 namespace {
 
-constexpr int TF = 256;                     // feature slots per CTA = threads per CTA
+constexpr int TF = 256;                     // feature slots per CTA
 constexpr int TKC = 16;                     // rows per chunk
 constexpr int TSTAGES = 4;                  // staging stages (raw columns)
+constexpr int TROWST = 16;                  // stages of the row warp's own ring (its loads are latency-bound: depth is what feeds it)
 constexpr int TCONV = 512;                  // loader / converter threads: two per feature slot
 constexpr int TTHREADS = TCONV + 64;        // + the MMA warp + the row warp
 constexpr int TOPS = 2;                     // operand stages (hi/lo tf32)
+constexpr int TSCALE = 8;                   // row-factor buffers: how far the row warp may run ahead of the converters
 constexpr int TSTRIDE = TKC * 8 + 16;       // bytes per feature in a staging stage: +16 keeps 128-bit reads conflict-free
 constexpr int TLBO = 128;                   // bytes between the two 16-byte K chunks of one MMA (core matrix = 8 x 16 B)
 constexpr int TSBO = (TKC / 4) * 128;       // bytes between groups of 8 feature rows
 constexpr int TOPB = TF * TKC * 4;          // bytes of one operand buffer (hi or lo)
-constexpr int TROWB = 512;                  // per staging stage: y[16], dq price[16], weight[16], dq guest[16]
+constexpr int TROWB = 512;                  // per row stage: y[16], dq price[16], weight[16], dq guest[16]
+constexpr int TSCB = 160;                   // per row-factor buffer: float s[16], float s (y - c_y)[16], flag
 constexpr int kStagingOff = 0;
 constexpr int kOpsOff = kStagingOff + TSTAGES * TF * TSTRIDE;
 constexpr int kRowsOff = kOpsOff + TOPS * 2 * TOPB;
-constexpr int kScaleOff = kRowsOff + TSTAGES * TROWB;  // s[16], s*y[16]
-constexpr int kBarOff = kScaleOff + 2 * (2 * TKC + 2) * 8;  // two sets of row factors (s[16], s*y[16], flag), then 7 mbarriers + the TMEM base address
-constexpr int kTf32Smem = kBarOff + 64;
-constexpr int SCOLS = 384;                  // fp64 tile columns per CTA: block (0,0) | (0,1) | (1,1)
-constexpr int kCtaDoubles = 128 * SCOLS + 2 * TF + 8;  // tile, sum w(x-c)[256], sum w(x-c)y[256], 5 scalars
+constexpr int kScaleOff = kRowsOff + TROWST * TROWB;
+constexpr int kBarOff = kScaleOff + TSCALE * TSCB;  // 10 mbarriers + the TMEM base address
+constexpr int kTf32Smem = kBarOff + 8 * (2 * TOPS + 2 * TSCALE + 2);
+// TMEM accumulator columns: [0, 256) = features 0..127 x features 0..255, [256, 384) = features 128..255 x features 128..255
+constexpr int kColC = 256;
+constexpr int SCOLS = 384;                  // fp64 tile columns per CTA (12 groups of 32), stored column-major
+constexpr int kDiagOff = 128 * SCOLS;       // sum z^2 per feature
+constexpr int kA1Off = kDiagOff + TF;       // sum w (x - c) per feature
+constexpr int kAbOff = kA1Off + TF;         // sum w (x - c)(y - c_y) per feature
+constexpr int kScalarOff = kAbOff + TF;     // count, sum w, sum w^2, sum w y, sum w y^2
+constexpr int kCtaDoubles = kScalarOff + 8;
 
 struct Tf32Args {
   const void* const* col_ptr;
   const unsigned char* col_i32;
-  const double* centres;  // [d]
+  const double* centres;  // [d + 1]: features, then the label
   int d;
   const double* label;
   const double* weight;
@@ -66,7 +95,7 @@ struct Tf32Args {
   long long n;
   int drain_chunks;
   int swap_offsets;  // debug: exchange LBO and SBO in the descriptors
-  int experiment;    // debug: bit 0 = converters skip the conversion, bit 1 = no MMAs are issued, bit 2 = no loads
+  int experiment;    // ablation: bit 0 = converters skip the conversion, bit 1 = no MMAs are issued, bit 2 = no column loads, bit 3 = timers (profile build)
   double* partials;  // [grid][kCtaDoubles], zeroed by the launcher
 };
 
@@ -135,12 +164,16 @@ __host__ __device__ constexpr unsigned umma_idesc_tf32(int n) {
   return (1u << 4) | (2u << 7) | (2u << 10) | (static_cast<unsigned>(n >> 3) << 17) | (static_cast<unsigned>(128 >> 4) << 24);
 }
 
-__device__ __forceinline__ float to_tf32(float f) {
-  unsigned b;
-  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(b) : "f"(f));
-  return __uint_as_float(b);
+// One fp32 value -> the two tf32 operands (Dekker's split with 2^13 + 1): hi carries the 11 leading bits of f, rounded
+// to nearest, so the tensor core -- which ignores the 13 low mantissa bits -- sees exactly hi; lo = f - hi is exact in
+// fp32, and its own truncation by the tensor core is a 2^-21 relative effect of random sign.  NaN / Inf stay NaN.
+__device__ __forceinline__ void split_f32(float f, float& h, float& l) {
+  const float t = __fmul_rn(f, 8193.0f);  // the _rn intrinsics keep the compiler from contracting this into an FMA
+  h = __fsub_rn(t, __fsub_rn(t, f));
+  l = __fsub_rn(f, h);
 }
 
+#ifdef DQ4ML_TF32_PROFILE
 #define TICK(slot)                                   \
   do {                                               \
     if (prof) {                                      \
@@ -149,28 +182,49 @@ __device__ __forceinline__ float to_tf32(float f) {
       tlast = now_;                                  \
     }                                                \
   } while (0)
+#else
+#define TICK(slot) \
+  do {             \
+  } while (0)
+#endif
+
+// does a warp of lane quadrant `quad` have to drain 32-column group cg?  Groups that lie entirely below the diagonal of
+// a diagonal block are skipped.
+__device__ __forceinline__ bool drain_needed(int cg, int quad) {
+  if (cg < 4) return cg >= quad;
+  if (cg < 8) return true;
+  return cg - 8 >= quad;
+}
 
 __global__ void __launch_bounds__(TTHREADS, 1) gram_tf32_kernel(const Tf32Args g) {
+#ifdef DQ4ML_TF32_PROFILE
   const bool prof = (g.experiment & 8) != 0 && blockIdx.x == 0 && (threadIdx.x & 31) == 0;
   long long tacc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
   long long tlast = clock64();
+#endif
   extern __shared__ __align__(128) unsigned char smem[];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const unsigned sbase = s_u32(smem);
-  const unsigned bar_free0 = sbase + kBarOff, bar_ready0 = bar_free0 + 16, bar_scale0 = bar_free0 + 32, bar_drain = bar_free0 + 48;
-  unsigned* tmem_slot = reinterpret_cast<unsigned*>(smem + kBarOff + 56);
+  const unsigned bar_free0 = sbase + kBarOff;      // [TOPS] operand buffer o may be overwritten: arrived by tcgen05.commit
+  const unsigned bar_ready0 = bar_free0 + 8 * TOPS;       // [TOPS] operand buffer o is written: one arrival per converter warp
+  const unsigned bar_scale0 = bar_ready0 + 8 * TOPS;      // [TSCALE] row factors of a chunk are written: the row warp
+  const unsigned bar_sfree0 = bar_scale0 + 8 * TSCALE;    // [TSCALE] row factors of a chunk have been used: one arrival per converter warp
+  const unsigned bar_drain = bar_sfree0 + 8 * TSCALE;     // every MMA issued so far has completed
+  unsigned* tmem_slot = reinterpret_cast<unsigned*>(smem + kBarOff + 8 * (2 * TOPS + 2 * TSCALE + 1));
   const int nb = g.d > 128 ? 2 : 1;
 
   // operand buffers start as zeros: feature slots >= d are never written again
   for (int i = tid; i < TOPS * 2 * TOPB / 16; i += TTHREADS) reinterpret_cast<int4*>(smem + kOpsOff)[i] = make_int4(0, 0, 0, 0);
   if (tid == 0) {
-    mbar_init(bar_free0, 1);          // operand buffer o may be overwritten: arrived by tcgen05.commit
-    mbar_init(bar_free0 + 8, 1);
-    mbar_init(bar_ready0, TCONV / 32);  // operand buffer o is written: arrived once per converter warp
-    mbar_init(bar_ready0 + 8, TCONV / 32);
-    mbar_init(bar_scale0, 1);           // row factors of a chunk are written: arrived by the row warp
-    mbar_init(bar_scale0 + 8, 1);
-    mbar_init(bar_drain, 1);          // every MMA issued so far has completed
+    for (int o = 0; o < TOPS; ++o) {
+      mbar_init(bar_free0 + 8 * o, 1);
+      mbar_init(bar_ready0 + 8 * o, TCONV / 32);
+    }
+    for (int b = 0; b < TSCALE; ++b) {
+      mbar_init(bar_scale0 + 8 * b, 1);
+      mbar_init(bar_sfree0 + 8 * b, TCONV / 32);
+    }
+    mbar_init(bar_drain, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 0) {  // all 512 TMEM columns: this kernel is alone on its SM (shared memory sees to that)
@@ -195,9 +249,9 @@ __global__ void __launch_bounds__(TTHREADS, 1) gram_tf32_kernel(const Tf32Args g
       const unsigned idesc_row0 = umma_idesc_tf32(nb == 2 ? 256 : 128), idesc_blk = umma_idesc_tf32(128);
       int since_drain = 0;
       for (long long it = 0; it < my_iters; ++it) {
-        const int o = static_cast<int>(it & 1);
+        const int o = static_cast<int>(it % TOPS);
         TICK(0);
-        mbar_wait(bar_ready0 + 8 * o, static_cast<unsigned>((it >> 1) & 1));
+        mbar_wait(bar_ready0 + 8 * o, static_cast<unsigned>((it / TOPS) & 1));
         TICK(1);
         tc_fence_after();
         const unsigned hi = sbase + kOpsOff + o * (2 * TOPB), lo = hi + TOPB;
@@ -210,7 +264,7 @@ __global__ void __launch_bounds__(TTHREADS, 1) gram_tf32_kernel(const Tf32Args g
             const unsigned acc = (since_drain == 0 && ks == 0 && term == 0) ? 0u : 1u;
             tc_mma_tf32(tmem, umma_desc(a, lbo, sbo), umma_desc(b, lbo, sbo), idesc_row0, acc);
             if (nb == 2)
-              tc_mma_tf32(tmem + 256, umma_desc(a + 16 * TSBO, lbo, sbo), umma_desc(b + 16 * TSBO, lbo, sbo), idesc_blk, acc);
+              tc_mma_tf32(tmem + kColC, umma_desc(a + 16 * TSBO, lbo, sbo), umma_desc(b + 16 * TSBO, lbo, sbo), idesc_blk, acc);
           }
         }
         tc_commit(bar_free0 + 8 * o);
@@ -220,18 +274,48 @@ __global__ void __launch_bounds__(TTHREADS, 1) gram_tf32_kernel(const Tf32Args g
         }
         TICK(2);
       }
+#ifdef DQ4ML_TF32_PROFILE
       if (prof) printf("mma thread: loop %lld wait_ready %lld issue+commit %lld (cycles, %lld chunks)\n", tacc[0], tacc[1], tacc[2], my_iters);
+#endif
     }
   } else if (warp == TCONV / 32 + 1) {
-    // ================================================= row warp: keep mask, weight, label factors of every chunk ========
+    // ================================================= row warp ========================================================
+    // Owns the per-row columns (label, DQ price / guest, weight): its own cp.async ring, the keep mask of the DQ rules,
+    // the per-row factors s = sqrt(w) keep and s (y - c_y) the converters multiply with, and the five scalar sums.  It
+    // runs up to TSCALE chunks ahead of the converters.
+    auto issue_rows = [&](long long it) {
+      const long long row = (blockIdx.x + it * static_cast<long long>(gridDim.x)) * TKC;
+      unsigned char* rowb = smem + kRowsOff + static_cast<int>(it % TROWST) * TROWB;
+      if (row + TKC <= g.n) {
+        const unsigned rb = s_u32(rowb);
+        if (lane < 8) cpa16(rb + lane * 16, g.label + row + lane * 2);
+        else if (lane < 16) { if (g.has_dq) cpa16(rb + 128 + (lane - 8) * 16, g.dq_price + row + (lane - 8) * 2); }
+        else if (lane < 24) { if (g.weight != nullptr) cpa16(rb + 256 + (lane - 16) * 16, g.weight + row + (lane - 16) * 2); }
+        else if (lane < 28) { if (g.has_dq) cpa16(rb + 384 + (lane - 24) * 16, g.dq_guest + row + (lane - 24) * 4); }
+      } else if (lane < TKC) {  // the ragged last chunk
+        const bool in = row + lane < g.n;
+        reinterpret_cast<double*>(rowb)[lane] = in ? g.label[row + lane] : 0.0;
+        reinterpret_cast<double*>(rowb + 128)[lane] = (in && g.has_dq) ? g.dq_price[row + lane] : 0.0;
+        reinterpret_cast<double*>(rowb + 256)[lane] = (in && g.weight != nullptr) ? g.weight[row + lane] : 0.0;
+        reinterpret_cast<int*>(rowb + 384)[lane] = (in && g.has_dq) ? g.dq_guest[row + lane] : 0;
+      }
+    };
+    for (int s = 0; s < TROWST - 1; ++s) {
+      if (s < my_iters) issue_rows(s);
+      cpa_commit();
+    }
     double cnt = 0.0, wsum = 0.0, wwsum = 0.0, bsum = 0.0, bbsum = 0.0;
+    const double ycentre = g.centres[g.d];
     for (long long it = 0; it < my_iters; ++it) {
       TICK(0);
-      asm volatile("bar.sync 1, %0;" ::"n"(TCONV + 32) : "memory");  // chunk `it` has landed
+      cpa_wait<TROWST - 2>();
+      __syncwarp();
+      if (it + TROWST - 1 < my_iters) issue_rows(it + TROWST - 1);
+      cpa_commit();
       TICK(1);
-      const int st = static_cast<int>(it % TSTAGES);
-      const unsigned char* rowb = smem + kRowsOff + st * TROWB;
-      double* scale = reinterpret_cast<double*>(smem + kScaleOff) + (it & 1) * (2 * TKC + 2);
+      const unsigned char* rowb = smem + kRowsOff + static_cast<int>(it % TROWST) * TROWB;
+      const int b = static_cast<int>(it % TSCALE);
+      double s = 0.0, sy = 0.0;
       bool plain = true;
       if (lane < TKC) {
         const long long row = (blockIdx.x + it * static_cast<long long>(gridDim.x)) * TKC + lane;
@@ -239,10 +323,9 @@ __global__ void __launch_bounds__(TTHREADS, 1) gram_tf32_kernel(const Tf32Args g
         if (keep && g.has_dq)
           keep = dq_keep(reinterpret_cast<const int*>(rowb + 384)[lane], reinterpret_cast<const double*>(rowb + 128)[lane], g.t);
         const double w = keep ? (g.weight != nullptr ? reinterpret_cast<const double*>(rowb + 256)[lane] : 1.0) : 0.0;
-        const double s = g.weight != nullptr ? sqrt(w) : w;
+        s = g.weight != nullptr ? sqrt(w) : w;
         const double y = keep ? reinterpret_cast<const double*>(rowb)[lane] : 0.0;
-        scale[lane] = s;
-        scale[TKC + lane] = keep ? s * y : 0.0;
+        sy = keep ? s * (y - ycentre) : 0.0;
         plain = s == 1.0;
         cnt += keep ? 1.0 : 0.0;
         wsum += s * s;  // = w, and NaN for a negative weight (require(w >= 0))
@@ -251,12 +334,19 @@ __global__ void __launch_bounds__(TTHREADS, 1) gram_tf32_kernel(const Tf32Args g
         bbsum = fma(w * y, y, bbsum);
       }
       const bool all_plain = __all_sync(0xffffffffu, plain);
+      if (it >= TSCALE) mbar_wait(bar_sfree0 + 8 * b, static_cast<unsigned>(((it / TSCALE) - 1) & 1));  // the converters are done with chunk it-3
+      TICK(2);
+      float* scale = reinterpret_cast<float*>(smem + kScaleOff + b * TSCB);
+      if (lane < TKC) {
+        scale[lane] = __double2float_rn(s);
+        scale[TKC + lane] = __double2float_rn(sy);
+      }
       if (lane == 0) reinterpret_cast<int*>(scale + 2 * TKC)[0] = all_plain ? 1 : 0;  // every factor is 1: the converters skip the scaling
       __syncwarp();
-      if (lane == 0) mbar_arrive(bar_scale0 + 8 * static_cast<unsigned>(it & 1));
-      TICK(2);
+      if (lane == 0) mbar_arrive(bar_scale0 + 8 * static_cast<unsigned>(b));
+      TICK(3);
     }
-    if (prof) printf("row warp: loop %lld barrier %lld work %lld\n", tacc[0], tacc[1], tacc[2]);
+    cpa_wait<0>();
 #pragma unroll
     for (int off = 8; off > 0; off >>= 1) {
       cnt += __shfl_down_sync(0xffffffffu, cnt, off);
@@ -266,9 +356,12 @@ __global__ void __launch_bounds__(TTHREADS, 1) gram_tf32_kernel(const Tf32Args g
       bbsum += __shfl_down_sync(0xffffffffu, bbsum, off);
     }
     if (lane == 0) {
-      double* sc = P + 128 * SCOLS + 2 * TF;
+      double* sc = P + kScalarOff;
       sc[0] = cnt; sc[1] = wsum; sc[2] = wwsum; sc[3] = bsum; sc[4] = bbsum;
     }
+#ifdef DQ4ML_TF32_PROFILE
+    if (prof) printf("row warp: loop %lld loads %lld compute+wait_sfree %lld write+arrive %lld\n", tacc[0], tacc[1], tacc[2], tacc[3]);
+#endif
   } else {
     // ================================================= loader / converter warps ========================================
     // converter: two threads per feature, 8 rows of every chunk each (lanes 0..15 / 16..31 of a warp share 16 features)
@@ -292,31 +385,20 @@ __global__ void __launch_bounds__(TTHREADS, 1) gram_tf32_kernel(const Tf32Args g
     }
     const unsigned piece_dst = static_cast<unsigned>(slot0 * TSTRIDE + ch * 16);
 
-    auto issue_tail = [&](long long row, int st) {  // the ragged last chunk: guarded plain loads, same raw formats
-      unsigned char* rowb = smem + kRowsOff + st * TROWB;
-      const int valid = static_cast<int>(g.n - row);
-      if (tid < g.d) {
-        const bool is_int = g.col_i32[tid] != 0;
-        unsigned char* dst = smem + kStagingOff + st * (TF * TSTRIDE) + tid * TSTRIDE;
-        for (int k = 0; k < TKC; ++k) {
-          if (is_int) reinterpret_cast<int*>(dst)[k] = k < valid ? static_cast<const int*>(g.col_ptr[tid])[row + k] : 0;
-          else reinterpret_cast<double*>(dst)[k] = k < valid ? static_cast<const double*>(g.col_ptr[tid])[row + k] : 0.0;
-        }
-      }
-      if (tid < TKC) {
-        const bool in = tid < valid;
-        reinterpret_cast<double*>(rowb)[tid] = in ? g.label[row + tid] : 0.0;
-        reinterpret_cast<double*>(rowb + 128)[tid] = (in && g.has_dq) ? g.dq_price[row + tid] : 0.0;
-        reinterpret_cast<double*>(rowb + 256)[tid] = (in && g.weight != nullptr) ? g.weight[row + tid] : 0.0;
-        reinterpret_cast<int*>(rowb + 384)[tid] = (in && g.has_dq) ? g.dq_guest[row + tid] : 0;
-      }
-    };
     auto issue_stage = [&](long long it) {
       const long long chunk = blockIdx.x + it * static_cast<long long>(gridDim.x);
       const long long row = chunk * TKC;
       const int st = static_cast<int>(it % TSTAGES);
-      if (chunk >= full_chunks) {
-        issue_tail(row, st);
+      if (chunk >= full_chunks) {  // the ragged last chunk: guarded plain loads, same raw formats
+        const int valid = static_cast<int>(g.n - row);
+        if (tid < g.d) {
+          const bool is_int = g.col_i32[tid] != 0;
+          unsigned char* dst = smem + kStagingOff + st * (TF * TSTRIDE) + tid * TSTRIDE;
+          for (int k = 0; k < TKC; ++k) {
+            if (is_int) reinterpret_cast<int*>(dst)[k] = k < valid ? static_cast<const int*>(g.col_ptr[tid])[row + k] : 0;
+            else reinterpret_cast<double*>(dst)[k] = k < valid ? static_cast<const double*>(g.col_ptr[tid])[row + k] : 0.0;
+          }
+        }
         return;
       }
       const unsigned stg = sbase + kStagingOff + st * (TF * TSTRIDE) + piece_dst;
@@ -324,24 +406,17 @@ __global__ void __launch_bounds__(TTHREADS, 1) gram_tf32_kernel(const Tf32Args g
       for (int i = 0; i < 4; ++i) {
         if (((live >> i) & 1u) && !(g.experiment & 4)) cpa16(stg + 64 * i * TSTRIDE, src[i] + (((ints >> i) & 1u) ? row * 4 : row * 8));
       }
-      const unsigned rb = sbase + kRowsOff + st * TROWB;
-      if (tid < 8) cpa16(rb + tid * 16, g.label + row + tid * 2);
-      else if (tid < 16) { if (g.has_dq) cpa16(rb + 128 + (tid - 8) * 16, g.dq_price + row + (tid - 8) * 2); }
-      else if (tid < 24) { if (g.weight != nullptr) cpa16(rb + 256 + (tid - 16) * 16, g.weight + row + (tid - 16) * 2); }
-      else if (tid < 28) { if (g.has_dq) cpa16(rb + 384 + (tid - 24) * 16, g.dq_guest + row + (tid - 24) * 4); }
     };
 
     // TMEM accumulators -> the CTA's fp64 tile, stored column-major (P[col * 128 + row]) so that the 32 lanes of a warp,
-    // which hold 32 consecutive rows of one column, read-modify-write 256 contiguous bytes.  Column groups that lie
-    // entirely below the diagonal of a diagonal block are skipped.
+    // which hold 32 consecutive rows of one column, read-modify-write 256 contiguous bytes.
     auto drain = [&]() {
       tc_fence_after();
       const int quad = warp & 3, part = warp >> 2;
       const int groups = nb == 2 ? SCOLS / 32 : 4;
       const int row = quad * 32 + lane;
       for (int cg = part; cg < groups; cg += TCONV / 128) {
-        if (cg < 4 && cg < quad) continue;            // block (0,0), below the diagonal
-        if (cg >= 8 && cg - 8 < quad) continue;       // block (1,1), below the diagonal
+        if (!drain_needed(cg, quad)) continue;
         unsigned r[32];
         tc_ld32(tmem + (static_cast<unsigned>(quad * 32) << 16) + static_cast<unsigned>(cg * 32), r);
         double* dst = P + static_cast<size_t>(cg * 32) * 128 + row;
@@ -351,25 +426,16 @@ __global__ void __launch_bounds__(TTHREADS, 1) gram_tf32_kernel(const Tf32Args g
       tc_fence_before();
     };
 
-    // one value -> the two tf32 operands.  hi = fp32(z) rounded to tf32 (so the tensor core, which ignores the 13 low
-    // mantissa bits, sees exactly hi; rounding rather than truncating keeps the sign of lo random, which keeps the
-    // truncation of lo by the tensor core from adding up); lo = fp32(z - hi).
-    auto split = [](double z, float& h, float& l) {
-      const unsigned hb = (__float_as_uint(__double2float_rn(z)) + 0x1000u) & 0xffffe000u;  // round to tf32 (half up in magnitude)
-      h = __uint_as_float(hb);
-      // hb as a double, by exponent re-bias (no conversion instruction): exact for normal numbers, and values below
-      // 2^-126 do not matter here
-      const unsigned mag = hb & 0x7fffffffu;
-      const int hw = mag != 0u ? static_cast<int>((hb & 0x80000000u) | ((mag >> 3) + 0x38000000u)) : static_cast<int>(hb);
-      l = __double2float_rn(z - __hiloint2double(hw, 0));
-    };
-
     for (int s = 0; s < TSTAGES - 1; ++s) {
       if (s < my_iters) issue_stage(s);
       cpa_commit();
     }
 
-    double a1 = 0.0, ab = 0.0;  // sum w (x - c), sum w (x - c) y over this thread's rows of its feature
+    // sum z^2 (the diagonal of the Gram), sum s z = sum w (x - c) and sum z s (y - c_y) = sum w (x - c)(y - c_y) over this
+    // thread's rows of its feature stay off the tensor core: they are sums of one sign, or get multiplied by the centres
+    // afterwards, or carry the signal of the regression, and fp32 accumulation that rounds towards zero biases all three.
+    // Per chunk they are summed over 8 rows in fp32 (round to nearest), across chunks in fp64.
+    double zz = 0.0, a1 = 0.0, ab = 0.0;
     int since_drain = 0;
     unsigned drains = 0;
     const unsigned char* sp0 = smem + kStagingOff + feat * TSTRIDE + half * (own_int ? 32 : 64);
@@ -378,63 +444,78 @@ __global__ void __launch_bounds__(TTHREADS, 1) gram_tf32_kernel(const Tf32Args g
     for (long long it = 0; it < my_iters; ++it) {
       TICK(0);
       cpa_wait<TSTAGES - 2>();
-      TICK(1);
-      asm volatile("bar.sync 1, %0;" ::"n"(TCONV + 32) : "memory");  // chunk `it` has landed; the stage chunk it+3 goes into is free
-      TICK(2);
+      asm volatile("bar.sync 1, %0;" ::"n"(TCONV) : "memory");  // chunk `it` has landed; the stage chunk it+3 goes into is free
       if (it + TSTAGES - 1 < my_iters) issue_stage(it + TSTAGES - 1);
       cpa_commit();
-      TICK(3);
+      TICK(1);
 
       const int st = static_cast<int>(it % TSTAGES);
-      const int o = static_cast<int>(it & 1);
-      const double* scale = reinterpret_cast<const double*>(smem + kScaleOff) + o * (2 * TKC + 2) + half * 8;
-      mbar_wait(bar_scale0 + 8 * o, static_cast<unsigned>((it >> 1) & 1));                     // the row warp has written this chunk's factors
-      TICK(4);
-      if (it >= 2) mbar_wait(bar_free0 + 8 * o, static_cast<unsigned>(((it >> 1) - 1) & 1));  // the MMAs of chunk it-2 have read this buffer
+      const int o = static_cast<int>(it % TOPS);
+      const int b = static_cast<int>(it % TSCALE);
+      mbar_wait(bar_scale0 + 8 * b, static_cast<unsigned>((it / TSCALE) & 1));                 // the row warp has written this chunk's factors
+      if (it >= TOPS) mbar_wait(bar_free0 + 8 * o, static_cast<unsigned>(((it / TOPS) - 1) & 1));  // the MMAs of chunk it-2 have read this buffer
+      TICK(2);
 
-      TICK(5);
       if (active && !(g.experiment & 1)) {
+        const float* scale = reinterpret_cast<const float*>(smem + kScaleOff + b * TSCB);
         const unsigned char* sp = sp0 + st * (TF * TSTRIDE);
         unsigned char* ohi = op0 + o * (2 * TOPB);
         unsigned char* olo = ohi + TOPB;
-        const bool plain = reinterpret_cast<const int*>(scale - half * 8 + 2 * TKC)[0] != 0;
+        const bool plain = reinterpret_cast<const int*>(scale + 2 * TKC)[0] != 0;
+        float fzz = 0.f, fa1 = 0.f, fab = 0.f;
 #pragma unroll
         for (int q = 0; q < 2; ++q) {
-          double x[4];
+          float z[4];
           if (own_int) {
             const int4 v = *reinterpret_cast<const int4*>(sp + q * 16);
-            x[0] = v.x; x[1] = v.y; x[2] = v.z; x[3] = v.w;
+            z[0] = __double2float_rn(static_cast<double>(v.x) - centre);
+            z[1] = __double2float_rn(static_cast<double>(v.y) - centre);
+            z[2] = __double2float_rn(static_cast<double>(v.z) - centre);
+            z[3] = __double2float_rn(static_cast<double>(v.w) - centre);
           } else {
             const double2 u = *reinterpret_cast<const double2*>(sp + q * 32), v = *reinterpret_cast<const double2*>(sp + q * 32 + 16);
-            x[0] = u.x; x[1] = u.y; x[2] = v.x; x[3] = v.y;
+            z[0] = __double2float_rn(u.x - centre);
+            z[1] = __double2float_rn(u.y - centre);
+            z[2] = __double2float_rn(v.x - centre);
+            z[3] = __double2float_rn(v.y - centre);
           }
+          const float4 yc = *reinterpret_cast<const float4*>(scale + TKC + half * 8 + 4 * q);
+          const float ycv[4] = {yc.x, yc.y, yc.z, yc.w};
           float h[4], l[4];
-          if (plain) {  // no dropped row, no weights in this chunk
+          if (plain) {
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
-              const double z = x[k] - centre;
-              a1 += z;
-              ab = fma(scale[TKC + 4 * q + k], z, ab);
-              split(z, h[k], l[k]);
+              fzz = fmaf(z[k], z[k], fzz);
+              fa1 += z[k];
+              fab = fmaf(z[k], ycv[k], fab);
+              split_f32(z[k], h[k], l[k]);
             }
-          } else {
+          } else {  // uniform over the CTA: a dropped row or a weight in this chunk
+            const float4 sc = *reinterpret_cast<const float4*>(scale + half * 8 + 4 * q);
+            const float scv[4] = {sc.x, sc.y, sc.z, sc.w};
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
-              const double s = scale[4 * q + k];
-              const double z = s != 0.0 ? s * (x[k] - centre) : 0.0;  // dropped rows may hold NaN / Inf payload
-              a1 = fma(s, z, a1);
-              ab = fma(scale[TKC + 4 * q + k], z, ab);
-              split(z, h[k], l[k]);
+              const float zk = scv[k] != 0.f ? scv[k] * z[k] : 0.f;  // dropped rows may hold NaN / Inf payload
+              fzz = fmaf(zk, zk, fzz);
+              fa1 = fmaf(scv[k], zk, fa1);
+              fab = fmaf(zk, ycv[k], fab);
+              split_f32(zk, h[k], l[k]);
             }
           }
           *reinterpret_cast<float4*>(ohi + q * TLBO) = make_float4(h[0], h[1], h[2], h[3]);
           *reinterpret_cast<float4*>(olo + q * TLBO) = make_float4(l[0], l[1], l[2], l[3]);
         }
+        zz += static_cast<double>(fzz);
+        a1 += static_cast<double>(fa1);
+        ab += static_cast<double>(fab);
       }
       asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic-proxy stores -> visible to the tensor core's reads
       __syncwarp();
-      if (lane == 0) mbar_arrive(bar_ready0 + 8 * o);  // one arrival per warp
-      TICK(6);
+      if (lane == 0) {  // one arrival per warp
+        mbar_arrive(bar_ready0 + 8 * o);
+        mbar_arrive(bar_sfree0 + 8 * b);
+      }
+      TICK(3);
 
       if (++since_drain == g.drain_chunks || it == my_iters - 1) {
         mbar_wait(bar_drain, drains & 1u);
@@ -442,13 +523,16 @@ __global__ void __launch_bounds__(TTHREADS, 1) gram_tf32_kernel(const Tf32Args g
         drain();
         since_drain = 0;
       }
-      TICK(7);
+      TICK(4);
     }
-    if (prof && (warp == 0 || warp == 9)) printf("converter warp %d: loop %lld cpwait %lld barrier %lld issue %lld wait_scale %lld wait_free %lld convert+arrive %lld drain %lld\n", warp, tacc[0], tacc[1], tacc[2], tacc[3], tacc[4], tacc[5], tacc[6], tacc[7]);
+#ifdef DQ4ML_TF32_PROFILE
+    if (prof && (warp == 0 || warp == 9)) printf("converter warp %d: loop %lld cpwait+barrier+issue %lld wait_scale+free %lld convert+arrive %lld drain %lld\n", warp, tacc[0], tacc[1], tacc[2], tacc[3], tacc[4]);
+#endif
     cpa_wait<0>();
     if (active) {  // the two halves of a feature add up in either order to the same value
-      atomicAdd(&P[128 * SCOLS + feat], a1);
-      atomicAdd(&P[128 * SCOLS + TF + feat], ab);
+      atomicAdd(&P[kDiagOff + feat], zz);
+      atomicAdd(&P[kA1Off + feat], a1);
+      atomicAdd(&P[kAbOff + feat], ab);
     }
   }
   tc_fence_before();
@@ -457,14 +541,15 @@ __global__ void __launch_bounds__(TTHREADS, 1) gram_tf32_kernel(const Tf32Args g
 }
 
 // centre of column j = mean of its first min(n, 256) values (0 when that is not finite): one warp per column
-__global__ void tf32_centres_kernel(const void* const* col_ptr, const unsigned char* col_i32, int d, long long n,
-                                    double* centres) {
-  const int j = blockIdx.x, lane = threadIdx.x;
-  if (j >= d) return;
+__global__ void tf32_centres_kernel(const void* const* col_ptr, const unsigned char* col_i32, const double* label, int d,
+                                    long long n, double* centres) {
+  const int j = blockIdx.x, lane = threadIdx.x;  // j == d: the label
+  if (j > d) return;
   const long long m = n < 256 ? n : 256;
   double s = 0.0;
   for (long long r = lane; r < m; r += 32)
-    s += col_i32[j] ? static_cast<double>(static_cast<const int*>(col_ptr[j])[r]) : static_cast<const double*>(col_ptr[j])[r];
+    s += j == d ? label[r]
+                : (col_i32[j] ? static_cast<double>(static_cast<const int*>(col_ptr[j])[r]) : static_cast<const double*>(col_ptr[j])[r]);
 #pragma unroll
   for (int off = 16; off > 0; off >>= 1) s += __shfl_down_sync(0xffffffffu, s, off);
   if (lane == 0) {
@@ -473,35 +558,42 @@ __global__ void tf32_centres_kernel(const void* const* col_ptr, const unsigned c
   }
 }
 
+// where the tile keeps sum z_i z_j (i < j)
+__device__ __forceinline__ size_t tile_off(long long i, long long j) {
+  if (i < 128) return static_cast<size_t>(j) * 128 + i;             // columns [0, 256): column j, row i
+  return static_cast<size_t>(kColC + (j - 128)) * 128 + (i - 128);  // columns [256, 384)
+}
+
 // scalars and the two border vectors, folded over the CTAs in a fixed order; tot = [5 scalars, sum w (x_j - c_j) per j]
 __global__ void tf32_border_reduce_kernel(const double* __restrict__ partials, int grid, int d,
                                           const double* __restrict__ centres, double* __restrict__ tot,
                                           double* __restrict__ out) {
   const int e = blockIdx.x * blockDim.x + threadIdx.x;
   if (e >= 5 + 2 * d) return;
-  auto fold = [&](int off) {
+  auto fold = [&](size_t off) {
     double s = 0.0;
-    for (int b = 0; b < grid; ++b) s += partials[static_cast<size_t>(b) * kCtaDoubles + 128 * SCOLS + off];
+    for (int b = 0; b < grid; ++b) s += partials[static_cast<size_t>(b) * kCtaDoubles + off];
     return s;
   };
   if (e < 5) {
-    const double v = fold(2 * TF + e);
+    const double v = fold(kScalarOff + e);
     tot[e] = v;
     out[e] = v;
   } else if (e < 5 + d) {
     const int j = e - 5;
-    const double a = fold(j), w = fold(2 * TF + 1);
+    const double a = fold(kA1Off + j), w = fold(kScalarOff + 1);
     tot[5 + j] = a;
     out[e] = fma(centres[j], w, a);  // sum w x_j
   } else {
+    // sum w x_j y = sum w (x_j - c_j)(y - c_y) + c_y sum w (x_j - c_j) + c_j sum w y
     const int j = e - 5 - d;
-    const double v = fold(TF + j), by = fold(2 * TF + 3);
-    out[e] = fma(centres[j], by, v);  // sum w x_j y
+    const double v = fold(kAbOff + j), a = fold(kA1Off + j), by = fold(kScalarOff + 3);
+    out[e] = v + centres[d] * a + centres[j] * by;
   }
 }
 
-// packed upper triangle: sum w x_i x_j = T_ij + c_j A'_i + c_i A'_j + c_i c_j W, with T the tensor-core tile and A' the
-// centred column sums
+// packed upper triangle: sum w x_i x_j = T_ij + c_j A'_i + c_i A'_j + c_i c_j W, with T the tensor-core tile (the exact
+// fp64 sums on the diagonal) and A' the centred column sums
 __global__ void tf32_pack_kernel(const double* __restrict__ partials, int grid, int d, const double* __restrict__ centres,
                                  const double* __restrict__ tot, double* __restrict__ out) {
   const long long q = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
@@ -511,7 +603,7 @@ __global__ void tf32_pack_kernel(const double* __restrict__ partials, int grid, 
   while (j * (j + 1) / 2 > q) --j;
   while ((j + 1) * (j + 2) / 2 <= q) ++j;
   const long long i = q - j * (j + 1) / 2;  // i <= j
-  const size_t off = i < 128 ? static_cast<size_t>(j) * 128 + i : static_cast<size_t>(256 + (j - 128)) * 128 + (i - 128);  // column-major tile
+  const size_t off = i == j ? static_cast<size_t>(kDiagOff + i) : tile_off(i, j);
   double t = 0.0;
   for (int b = 0; b < grid; ++b) t += partials[static_cast<size_t>(b) * kCtaDoubles + off];
   const double ci = centres[i], cj = centres[j];
@@ -535,7 +627,7 @@ int gram_tf32_wls_moments(dq4ml_ctx* ctx, const std::vector<const void*>& col_pt
   if (grid > chunks) grid = static_cast<int>(chunks);
   if (grid < 1) grid = 1;
   const size_t table_bytes = (static_cast<size_t>(d) * 9 + 255) & ~static_cast<size_t>(255);
-  const size_t centre_bytes = TF * sizeof(double);
+  const size_t centre_bytes = (TF + 8) * sizeof(double);  // features, then the label
   const size_t tot_bytes = (5 + TF + 3) * sizeof(double);
   const size_t part_bytes = static_cast<size_t>(grid) * kCtaDoubles * sizeof(double);
   const size_t out_bytes = static_cast<size_t>(len) * sizeof(double);
@@ -587,7 +679,7 @@ int gram_tf32_wls_moments(dq4ml_ctx* ctx, const std::vector<const void*>& col_pt
   g.t.min_guest = dq.params.min_guest;
   g.has_dq = dq.guest != nullptr ? 1 : 0;
   g.n = n;
-  int drain_rows = 1024;  // fp32 accumulation span; see the header comment
+  int drain_rows = 2048;  // fp32 accumulation span; see the header comment
   if (const char* env = getenv("DQ4ML_TF32_DRAIN_ROWS")) { const int v = atoi(env); if (v >= TKC) drain_rows = v; }
   g.drain_chunks = drain_rows / TKC;
   g.swap_offsets = getenv("DQ4ML_TF32_SWAP_OFFSETS") != nullptr ? 1 : 0;
@@ -600,7 +692,7 @@ int gram_tf32_wls_moments(dq4ml_ctx* ctx, const std::vector<const void*>& col_pt
     attr_set[ctx->device] = true;
   }
   if (ctx->pass_timing) cudaEventRecord(ctx->pass_ev0, ctx->stream);
-  tf32_centres_kernel<<<d, 32, 0, ctx->stream>>>(d_ptrs, d_i32, d, n, d_centres);
+  tf32_centres_kernel<<<d + 1, 32, 0, ctx->stream>>>(d_ptrs, d_i32, label, d, n, d_centres);
   if ((e = cudaGetLastError()) != cudaSuccess) return fail(e, "tf32 centres kernel");
   if ((e = cudaMemsetAsync(d_part, 0, part_bytes, ctx->stream)) != cudaSuccess) return fail(e, "tf32 tile clear");
   gram_tf32_kernel<<<grid, TTHREADS, kTf32Smem, ctx->stream>>>(g);
