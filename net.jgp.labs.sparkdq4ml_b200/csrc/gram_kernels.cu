@@ -83,6 +83,9 @@ __device__ __forceinline__ void dmma884(double (&c)[2], double a, double b) {
   asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};" : "+d"(c[0]), "+d"(c[1]) : "d"(a), "d"(b));
 }
 
+// W: instance weights present.  A template parameter so that the unweighted kernel carries none of the weight code
+// (as a run-time branch it cost 5 % at 62.5 M x 256: 178.5 ms against 169.9 ms).
+template <bool W>
 __global__ void __launch_bounds__(GTHREADS, 2) gram_tile_kernel(const GramArgs g) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   GramStage* st = reinterpret_cast<GramStage*>(smem_raw);
@@ -165,7 +168,7 @@ __global__ void __launch_bounds__(GTHREADS, 2) gram_tile_kernel(const GramArgs g
       if (tid >= 32 && tid < 48) cp_async16(&S.dqp[(tid - 32) * 2], g.dq_price + row + (tid - 32) * 2);
       if (tid >= 64 && tid < 72) cp_async16(&S.dqg[(tid - 64) * 4], g.dq_guest + row + (tid - 64) * 4);
     }
-    if (g.weight != nullptr && tid >= 96 && tid < 112) cp_async16(&S.wt[(tid - 96) * 2], g.weight + row + (tid - 96) * 2);
+    if (W && tid >= 96 && tid < 112) cp_async16(&S.wt[(tid - 96) * 2], g.weight + row + (tid - 96) * 2);
   };
 
   const int wm = warp >> 1, wn = warp & 1;
@@ -195,13 +198,17 @@ __global__ void __launch_bounds__(GTHREADS, 2) gram_tile_kernel(const GramArgs g
       if (lane == 0) *mask_slot = static_cast<int>(m);
       // WeightedLeastSquares.Aggregator: wSum += w, wwSum += w^2, bSum += w y, aSum += w x, aaSum += w x x^T.  Every row of
       // the chunk is scaled by sqrt(w) below, so Z^T Z carries the weights; count and wwSum ride in two more border columns.
-      const double w = keep ? (g.weight != nullptr ? S.wt[lane] : 1.0) : 0.0;
-      const double sw = g.weight != nullptr ? sqrt(w) : w;  // w is 0 or 1 without a weight column
-      if (g.weight != nullptr) S.wt[lane] = sw;
-      if (diag) {
-        S.border[1][swz(1, lane)] = sw;
-        S.border[2][swz(2, lane)] = w;
-        S.border[3][swz(3, lane)] = keep ? 1.0 : 0.0;
+      if constexpr (W) {
+        const double w = keep ? S.wt[lane] : 0.0;
+        const double sw = sqrt(w);
+        S.wt[lane] = sw;
+        if (diag) {
+          S.border[1][swz(1, lane)] = sw;
+          S.border[2][swz(2, lane)] = w;
+          S.border[3][swz(3, lane)] = keep ? 1.0 : 0.0;
+        }
+      } else {
+        if (diag) S.border[1][swz(1, lane)] = keep ? 1.0 : 0.0;  // count = wSum = wwSum: one border column is enough
       }
     }
     __syncthreads();
@@ -215,7 +222,7 @@ __global__ void __launch_bounds__(GTHREADS, 2) gram_tile_kernel(const GramArgs g
       }
       __syncthreads();
     }
-    if (g.weight != nullptr) {  // scale every row of both panels and of y by sqrt(w): the same 16-byte pieces this thread staged
+    if constexpr (W) {  // scale every row of both panels and of y by sqrt(w): the same 16-byte pieces this thread staged
       const int pch = tid & 15, slot_base = tid >> 4;
       const int lch = pch ^ ((slot_base & 7) << 1);  // logical chunk held at physical position pch: rows 2 lch, 2 lch + 1
       const double s0 = S.wt[2 * lch], s1 = S.wt[2 * lch + 1];
@@ -292,7 +299,7 @@ __global__ void __launch_bounds__(GTHREADS, 2) gram_tile_kernel(const GramArgs g
       S.border[0][swz(0, tid)] = (diag && tid < tail_rows) ? g.label[row0 + tid] : 0.0;
       S.dqg[tid] = (g.has_dq && tid < tail_rows) ? g.dq_guest[row0 + tid] : 0;
       S.dqp[tid] = (g.has_dq && tid < tail_rows) ? g.dq_price[row0 + tid] : 0.0;
-      if (g.weight != nullptr) S.wt[tid] = tid < tail_rows ? g.weight[row0 + tid] : 0.0;
+      if (W) S.wt[tid] = tid < tail_rows ? g.weight[row0 + tid] : 0.0;
     }
     __syncthreads();
     consume(S, &s_meta[4], false, tail_rows);
@@ -320,14 +327,17 @@ __global__ void __launch_bounds__(GTHREADS, 2) gram_tile_kernel(const GramArgs g
 // Sums the row slices in a fixed order and lays the result out as
 // [count, wSum, wwSum, bSum, bbSum, aSum[d], abSum[d], aaSum packed upper column-major].
 __global__ void __launch_bounds__(256) gram_reduce_kernel(const double* __restrict__ partials, int d, int nb, int kinds,
-                                                          int splits, long long len, double* __restrict__ out) {
+                                                          int splits, long long len, int weighted,
+                                                          double* __restrict__ out) {
   const long long e = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
   if (e >= len) return;
   int bi, bj, off;
   if (e < 5) {
     bi = bj = 0;
     // corner = [sqrt(w) y, sqrt(w), w, keep]^T [same]: [3][3] = count, [1][1] = wSum, [2][2] = wwSum, [0][1] = bSum, [0][0] = bbSum
-    off = GT * GT + GT * 8 + (e == 0 ? 3 * 8 + 3 : (e == 1 ? 1 * 8 + 1 : (e == 2 ? 2 * 8 + 2 : (e == 3 ? 0 * 8 + 1 : 0))));
+    // (unweighted: only column 1 = keep is written, and [1][1] serves count, wSum and wwSum)
+    const int diag3 = weighted ? (e == 0 ? 3 * 8 + 3 : (e == 1 ? 1 * 8 + 1 : 2 * 8 + 2)) : 1 * 8 + 1;
+    off = GT * GT + GT * 8 + (e < 3 ? diag3 : (e == 3 ? 0 * 8 + 1 : 0));
   } else if (e < 5 + 2LL * d) {
     const int j = static_cast<int>((e - 5) % d);
     const bool ab = (e - 5) >= d;
@@ -416,15 +426,18 @@ int gram_wls_moments(dq4ml_ctx* ctx, const std::vector<const void*>& col_ptrs, c
   g.partials = d_part;
   static bool attr_set[64] = {false};
   if (ctx->device < 64 && !attr_set[ctx->device]) {
-    if ((e = cudaFuncSetAttribute(gram_tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(kGramSmem))) != cudaSuccess)
+    if ((e = cudaFuncSetAttribute(gram_tile_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(kGramSmem))) != cudaSuccess)
+      return fail(e, "gram smem attribute");
+    if ((e = cudaFuncSetAttribute(gram_tile_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(kGramSmem))) != cudaSuccess)
       return fail(e, "gram smem attribute");
     attr_set[ctx->device] = true;
   }
   if (ctx->pass_timing) cudaEventRecord(ctx->pass_ev0, ctx->stream);
-  gram_tile_kernel<<<static_cast<unsigned>(splits * kinds), GTHREADS, kGramSmem, ctx->stream>>>(g);
+  if (weight != nullptr) gram_tile_kernel<true><<<static_cast<unsigned>(splits * kinds), GTHREADS, kGramSmem, ctx->stream>>>(g);
+  else gram_tile_kernel<false><<<static_cast<unsigned>(splits * kinds), GTHREADS, kGramSmem, ctx->stream>>>(g);
   if ((e = cudaGetLastError()) != cudaSuccess) return fail(e, "gram tile kernel");
   ++ctx->launches;
-  gram_reduce_kernel<<<static_cast<unsigned>((len + 255) / 256), 256, 0, ctx->stream>>>(d_part, d, nb, kinds, static_cast<int>(splits), len, d_out);
+  gram_reduce_kernel<<<static_cast<unsigned>((len + 255) / 256), 256, 0, ctx->stream>>>(d_part, d, nb, kinds, static_cast<int>(splits), len, weight != nullptr ? 1 : 0, d_out);
   if ((e = cudaGetLastError()) != cudaSuccess) return fail(e, "gram reduce kernel");
   ++ctx->launches;
   if (ctx->pass_timing) {

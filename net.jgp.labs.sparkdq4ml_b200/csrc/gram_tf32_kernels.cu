@@ -164,13 +164,40 @@ __host__ __device__ constexpr unsigned umma_idesc_tf32(int n) {
   return (1u << 4) | (2u << 7) | (2u << 10) | (static_cast<unsigned>(n >> 3) << 17) | (static_cast<unsigned>(128 >> 4) << 24);
 }
 
-// One fp32 value -> the two tf32 operands (Dekker's split with 2^13 + 1): hi carries the 11 leading bits of f, rounded
-// to nearest, so the tensor core -- which ignores the 13 low mantissa bits -- sees exactly hi; lo = f - hi is exact in
-// fp32, and its own truncation by the tensor core is a 2^-21 relative effect of random sign.  NaN / Inf stay NaN.
-__device__ __forceinline__ void split_f32(float f, float& h, float& l) {
-  const float t = __fmul_rn(f, 8193.0f);  // the _rn intrinsics keep the compiler from contracting this into an FMA
-  h = __fsub_rn(t, __fsub_rn(t, f));
-  l = __fsub_rn(f, h);
+// One fp32 value -> the two tf32 operands (Dekker's split with 2^13 + 1, see split2 below): hi carries the 11 leading
+// bits of f, rounded to nearest, so the tensor core -- which ignores the 13 low mantissa bits -- sees exactly hi;
+// lo = f - hi is exact in fp32, and its own truncation by the tensor core is a 2^-21 relative effect of random sign.
+// NaN / Inf stay NaN.
+// packed fp32 pairs (FADD2 / FMUL2 / FFMA2 on sm_100): half the instruction count for the split and the three sums
+using f32x2 = unsigned long long;
+__device__ __forceinline__ f32x2 pack2(float lo, float hi) {
+  f32x2 r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+  return r;
+}
+__device__ __forceinline__ void unpack2(f32x2 v, float& lo, float& hi) { asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v)); }
+__device__ __forceinline__ f32x2 add2(f32x2 a, f32x2 b) {
+  f32x2 r;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+__device__ __forceinline__ f32x2 sub2(f32x2 a, f32x2 b) {
+  f32x2 r;
+  asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+__device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c) {
+  f32x2 r;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+  return r;
+}
+// split_f32 on a pair.  The product with 2^13 + 1 is taken with scalar __fmul_rn: ptxas contracts a packed
+// mul.rn.f32x2 followed by sub.rn.f32x2 into one FFMA2, which turns the split into hi = f, lo = 0.
+__device__ __forceinline__ void split2(float f0, float f1, f32x2& h, f32x2& l) {
+  const f32x2 f = pack2(f0, f1);
+  const f32x2 t = pack2(__fmul_rn(f0, 8193.0f), __fmul_rn(f1, 8193.0f));
+  h = sub2(t, sub2(t, f));
+  l = sub2(f, h);
 }
 
 #ifdef DQ4ML_TF32_PROFILE
@@ -248,7 +275,7 @@ __global__ void __launch_bounds__(TTHREADS, 1) gram_tf32_kernel(const Tf32Args g
       const unsigned lbo = g.swap_offsets ? TSBO : TLBO, sbo = g.swap_offsets ? TLBO : TSBO;
       const unsigned idesc_row0 = umma_idesc_tf32(nb == 2 ? 256 : 128), idesc_blk = umma_idesc_tf32(128);
       int since_drain = 0;
-      for (long long it = 0; it < my_iters; ++it) {
+      for (unsigned it = 0; it < my_iters; ++it) {
         const int o = static_cast<int>(it % TOPS);
         TICK(0);
         mbar_wait(bar_ready0 + 8 * o, static_cast<unsigned>((it / TOPS) & 1));
@@ -283,7 +310,7 @@ __global__ void __launch_bounds__(TTHREADS, 1) gram_tf32_kernel(const Tf32Args g
     // Owns the per-row columns (label, DQ price / guest, weight): its own cp.async ring, the keep mask of the DQ rules,
     // the per-row factors s = sqrt(w) keep and s (y - c_y) the converters multiply with, and the five scalar sums.  It
     // runs up to TSCALE chunks ahead of the converters.
-    auto issue_rows = [&](long long it) {
+    auto issue_rows = [&](unsigned it) {
       const long long row = (blockIdx.x + it * static_cast<long long>(gridDim.x)) * TKC;
       unsigned char* rowb = smem + kRowsOff + static_cast<int>(it % TROWST) * TROWB;
       if (row + TKC <= g.n) {
@@ -306,7 +333,7 @@ __global__ void __launch_bounds__(TTHREADS, 1) gram_tf32_kernel(const Tf32Args g
     }
     double cnt = 0.0, wsum = 0.0, wwsum = 0.0, bsum = 0.0, bbsum = 0.0;
     const double ycentre = g.centres[g.d];
-    for (long long it = 0; it < my_iters; ++it) {
+    for (unsigned it = 0; it < my_iters; ++it) {
       TICK(0);
       cpa_wait<TROWST - 2>();
       __syncwarp();
@@ -385,7 +412,7 @@ __global__ void __launch_bounds__(TTHREADS, 1) gram_tf32_kernel(const Tf32Args g
     }
     const unsigned piece_dst = static_cast<unsigned>(slot0 * TSTRIDE + ch * 16);
 
-    auto issue_stage = [&](long long it) {
+    auto issue_stage = [&](unsigned it) {
       const long long chunk = blockIdx.x + it * static_cast<long long>(gridDim.x);
       const long long row = chunk * TKC;
       const int st = static_cast<int>(it % TSTAGES);
@@ -441,7 +468,7 @@ __global__ void __launch_bounds__(TTHREADS, 1) gram_tf32_kernel(const Tf32Args g
     const unsigned char* sp0 = smem + kStagingOff + feat * TSTRIDE + half * (own_int ? 32 : 64);
     unsigned char* op0 = smem + kOpsOff + (feat >> 3) * TSBO + (feat & 7) * 16 + half * 2 * TLBO;
 
-    for (long long it = 0; it < my_iters; ++it) {
+    for (unsigned it = 0; it < my_iters; ++it) {
       TICK(0);
       cpa_wait<TSTAGES - 2>();
       asm volatile("bar.sync 1, %0;" ::"n"(TCONV) : "memory");  // chunk `it` has landed; the stage chunk it+3 goes into is free
@@ -462,7 +489,7 @@ __global__ void __launch_bounds__(TTHREADS, 1) gram_tf32_kernel(const Tf32Args g
         unsigned char* ohi = op0 + o * (2 * TOPB);
         unsigned char* olo = ohi + TOPB;
         const bool plain = reinterpret_cast<const int*>(scale + 2 * TKC)[0] != 0;
-        float fzz = 0.f, fa1 = 0.f, fab = 0.f;
+        f32x2 pzz = 0ull, pa1 = 0ull, pab = 0ull;  // (0.f, 0.f)
 #pragma unroll
         for (int q = 0; q < 2; ++q) {
           float z[4];
@@ -479,35 +506,41 @@ __global__ void __launch_bounds__(TTHREADS, 1) gram_tf32_kernel(const Tf32Args g
             z[2] = __double2float_rn(v.x - centre);
             z[3] = __double2float_rn(v.y - centre);
           }
-          const float4 yc = *reinterpret_cast<const float4*>(scale + TKC + half * 8 + 4 * q);
-          const float ycv[4] = {yc.x, yc.y, yc.z, yc.w};
-          float h[4], l[4];
+          const ulonglong2 yc = *reinterpret_cast<const ulonglong2*>(scale + TKC + half * 8 + 4 * q);  // s (y - c_y) of the 4 rows
+          f32x2 z01, z23;
           if (plain) {
-#pragma unroll
-            for (int k = 0; k < 4; ++k) {
-              fzz = fmaf(z[k], z[k], fzz);
-              fa1 += z[k];
-              fab = fmaf(z[k], ycv[k], fab);
-              split_f32(z[k], h[k], l[k]);
-            }
+            z01 = pack2(z[0], z[1]);
+            z23 = pack2(z[2], z[3]);
+            pa1 = add2(pa1, add2(z01, z23));
           } else {  // uniform over the CTA: a dropped row or a weight in this chunk
             const float4 sc = *reinterpret_cast<const float4*>(scale + half * 8 + 4 * q);
-            const float scv[4] = {sc.x, sc.y, sc.z, sc.w};
-#pragma unroll
-            for (int k = 0; k < 4; ++k) {
-              const float zk = scv[k] != 0.f ? scv[k] * z[k] : 0.f;  // dropped rows may hold NaN / Inf payload
-              fzz = fmaf(zk, zk, fzz);
-              fa1 = fmaf(scv[k], zk, fa1);
-              fab = fmaf(zk, ycv[k], fab);
-              split_f32(zk, h[k], l[k]);
-            }
+            // dropped rows may hold NaN / Inf payload: they become exact zeros
+            z[0] = sc.x != 0.f ? sc.x * z[0] : 0.f;
+            z[1] = sc.y != 0.f ? sc.y * z[1] : 0.f;
+            z[2] = sc.z != 0.f ? sc.z * z[2] : 0.f;
+            z[3] = sc.w != 0.f ? sc.w * z[3] : 0.f;
+            z01 = pack2(z[0], z[1]);
+            z23 = pack2(z[2], z[3]);
+            pa1 = fma2(pack2(sc.x, sc.y), z01, pa1);
+            pa1 = fma2(pack2(sc.z, sc.w), z23, pa1);
           }
-          *reinterpret_cast<float4*>(ohi + q * TLBO) = make_float4(h[0], h[1], h[2], h[3]);
-          *reinterpret_cast<float4*>(olo + q * TLBO) = make_float4(l[0], l[1], l[2], l[3]);
+          pzz = fma2(z01, z01, pzz);
+          pzz = fma2(z23, z23, pzz);
+          pab = fma2(z01, yc.x, pab);
+          pab = fma2(z23, yc.y, pab);
+          f32x2 h01, l01, h23, l23;
+          split2(z[0], z[1], h01, l01);
+          split2(z[2], z[3], h23, l23);
+          *reinterpret_cast<ulonglong2*>(ohi + q * TLBO) = make_ulonglong2(h01, h23);
+          *reinterpret_cast<ulonglong2*>(olo + q * TLBO) = make_ulonglong2(l01, l23);
         }
-        zz += static_cast<double>(fzz);
-        a1 += static_cast<double>(fa1);
-        ab += static_cast<double>(fab);
+        float e0, e1;
+        unpack2(pzz, e0, e1);
+        zz += static_cast<double>(e0 + e1);
+        unpack2(pa1, e0, e1);
+        a1 += static_cast<double>(e0 + e1);
+        unpack2(pab, e0, e1);
+        ab += static_cast<double>(e0 + e1);
       }
       asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic-proxy stores -> visible to the tensor core's reads
       __syncwarp();
