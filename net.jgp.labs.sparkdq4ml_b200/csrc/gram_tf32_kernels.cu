@@ -35,11 +35,15 @@
 //     groups below the diagonal of a diagonal block are skipped.
 // A small kernel pair folds the per-CTA tiles in a fixed order and rebuilds the public moment layout.
 //
-// Where the time goes (62.5 M x 256: 50 ms = 0.39 of the HBM roofline, tensor pipe 40 % busy, vs 178 ms for the fp64
-// kernel): the converter warps.  Each executes ~240 instructions per chunk (conversion ~140, synchronisation and load
-// issue ~100) as a mostly serial stream, four warps per scheduler; ablations (DQ4ML_TF32_EXPERIMENT) put loads alone at
-// 30 ms, conversion alone at 32 ms, MMAs alone at 37 ms.  Next: packed f32x2 arithmetic for the split and the sums,
-// wrap-around counters instead of 64-bit modulo, two chunks per row-warp iteration.
+// Where the time goes (62.5 M x 256: 48.5 ms = 0.40 of the HBM roofline, tensor pipe 40 % busy, vs 170 ms for the fp64
+// kernel): the converter warps.  Each executes ~200 instructions per chunk (conversion ~110 with the packed f32x2
+// arithmetic, synchronisation and load issue ~90) as a mostly serial stream, four warps per scheduler; ablations
+// (DQ4ML_TF32_EXPERIMENT) put loads alone at 30 ms, conversion alone at 32 ms, MMAs alone at 37 ms, and the bare
+// synchronisation skeleton at 20 ms -- a lone warp pays ~8 cycles per dependent instruction, so the row warp's ~200
+// instructions per chunk bound the skeleton.  History: 83 ms (one role per thread, 256 threads, row-major drain)
+// -> 66 (MMA warp, column-major drain) -> 61 (512 converter threads, row warp) -> 50 (sums off the tensor core,
+// own row ring) -> 48.5 (packed arithmetic).  Next: two chunks per row-warp iteration, a TMA tensor-map load path
+// for uniformly strided tables (no per-thread load issue), 32-row chunks once the raw staging is gone.
 #include <algorithm>
 #include <cstdio>
 #include <cstdlib>
