@@ -21,8 +21,10 @@
 //
 // Shape of the kernel: one persistent CTA per SM (all 512 TMEM columns, ~217 KB of shared memory), 18 warps:
 //   - 16 loader / converter warps.  Rows are taken in chunks of 16.  A 4-stage cp.async ring stages the raw fp64 / int32
-//     pieces of all columns (8 neighbouring threads fetch one 128-byte line); after one named barrier per chunk, two
-//     threads per feature convert 8 rows each and write the hi and lo operands in the canonical no-swizzle K-major UMMA
+//     pieces of the columns; every warp fetches the 16 features it converts (8 neighbouring lanes fetch one 128-byte
+//     line), so a __syncwarp is all that stands between the copies and their use (a CTA-wide barrier there measured
+//     the same: the warps are paced by the mbarriers below, not by each other).  Two threads per feature convert 8
+//     rows each and write the hi and lo operands in the canonical no-swizzle K-major UMMA
 //     layout (8-row x 16-byte core matrices; LBO = 128 B between the K chunks, SBO = 512 B between 8-feature groups),
 //     then fence.proxy.async and one mbarrier arrival per warp;
 //   - the MMA warp: one thread waits for the operands of a chunk and issues, per 8 rows and per split term,
@@ -400,13 +402,15 @@ __global__ void __launch_bounds__(TTHREADS, 1) gram_tf32_kernel(const Tf32Args g
     const bool active = feat < g.d;
     const bool own_int = active && g.col_i32[feat] != 0;
     const double centre = active ? g.centres[feat] : 0.0;
-    // loader: 16-byte piece `ch` of the column slots (tid >> 3) + 64 i, so that 8 neighbouring threads fetch one 128-byte line
-    const int ch = tid & 7, slot0 = tid >> 3;
+    // loader: every warp fetches exactly the 16 features it converts (so that a __syncwarp, not a CTA-wide barrier,
+    // stands between the copies and their use, and the warps may drift apart by as much as the mbarriers allow):
+    // 16-byte piece `ch` of the column slots 16 warp + (lane >> 3) + 4 i; 8 neighbouring lanes fetch one 128-byte line
+    const int ch = lane & 7, slot0 = warp * 16 + (lane >> 3);
     const char* src[4];
     unsigned live = 0, ints = 0;
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
-      const int slot = slot0 + 64 * i;
+      const int slot = slot0 + 4 * i;
       const bool on = slot < g.d;
       const char* base = on ? static_cast<const char*>(g.col_ptr[slot]) : nullptr;
       const bool is_int = on && g.col_i32[slot] != 0;
@@ -422,12 +426,11 @@ __global__ void __launch_bounds__(TTHREADS, 1) gram_tf32_kernel(const Tf32Args g
       const int st = static_cast<int>(it % TSTAGES);
       if (chunk >= full_chunks) {  // the ragged last chunk: guarded plain loads, same raw formats
         const int valid = static_cast<int>(g.n - row);
-        if (tid < g.d) {
-          const bool is_int = g.col_i32[tid] != 0;
-          unsigned char* dst = smem + kStagingOff + st * (TF * TSTRIDE) + tid * TSTRIDE;
+        if (half == 0 && active) {  // lanes 0..15 fill the rows of the warp's own 16 features
+          unsigned char* dst = smem + kStagingOff + st * (TF * TSTRIDE) + feat * TSTRIDE;
           for (int k = 0; k < TKC; ++k) {
-            if (is_int) reinterpret_cast<int*>(dst)[k] = k < valid ? static_cast<const int*>(g.col_ptr[tid])[row + k] : 0;
-            else reinterpret_cast<double*>(dst)[k] = k < valid ? static_cast<const double*>(g.col_ptr[tid])[row + k] : 0.0;
+            if (own_int) reinterpret_cast<int*>(dst)[k] = k < valid ? static_cast<const int*>(g.col_ptr[feat])[row + k] : 0;
+            else reinterpret_cast<double*>(dst)[k] = k < valid ? static_cast<const double*>(g.col_ptr[feat])[row + k] : 0.0;
           }
         }
         return;
@@ -435,7 +438,7 @@ __global__ void __launch_bounds__(TTHREADS, 1) gram_tf32_kernel(const Tf32Args g
       const unsigned stg = sbase + kStagingOff + st * (TF * TSTRIDE) + piece_dst;
 #pragma unroll
       for (int i = 0; i < 4; ++i) {
-        if (((live >> i) & 1u) && !(g.experiment & 4)) cpa16(stg + 64 * i * TSTRIDE, src[i] + (((ints >> i) & 1u) ? row * 4 : row * 8));
+        if (((live >> i) & 1u) && !(g.experiment & 4)) cpa16(stg + 4 * i * TSTRIDE, src[i] + (((ints >> i) & 1u) ? row * 4 : row * 8));
       }
     };
 
@@ -475,7 +478,7 @@ __global__ void __launch_bounds__(TTHREADS, 1) gram_tf32_kernel(const Tf32Args g
     for (unsigned it = 0; it < my_iters; ++it) {
       TICK(0);
       cpa_wait<TSTAGES - 2>();
-      asm volatile("bar.sync 1, %0;" ::"n"(TCONV) : "memory");  // chunk `it` has landed; the stage chunk it+3 goes into is free
+      __syncwarp();  // chunk `it` has landed for this warp's features; the stage chunk it+3 goes into was read by this warp only
       if (it + TSTAGES - 1 < my_iters) issue_stage(it + TSTAGES - 1);
       cpa_commit();
       TICK(1);
