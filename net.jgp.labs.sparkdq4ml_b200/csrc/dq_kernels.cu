@@ -90,6 +90,9 @@ __device__ __forceinline__ void st_state(unsigned long long* p, unsigned long lo
 }
 
 // One short-lived CTA per tile; blockIdx order is dispatch order, so every predecessor of a running tile has started.
+// (Two consecutive tiles per CTA with both tiles' loads issued up front -- to hide the second tile's DRAM latency behind
+// the first tile's look-back -- is 70x slower: tile 2b+1 publishes its count only after tile 2b is completely done,
+// which chains every CTA behind its predecessor.  Publishing both counts first removes the chain but also the overlap.)
 // Measured alternatives (round 1, 10^9 rows): 512 x 4-row threads with per-thread stores 0.33 of the HBM roofline;
 // 256 threads x 16 rows (128-bit loads, shuffle scans, shared-memory staging) 0.51; persistent CTAs with cp.async
 // prefetch of the next tile and a ticket counter 0.20 (every round turns into a grid-wide barrier on the slowest CTA);
