@@ -44,7 +44,10 @@
 // synchronisation skeleton at 20 ms -- a lone warp pays ~8 cycles per dependent instruction, so the row warp's ~200
 // instructions per chunk bound the skeleton.  History: 83 ms (one role per thread, 256 threads, row-major drain)
 // -> 66 (MMA warp, column-major drain) -> 61 (512 converter threads, row warp) -> 50 (sums off the tensor core,
-// own row ring) -> 48.5 (packed arithmetic).  Next: two chunks per row-warp iteration, a TMA tensor-map load path
+// own row ring) -> 48.5 (packed arithmetic).  Per chunk a converter warp spends ~390 cycles on load issue, ~380 waiting
+// for the row factors / a free operand buffer, ~1700 in the conversion and ~270 (amortised) in the drain.  Tried and
+// dropped: fp64 <-> fp32 conversion with integer instructions instead of F2F (55.7 ms: the phase follows its instruction
+// count, not the conversion pipe); three operand buffers with three staging stages (same time).  Next: two chunks per row-warp iteration, a TMA tensor-map load path
 // for uniformly strided tables (no per-thread load issue), 32-row chunks once the raw staging is gone.
 #include <algorithm>
 #include <cstdio>
