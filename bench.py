@@ -256,7 +256,7 @@ def run_ours(args):
                 "steps": e2e_steps, "ms_per_step": e2e_ms / e2e_steps,
                 "note": "pinned host columns -> dq4ml_linreg_fit; H2D staging + pass + D2H of the moments inside the timed region"},
         "gpu_launches": int(launches),
-        "roofline": {"bound": "hbm", "kernel": "stream_reduce_kernel<WlsOp<1>,1,4,kDqLab> (fused DQ + WLS moments)",
+        "roofline": {"bound": "hbm", "kernel": "stream_reduce_kernel<WlsOp<1>,1,8,kDqLab> (fused DQ + WLS moments)",
                      "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                      "traffic": ncu_traffic_per_launch("wls_moments_d1_lab"), "peak_source": peak_src,
                      "algorithmic_bytes_per_launch": BYTES_PER_ROW * n, "avg_launch_ms": per_launch_ms,
