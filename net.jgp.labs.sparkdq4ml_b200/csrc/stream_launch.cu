@@ -1,6 +1,6 @@
 // stream_launch.cu -- instantiates stream_reduce_kernel for every (op, column-group bucket, DQ mode) the path uses
-// and picks one at run time.  Buckets 1,2,4,8 stream 4 rows per thread per tile, buckets 16,32 stream 2 (register
-// budget); grids are sized to (CTAs resident per SM) x (SM count) so the whole pass is one wave of persistent CTAs.
+// and picks one at run time.  Buckets 1,2 stream 8 rows per thread per tile, buckets 4,8,16 stream 4, bucket 32 streams 2
+// (register budget); grids are sized to (CTAs resident per SM) x (SM count) so the whole pass is one wave of persistent CTAs.
 #include <cstdlib>
 #include <map>
 #include <mutex>
@@ -117,11 +117,8 @@ EvalOp<DMAX> make_eval(const EvalConsts& c) {
   return op;
 }
 
-template <int DMAX>
-cudaError_t launch_bucket(StreamOpKind kind, const PassArgs& a, const void* host_consts) {
-  // rows per thread per tile: what keeps ~100 bytes per thread in flight without spilling (tools/k2_variants.cu: 8 rows
-  // with 256-bit loads at 3 CTAs/SM stream a 12 B/row table at 6.2 TB/s, 4 rows at 6 CTAs/SM at 5.8)
-  constexpr int ROWS = DMAX <= 2 ? 8 : (DMAX <= 8 ? 4 : 2);
+template <int DMAX, int ROWS>
+cudaError_t launch_bucket_rows(StreamOpKind kind, const PassArgs& a, const void* host_consts) {
   switch (kind) {
     case kOpWls:
       if constexpr (DMAX <= 8) return launch_mode<WlsOp<DMAX>, DMAX, ROWS>(WlsOp<DMAX>{}, a);
@@ -144,6 +141,16 @@ cudaError_t launch_bucket(StreamOpKind kind, const PassArgs& a, const void* host
       return cudaErrorInvalidValue;
   }
   return cudaErrorInvalidValue;
+}
+
+template <int DMAX>
+cudaError_t launch_bucket(StreamOpKind kind, const PassArgs& a, const void* host_consts) {
+  // rows per thread per tile: what keeps ~100 bytes per thread in flight without spilling (tools/k2_variants.cu: 8 rows
+  // with 256-bit loads at 3 CTAs/SM stream a 12 B/row table at 6.2 TB/s, 4 rows at 6 CTAs/SM at 5.8)
+  // The 16-column bucket also takes 4 rows (256-bit loads for f64) although that leaves one CTA of ~220 registers per
+  // SM: 10^9 rows x 132 B/row per pass went from 0.88 to 0.97 of the measured HBM peak (22.8 -> 20.9 ms).
+  constexpr int ROWS = DMAX <= 2 ? 8 : (DMAX <= 16 ? 4 : 2);
+  return launch_bucket_rows<DMAX, ROWS>(kind, a, host_consts);
 }
 
 }  // namespace

@@ -97,7 +97,7 @@ __device__ __forceinline__ void process_rows(const Op& op, double (&acc)[Op::NAC
 }
 
 template <class Op, int DMAX, int ROWS, int DQMODE>
-__global__ void __launch_bounds__(kBlock, (DMAX <= 2 ? 4 : (DMAX == 4 ? 3 : (DMAX <= 16 ? 2 : 1))))
+__global__ void __launch_bounds__(kBlock, (DMAX * ROWS >= 64 ? 1 : (DMAX <= 2 ? 4 : (DMAX == 4 ? 3 : 2))))
     stream_reduce_kernel(const Op op, const ColTable cols, const int d, const double* __restrict__ label,
                          const DqArgs dq, const int64_t n, const double* __restrict__ dev_consts,
                          double* __restrict__ row_out, double* __restrict__ partials, unsigned int* __restrict__ ticket,
