@@ -96,7 +96,8 @@ __device__ __forceinline__ void st_state(unsigned long long* p, unsigned long lo
 // Measured alternatives (round 1, 10^9 rows): 512 x 4-row threads with per-thread stores 0.33 of the HBM roofline;
 // 256 threads x 16 rows (128-bit loads, shuffle scans, shared-memory staging) 0.51; persistent CTAs with cp.async
 // prefetch of the next tile and a ticket counter 0.20 (every round turns into a grid-wide barrier on the slowest CTA);
-// 512 threads x 8 rows 0.43.  An ablation of the 0.51 shape without look-back and write-out still took 4.15 ms per 10^9
+// 512 threads x 8 rows 0.43; the shipped striped shape with 1024 threads x 16 rows (one 192 KB CTA per SM, a single
+// look-back step) 0.64 against 0.66 for 256 x 16 at four CTAs per SM -- the shape no longer matters.  An ablation of the 0.51 shape without look-back and write-out still took 4.15 ms per 10^9
 // rows: the tile-local work was instruction-bound (~67 thread instructions per row: 5-step shuffle scans and 4-way
 // bank-conflicted parking).  Hence the striped row assignment below: lane l of a warp owns rows l, l + 32, ... of the
 // warp's 512-row slice, so one __ballot_sync per 32 rows replaces the scans and survivors of one ballot land on
