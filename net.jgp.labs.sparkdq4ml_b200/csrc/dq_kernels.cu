@@ -97,7 +97,13 @@ __device__ __forceinline__ void st_state(unsigned long long* p, unsigned long lo
 // 256 threads x 16 rows (128-bit loads, shuffle scans, shared-memory staging) 0.51; persistent CTAs with cp.async
 // prefetch of the next tile and a ticket counter 0.20 (every round turns into a grid-wide barrier on the slowest CTA);
 // 512 threads x 8 rows 0.43; the shipped striped shape with 1024 threads x 16 rows (one 192 KB CTA per SM, a single
-// look-back step) 0.64 against 0.66 for 256 x 16 at four CTAs per SM -- the shape no longer matters.  An ablation of the 0.51 shape without look-back and write-out still took 4.15 ms per 10^9
+// look-back step) 0.64 against 0.66 for 256 x 16 at four CTAs per SM -- the shape no longer matters.  Where the
+// remaining third goes (10^9 rows, tools/filter_ceiling.cu and ablations of this kernel): a plain copy with the same
+// loads, shared-memory parking and write-out takes 3.46 ms (6.9 TB/s); this kernel 5.61 ms; without the look-back
+// 4.17 ms; without look-back and write-out 2.06 ms.  So the look-back costs 1.4 ms and the tile-local logic 0.7 ms.
+// Reading three look-back windows in one round trip instead of one per step made it slower (6.09 ms, spills): the
+// time is not in the number of steps but in waiting for the slowest of the ~600 tiles in flight to publish its count,
+// and four CTAs per SM (shared memory and registers both full) are not enough other work to cover that.  An ablation of the 0.51 shape without look-back and write-out still took 4.15 ms per 10^9
 // rows: the tile-local work was instruction-bound (~67 thread instructions per row: 5-step shuffle scans and 4-way
 // bank-conflicted parking).  Hence the striped row assignment below: lane l of a warp owns rows l, l + 32, ... of the
 // warp's 512-row slice, so one __ballot_sync per 32 rows replaces the scans and survivors of one ballot land on
