@@ -65,7 +65,9 @@ constexpr int TF = 256;                     // feature slots per CTA
 constexpr int TKC = 16;                     // rows per chunk
 constexpr int TSTAGES = 4;                  // staging stages (raw columns)
 constexpr int TROWST = 16;                  // stages of the row warp's own ring (its loads are latency-bound: depth is what feeds it)
-constexpr int TCONV = 512;                  // loader / converter threads: two per feature slot
+constexpr int TCONV = 512;                  // loader / converter threads: TCONV / TF per feature slot (256: 53 ms against 48.5)
+constexpr int TFPW = 32 * TF / TCONV;       // features per converter warp
+constexpr int TRPT = TKC * TF / TCONV;      // rows of a chunk per converter thread
 constexpr int TTHREADS = TCONV + 64;        // + the MMA warp + the row warp
 constexpr int TOPS = 2;                     // operand stages (hi/lo tf32)
 constexpr int TSCALE = 8;                   // row-factor buffers: how far the row warp may run ahead of the converters
@@ -401,18 +403,18 @@ __global__ void __launch_bounds__(TTHREADS, 1) gram_tf32_kernel(const Tf32Args g
   } else {
     // ================================================= loader / converter warps ========================================
     // converter: two threads per feature, 8 rows of every chunk each (lanes 0..15 / 16..31 of a warp share 16 features)
-    const int feat = warp * 16 + (lane & 15), half = lane >> 4;
+    const int feat = warp * TFPW + (lane % TFPW), half = lane / TFPW;
     const bool active = feat < g.d;
     const bool own_int = active && g.col_i32[feat] != 0;
     const double centre = active ? g.centres[feat] : 0.0;
     // loader: every warp fetches exactly the 16 features it converts (so that a __syncwarp, not a CTA-wide barrier,
     // stands between the copies and their use, and the warps may drift apart by as much as the mbarriers allow):
     // 16-byte piece `ch` of the column slots 16 warp + (lane >> 3) + 4 i; 8 neighbouring lanes fetch one 128-byte line
-    const int ch = lane & 7, slot0 = warp * 16 + (lane >> 3);
-    const char* src[4];
+    const int ch = lane & 7, slot0 = warp * TFPW + (lane >> 3);
+    const char* src[TFPW / 4];
     unsigned live = 0, ints = 0;
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
+    for (int i = 0; i < TFPW / 4; ++i) {
       const int slot = slot0 + 4 * i;
       const bool on = slot < g.d;
       const char* base = on ? static_cast<const char*>(g.col_ptr[slot]) : nullptr;
@@ -440,7 +442,7 @@ __global__ void __launch_bounds__(TTHREADS, 1) gram_tf32_kernel(const Tf32Args g
       }
       const unsigned stg = sbase + kStagingOff + st * (TF * TSTRIDE) + piece_dst;
 #pragma unroll
-      for (int i = 0; i < 4; ++i) {
+      for (int i = 0; i < TFPW / 4; ++i) {
         if (((live >> i) & 1u) && !(g.experiment & 4)) cpa16(stg + 4 * i * TSTRIDE, src[i] + (((ints >> i) & 1u) ? row * 4 : row * 8));
       }
     };
@@ -475,8 +477,8 @@ __global__ void __launch_bounds__(TTHREADS, 1) gram_tf32_kernel(const Tf32Args g
     double zz = 0.0, a1 = 0.0, ab = 0.0;
     int since_drain = 0;
     unsigned drains = 0;
-    const unsigned char* sp0 = smem + kStagingOff + feat * TSTRIDE + half * (own_int ? 32 : 64);
-    unsigned char* op0 = smem + kOpsOff + (feat >> 3) * TSBO + (feat & 7) * 16 + half * 2 * TLBO;
+    const unsigned char* sp0 = smem + kStagingOff + feat * TSTRIDE + half * (own_int ? TRPT * 4 : TRPT * 8);
+    unsigned char* op0 = smem + kOpsOff + (feat >> 3) * TSBO + (feat & 7) * 16 + half * (TRPT / 4) * TLBO;
 
     for (unsigned it = 0; it < my_iters; ++it) {
       TICK(0);
@@ -501,7 +503,7 @@ __global__ void __launch_bounds__(TTHREADS, 1) gram_tf32_kernel(const Tf32Args g
         const bool plain = reinterpret_cast<const int*>(scale + 2 * TKC)[0] != 0;
         f32x2 pzz = 0ull, pa1 = 0ull, pab = 0ull;  // (0.f, 0.f)
 #pragma unroll
-        for (int q = 0; q < 2; ++q) {
+        for (int q = 0; q < TRPT / 4; ++q) {
           float z[4];
           if (own_int) {
             const int4 v = *reinterpret_cast<const int4*>(sp + q * 16);
@@ -516,14 +518,14 @@ __global__ void __launch_bounds__(TTHREADS, 1) gram_tf32_kernel(const Tf32Args g
             z[2] = __double2float_rn(v.x - centre);
             z[3] = __double2float_rn(v.y - centre);
           }
-          const ulonglong2 yc = *reinterpret_cast<const ulonglong2*>(scale + TKC + half * 8 + 4 * q);  // s (y - c_y) of the 4 rows
+          const ulonglong2 yc = *reinterpret_cast<const ulonglong2*>(scale + TKC + half * TRPT + 4 * q);  // s (y - c_y) of the 4 rows
           f32x2 z01, z23;
           if (plain) {
             z01 = pack2(z[0], z[1]);
             z23 = pack2(z[2], z[3]);
             pa1 = add2(pa1, add2(z01, z23));
           } else {  // uniform over the CTA: a dropped row or a weight in this chunk
-            const float4 sc = *reinterpret_cast<const float4*>(scale + half * 8 + 4 * q);
+            const float4 sc = *reinterpret_cast<const float4*>(scale + half * TRPT + 4 * q);
             // dropped rows may hold NaN / Inf payload: they become exact zeros
             z[0] = sc.x != 0.f ? sc.x * z[0] : 0.f;
             z[1] = sc.y != 0.f ? sc.y * z[1] : 0.f;
