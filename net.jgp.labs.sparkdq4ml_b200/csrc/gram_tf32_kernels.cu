@@ -47,7 +47,8 @@
 // own row ring) -> 48.5 (packed arithmetic).  Per chunk a converter warp spends ~390 cycles on load issue, ~380 waiting
 // for the row factors / a free operand buffer, ~1700 in the conversion and ~270 (amortised) in the drain.  Tried and
 // dropped: fp64 <-> fp32 conversion with integer instructions instead of F2F (55.7 ms: the phase follows its instruction
-// count, not the conversion pipe); three operand buffers with three staging stages (same time).  Next: two chunks per row-warp iteration, a TMA tensor-map load path
+// count, not the conversion pipe); three operand buffers with three staging stages (same time); draining the CTAs at
+// different chunks instead of all at once (same time: the drain is not an L2 burst problem).  Next: two chunks per row-warp iteration, a TMA tensor-map load path
 // for uniformly strided tables (no per-thread load issue), 32-row chunks once the raw staging is gone.
 #include <algorithm>
 #include <cstdio>
