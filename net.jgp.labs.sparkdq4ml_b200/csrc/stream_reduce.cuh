@@ -114,7 +114,7 @@ __global__ void __launch_bounds__(kBlock, (DMAX * ROWS >= 64 ? 1 : (DMAX <= 2 ? 
   // in flight during the arithmetic of this one (the ragged end of the table is one extra partial tile below).
   const int64_t tile_rows = static_cast<int64_t>(kBlock) * ROWS;
   const int64_t full_tiles = n / tile_rows;
-#pragma unroll 2
+#pragma unroll (DMAX >= 32 ? 1 : 2)
   for (int64_t tile = blockIdx.x; tile < full_tiles; tile += gridDim.x) {
     const int64_t row = tile * tile_rows + static_cast<int64_t>(threadIdx.x) * ROWS;
     process_rows<Op, DMAX, ROWS, DQMODE, true>(op, acc, consts, cols, d, label, dq, row, row_out);

@@ -35,9 +35,8 @@ def frame(pkg, ctx, g, p, x, d):
     return pkg.VectorAssembler().setInputCols(names).setOutputCol("features").transform(df)
 
 
-def config3(pkg, ctx, rows, reps, row0=0, world=1, global_rows=None):
+def config3(pkg, ctx, rows, reps, row0=0, world=1, global_rows=None, d=16):
     import torch
-    d = 16
     g, p, x = ctx.synth_generate(rows, d=d, row0=row0)
     df = frame(pkg, ctx, g, p, x, d)
     lr = pkg.LinearRegression().setMaxIter(40).setRegParam(1.0).setElasticNetParam(0.5).setSolver("l-bfgs")
@@ -132,6 +131,7 @@ def main():
     ap.add_argument("--config", type=int, required=True)
     ap.add_argument("--rows", type=int, default=0)
     ap.add_argument("--reps", type=int, default=3)
+    ap.add_argument("--features", type=int, default=16, help="config 3 only: number of feature columns (the config itself names 16)")
     ap.add_argument("--gram-tier", type=str, default="fp64", choices=["fp64", "tf32x3"])
     ap.add_argument("--sizes", type=str, default="10000000,100000000,1000000000,4000000000")
     a = ap.parse_args()
@@ -146,7 +146,7 @@ def main():
     if a.config == 3:
         n_global = a.rows or 1_000_000_000
         lo, hi = pkg.shard_bounds(n_global, rank, world)
-        config3(pkg, ctx, hi - lo, a.reps, row0=lo, world=world, global_rows=n_global)
+        config3(pkg, ctx, hi - lo, a.reps, row0=lo, world=world, global_rows=n_global, d=a.features)
     elif a.config == 4:
         rows = a.rows or 62_500_000
         config4(pkg, ctx, rows, a.reps, row0=rank * rows, world=world, tier=a.gram_tier)
