@@ -7,6 +7,7 @@
 
 #include "kernels.hpp"
 #include "ops.cuh"
+#include "pair32.hpp"
 #include "stream_reduce.cuh"
 
 namespace dq4ml {
@@ -187,6 +188,12 @@ cudaError_t launch_stream_pass(StreamOpKind op, const DeviceCols& cols, const do
   a.scratch = scratch;
   a.stream = stream;
   cudaError_t e;
+  if ((op == kOpLsq || op == kOpSummCore) && cols.n > 16) {  // 17..32 columns: the lane-pair kernels (pair32_kernels.cu)
+    e = launch_pair32(op == kOpLsq ? kPairLsq : kPairSumm, a.cols, a.d, a.label, a.dq, a.dq_mode, a.n,
+                      static_cast<const LsqConsts*>(host_consts), scratch, stream);
+    if (e == cudaSuccess) ++*launches;
+    return e;
+  }
   switch (stream_bucket(cols.n > 0 ? cols.n : 1)) {
     case 1: e = launch_bucket<1>(op, a, host_consts); break;
     case 2: e = launch_bucket<2>(op, a, host_consts); break;
