@@ -42,6 +42,7 @@ def main():
     t0 = time.time()
     cases = [("wls_d1", 1, dict(reg=1.0, alpha=1.0, solver="auto")),
              ("owlqn_d16", 16, dict(reg=0.3, alpha=0.5, solver="l-bfgs")),
+             ("owlqn_d24", 24, dict(reg=0.3, alpha=0.5, solver="l-bfgs")),
              ("gram_d40", 40, dict(reg=0.1, alpha=0.0, solver="normal")),
              ("gram_d40_weighted", 40, dict(reg=0.1, alpha=0.0, solver="normal", weighted=True)),
              ("lbfgs_d12_weighted", 12, dict(reg=0.2, alpha=0.0, solver="l-bfgs", weighted=True)),
