@@ -16,4 +16,4 @@ for rep in range(3):
     ms, cnt = ctx.pass_timing()
     ctx.enable_pass_timing(False)
 bytes_row = 4 + 8 * d
-print(json.dumps({"d": d, "rows": rows, "pass_ms": ms / cnt, "gbs": bytes_row * rows / (ms / cnt) / 1e6, "count": float(out[1])}))
+print(json.dumps({"d": d, "rows": rows, "kernels": cnt, "total_ms": ms, "pass_ms": ms / cnt, "gbs": bytes_row * rows / (ms / cnt) / 1e6, "count": float(out[1])}))
