@@ -10,9 +10,10 @@
 // per SM; warp shuffle over same-parity lanes -> shared memory -> one partial per CTA -> the CTA that takes the last
 // ticket folds the partials in a fixed order, like stream_reduce_kernel.
 //
-// Measured (4 x 10^8 rows, one loss/gradient pass): 0.90 of the measured HBM peak at 32 columns, 0.82 at 24, 0.65 at 17;
-// the pass time hardly depends on d because one tile per CTA is in flight and the registers leave no room to prefetch
-// the next.  Tried instead: a 3-stage shared-memory ring (256-row tiles, one cp.async.bulk of 2 KB per column slot on an
+// Measured (4 x 10^8 rows, one loss/gradient pass, fraction of the measured HBM peak): 0.90 at 32 columns with 256
+// threads; up to 24 columns the 12-register-column variant fits 384 threads per SM, half as many bytes again in flight:
+// 0.92 at 17 columns, 0.98 at 20, 1.02 at 24 (0.65 / 0.74 / 0.82 with 256 threads -- the pass is bound by how many
+// loads the registers of an SM can hold in flight, ~140 KB at 32 columns).  Tried instead: a 3-stage shared-memory ring (256-row tiles, one cp.async.bulk of 2 KB per column slot on an
 // mbarrier, one row per thread out of shared memory into the generic Op bodies).  Its loads alone reach 0.91, but the
 // one-row-per-thread consumer is a serial fp64 chain (the 32-term dot product) on 8 warps and the whole pass measured
 // 0.45 (0.52 with 16-byte cp.async pieces); it needs several rows per thread, which the tile size in shared memory does
@@ -23,17 +24,17 @@ namespace dq4ml {
 namespace {
 
 constexpr int PR = 4;    // rows per lane pair and tile
-constexpr int PH = 16;   // columns per lane
-constexpr int kPairTile = (kBlock / 2) * PR;  // 512 rows per CTA and tile
+// PH = register columns per lane (16, or 12 when the table has at most 24 columns), BLK = threads per CTA (256, or 384
+// with the smaller register footprint of PH = 12: half as many bytes again in flight per SM); a tile is BLK / 2 x PR rows.
 
-template <int OP>
+template <int OP, int PH>
 struct PairShape {
   static constexpr int NT = OP == kPairLsq ? 2 + PH : 1 + 2 * PH + 2;  // accumulators per thread
 };
 
 // index of a thread accumulator in the public result vector of the 32-column bucket, or -1 if this lane class does not
 // own it (LsqOp<32>: loss, count, grad[32]; SummCoreOp<32>: count, (S1, S2) x 32 columns, (S1, S2) of the label)
-template <int OP>
+template <int OP, int PH>
 __device__ __forceinline__ int final_index(int h, int k, int hs, int d) {
   if (OP == kPairLsq) {
     if (k < 2) return h == 0 ? k : -1;
@@ -48,8 +49,8 @@ __device__ __forceinline__ int final_index(int h, int k, int hs, int d) {
   return h == 0 ? 1 + 2 * 32 + (k - 1 - 2 * PH) : -1;
 }
 
-template <int OP, int DQMODE, bool VEC>
-__device__ __forceinline__ void pair_rows(double (&acc)[PairShape<OP>::NT], const double (&cst)[PH], const double lab_c,
+template <int OP, int DQMODE, bool VEC, int PH>
+__device__ __forceinline__ void pair_rows(double (&acc)[PairShape<OP, PH>::NT], const double (&cst)[PH], const double lab_c,
                                           const double offset, const double inv_ystd, const ColTable& cols, const int d,
                                           const int hs, const double* __restrict__ label, const DqArgs& dq,
                                           const int64_t row, const int64_t n, const int h) {
@@ -166,12 +167,13 @@ struct PairConsts {
   double offset, inv_ystd;
 };
 
-template <int OP, int DQMODE>
-__global__ void __launch_bounds__(kBlock, 1)
+template <int OP, int DQMODE, int PH, int BLK>
+__global__ void __launch_bounds__(BLK, 1)
     pair32_kernel(const PairConsts c, const ColTable cols, const int d, const double* __restrict__ label, const DqArgs dq,
                   const int64_t n, const int hs, const double* __restrict__ centres, double* __restrict__ partials,
                   unsigned int* __restrict__ ticket, double* __restrict__ result) {
-  constexpr int NT = PairShape<OP>::NT;
+  constexpr int NT = PairShape<OP, PH>::NT;
+  constexpr int kPairTile = (BLK / 2) * PR;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, h = lane & 1;
   double acc[NT];
 #pragma unroll
@@ -187,12 +189,12 @@ __global__ void __launch_bounds__(kBlock, 1)
   const int64_t full_tiles = n / kPairTile;
   const int64_t in_tile = static_cast<int64_t>(threadIdx.x >> 1) * PR;
   for (int64_t tile = blockIdx.x; tile < full_tiles; tile += gridDim.x)
-    pair_rows<OP, DQMODE, true>(acc, cst, lab_c, c.offset, c.inv_ystd, cols, d, hs, label, dq, tile * kPairTile + in_tile, n, h);
+    pair_rows<OP, DQMODE, true, PH>(acc, cst, lab_c, c.offset, c.inv_ystd, cols, d, hs, label, dq, tile * kPairTile + in_tile, n, h);
   if (full_tiles * kPairTile < n && static_cast<int64_t>(blockIdx.x) == full_tiles % gridDim.x)  // the ragged end, guarded loads
-    pair_rows<OP, DQMODE, false>(acc, cst, lab_c, c.offset, c.inv_ystd, cols, d, hs, label, dq, full_tiles * kPairTile + in_tile, n, h);
+    pair_rows<OP, DQMODE, false, PH>(acc, cst, lab_c, c.offset, c.inv_ystd, cols, d, hs, label, dq, full_tiles * kPairTile + in_tile, n, h);
 
   // ---- CTA reduction, the two lane classes kept apart: even shuffle distances stay within a class
-  __shared__ double s_warp[(kBlock / 32) * 2 * NT];
+  __shared__ double s_warp[(BLK / 32) * 2 * NT];
   __shared__ bool s_last;
 #pragma unroll
   for (int k = 0; k < NT; ++k) {
@@ -202,9 +204,9 @@ __global__ void __launch_bounds__(kBlock, 1)
     if (lane < 2) s_warp[(warp * 2 + lane) * NT + k] = v;
   }
   __syncthreads();
-  for (int e = threadIdx.x; e < 2 * NT; e += kBlock) {
+  for (int e = threadIdx.x; e < 2 * NT; e += BLK) {
     double v = s_warp[e];
-    for (int w = 1; w < kBlock / 32; ++w) v += s_warp[w * 2 * NT + e];
+    for (int w = 1; w < BLK / 32; ++w) v += s_warp[w * 2 * NT + e];
     partials[static_cast<size_t>(blockIdx.x) * 2 * NT + e] = v;
   }
   // ---- grid reduction by whichever CTA finishes last, in a fixed order
@@ -214,35 +216,44 @@ __global__ void __launch_bounds__(kBlock, 1)
   __syncthreads();
   if (!s_last) return;
   __threadfence();
-  __shared__ double s_red[kBlock / 32];
+  __shared__ double s_red[BLK / 32];
   for (int e = 0; e < 2 * NT; ++e) {
-    const int out = final_index<OP>(e / NT, e % NT, hs, d);
+    const int out = final_index<OP, PH>(e / NT, e % NT, hs, d);
     if (out < 0) continue;  // uniform over the CTA
     double v = 0.0;
-    for (unsigned b = threadIdx.x; b < gridDim.x; b += kBlock) v += __ldcg(partials + static_cast<size_t>(b) * 2 * NT + e);
+    for (unsigned b = threadIdx.x; b < gridDim.x; b += BLK) v += __ldcg(partials + static_cast<size_t>(b) * 2 * NT + e);
     v = block_reduce(v, kSum, s_red);
     if (threadIdx.x == 0) result[out] = v;
   }
   if (threadIdx.x == 0) *ticket = 0u;  // ready for the next launch on this stream
 }
 
-template <int OP>
-cudaError_t launch_mode(int dq_mode, const PairConsts& c, const ColTable& cols, int d, const double* label, const DqArgs& dq,
-                        int64_t n, const Scratch& scratch, cudaStream_t stream) {
+template <int OP, int PH, int BLK>
+cudaError_t launch_shape(int dq_mode, const PairConsts& c, const ColTable& cols, int d, const double* label, const DqArgs& dq,
+                         int64_t n, const Scratch& scratch, cudaStream_t stream) {
+  constexpr int kPairTile = (BLK / 2) * PR;
   const int64_t tiles = (n + kPairTile - 1) / kPairTile;
   int64_t grid = scratch.sm_count;
   if (grid > tiles) grid = tiles;
   if (grid < 1) grid = 1;
-  if (static_cast<size_t>(grid) * 2 * PairShape<OP>::NT * sizeof(double) > scratch.partials_bytes) return cudaErrorMemoryAllocation;
+  if (static_cast<size_t>(grid) * 2 * PairShape<OP, PH>::NT * sizeof(double) > scratch.partials_bytes) return cudaErrorMemoryAllocation;
   const unsigned gsz = static_cast<unsigned>(grid);
   const int hs = (d + 1) / 2;  // columns per lane: the table is split evenly over the pair
   if (dq_mode == kDqNone)
-    pair32_kernel<OP, kDqNone><<<gsz, kBlock, 0, stream>>>(c, cols, d, label, dq, n, hs, scratch.consts, scratch.partials, scratch.ticket, scratch.result);
+    pair32_kernel<OP, kDqNone, PH, BLK><<<gsz, BLK, 0, stream>>>(c, cols, d, label, dq, n, hs, scratch.consts, scratch.partials, scratch.ticket, scratch.result);
   else if (dq_mode == kDqSeparate)
-    pair32_kernel<OP, kDqSeparate><<<gsz, kBlock, 0, stream>>>(c, cols, d, label, dq, n, hs, scratch.consts, scratch.partials, scratch.ticket, scratch.result);
+    pair32_kernel<OP, kDqSeparate, PH, BLK><<<gsz, BLK, 0, stream>>>(c, cols, d, label, dq, n, hs, scratch.consts, scratch.partials, scratch.ticket, scratch.result);
   else
-    pair32_kernel<OP, kDqLab><<<gsz, kBlock, 0, stream>>>(c, cols, d, label, dq, n, hs, scratch.consts, scratch.partials, scratch.ticket, scratch.result);
+    pair32_kernel<OP, kDqLab, PH, BLK><<<gsz, BLK, 0, stream>>>(c, cols, d, label, dq, n, hs, scratch.consts, scratch.partials, scratch.ticket, scratch.result);
   return cudaGetLastError();
+}
+
+template <int OP>
+cudaError_t launch_mode(int dq_mode, const PairConsts& c, const ColTable& cols, int d, const double* label, const DqArgs& dq,
+                        int64_t n, const Scratch& scratch, cudaStream_t stream) {
+  if (d <= 24) return launch_shape<OP, 12, 384>(dq_mode, c, cols, d, label, dq, n, scratch, stream);
+  // (320 threads for 25..32 columns: ptxas spills 350..630 bytes per thread at that occupancy, 0.73 against 0.88)
+  return launch_shape<OP, 16, 256>(dq_mode, c, cols, d, label, dq, n, scratch, stream);
 }
 
 }  // namespace
