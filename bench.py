@@ -1,12 +1,20 @@
 #!/usr/bin/env python
 """bench.py -- rows/sec of DQ + LinearRegression fit (BASELINE.json metric) on N B200s.
 
-Workload (BASELINE.json configs[1]): synthetic `guest:int32, price:f64` rows (100 M per GPU, weak scaling), the two DQ
-rules + filters fused into the single WeightedLeastSquares aggregation pass, single-feature lasso
-(maxIter 40, regParam 1, elasticNetParam 1 -- DataQuality4MachineLearningApp.java:120-123), OWL-QN on the host.
-One step = one complete `LinearRegression.fit` through the C ABI.
+Headline workload (BASELINE.json configs[1], `--config 2`, the default): synthetic `guest:int32, price:f64` rows
+(100 M per GPU, weak scaling), the two DQ rules + filters fused into the single WeightedLeastSquares aggregation pass,
+single-feature lasso (maxIter 40, regParam 1, elasticNetParam 1 -- DataQuality4MachineLearningApp.java:120-123), OWL-QN
+on the host.  One step = one complete `LinearRegression.fit` through the C ABI.
 
-  python bench.py [--gpus N] [--steps K] [--warmup W] [--rows R]            (torchrun launches N > 1)
+The same run also measures the other BASELINE.json configs and reports them in the `extra` object of the one JSON line
+(skip with --no-extra):
+  config3  10^9 rows x 16 features, solver l-bfgs (OWL-QN, regParam 1, elasticNet 0.5), STRONG-scaled: the global
+           10^9 rows are sharded over the N ranks (App.java:106-126 with wider inputCols)
+  config4  62.5 M rows per GPU x 256 features, normal equations (Gram pass): fp64 tier and tcgen05 tf32x3 tier
+  config5  the DQ section alone (App.java:68-90): filter-compaction at 10^8 / 10^9 / 4*10^9 rows per GPU + digest
+`--config {3,4,5}` makes one of them the headline line instead.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--config C] [--rows R]     (torchrun launches N > 1)
   python bench.py --impl reference ...    times the CPU restatement of the reference (oracle/) on the host cores
 """
 import argparse
@@ -23,75 +31,140 @@ sys.path.insert(0, ROOT)
 METRIC = "rows/sec DQ+LinearRegression fit"
 UNIT = "rows/s"
 LAB = dict(max_iter=40, reg_param=1.0, elastic_net_param=1.0)
+CONFIG3 = dict(max_iter=40, reg_param=1.0, elastic_net_param=0.5, solver="l-bfgs")
 BYTES_PER_ROW = 12  # int32 guest + f64 price, read once by the fused pass
 FALLBACK_HBM_GBS = 6650.0  # B200_PROFILING.md fallback when MEASURED_PEAKS.json is absent
+FP64_PEAK_TFLOPS = 37.2    # measured DMMA/DFMA peak of this part (tools/fp64_peak.cu, profiles/r1_fp64_peak.json)
+
+WORKLOADS = {
+    2: "configs[1]: synthetic guest/price rows, DQ rules fused + single-feature lasso LinearRegression "
+       "(maxIter=40 regParam=1 elasticNet=1, WLS + OWL-QN)",
+    3: "configs[2]: synthetic rows x 16 features via VectorAssembler, DQ rules fused, solver l-bfgs "
+       "(OWL-QN: maxIter=40 regParam=1 elasticNet=0.5), row-sharded",
+    4: "configs[3]: synthetic rows x 256 features, DQ rules fused, normal-equation solver (Gram pass + all-reduce of "
+       "the packed d x d + Cholesky)",
+    5: "configs[4]: DQ rules only (rule 1 -> filter -> rule 2 -> filter, stable compaction), row-sharded",
+}
 
 
-def config(rows, extra=None):
-    c = {"workload": "configs[1]: synthetic guest/price rows, DQ rules fused + single-feature lasso LinearRegression "
-                     "(maxIter=40 regParam=1 elasticNet=1, WLS + OWL-QN)",
-         "rows_per_gpu": rows, "features": 1, "l2_policy": "inputs (12 B/row x rows_per_gpu) larger than the 126 MB L2",
+def config(cfg, rows, extra=None):
+    c = {"workload": WORKLOADS[cfg], "rows_per_gpu": rows, "features": {2: 1, 3: 16, 4: 256, 5: 0}[cfg],
+         "l2_policy": "inputs larger than the 126 MB L2",
          "anomaly_rates": {"p_low": 0.01, "p_high": 0.01}, "seeds": {"data": 20200601, "anomalies": 7}}
     if extra:
         c.update(extra)
     return c
 
 
+def measured_peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "MEASURED_PEAKS.json hbm_gbs (of measured)"
+    except Exception:
+        return FALLBACK_HBM_GBS, "B200_PROFILING.md fallback (of fallback)"
+
+
 # ------------------------------------------------------------------------------------------------ CPU legs (oracle)
 
-def cpu_fit_rate(sample_rows, min_seconds, max_reps, threads=None, warmup=0):
-    """Times oracle fits (fused DQ + WLS moments pass with OpenMP, then the Breeze-style host solve).  Returns
-    (rows/s, threads, reps, seconds, list of per-rep seconds)."""
-    from oracle import passes, spark_ml
+def cpu_threads():
+    """Every hardware thread this process may use -- Spark's local[*] -- NOT OpenMP's default: torchrun exports
+    OMP_NUM_THREADS=1, which must not shrink the CPU baseline."""
+    from oracle import passes
+    return passes.host_threads()
 
-    threads = threads or passes.max_threads()
-    guest, price, _ = passes.synth_generate(sample_rows, d=1, threads=threads)
+
+def cpu_step_fn(cfg, rows, threads):
+    """Returns (step function, rows per step, description) for the CPU restatement of one config."""
+    from oracle import passes, spark_ml
+    if cfg == 2:
+        guest, price, _ = passes.synth_generate(rows, d=1, threads=threads)
+        params = spark_ml.LRParams(**LAB)
+        return (lambda: spark_ml.linear_regression_fit([guest], price, params, dq=(guest, price), threads=threads),
+                rows, "columnar fold (fused DQ + WLS moments, OpenMP over row partitions) + Breeze-style host solve")
+    if cfg == 3:
+        import numpy as np
+        guest, price, extra = passes.synth_generate(rows, d=16, threads=threads)
+        feats = [guest] + [np.ascontiguousarray(extra[k]) for k in range(15)]
+        params = spark_ml.LRParams(**CONFIG3)
+        return (lambda: spark_ml.linear_regression_fit(feats, price, params, dq=(guest, price), threads=threads),
+                rows, "summarizer + one LeastSquaresAggregator pass per OWL-QN evaluation, OpenMP")
+    if cfg == 4:
+        import numpy as np
+        guest, price, extra = passes.synth_generate(rows, d=256, threads=threads)
+        feats = [guest] + [np.ascontiguousarray(extra[k]) for k in range(255)]
+        params = spark_ml.LRParams(max_iter=40, reg_param=0.0, elastic_net_param=0.0, solver="normal")
+        return (lambda: spark_ml.linear_regression_fit(feats, price, params, dq=(guest, price), threads=threads),
+                rows, "WLS aggregator (packed dspr per row) + Cholesky, OpenMP")
+    guest, price, _ = passes.synth_generate(rows, d=1, threads=threads)
+    return (lambda: passes.dq_filter(guest, price), rows, "sequential order-preserving filter (1 thread)")
+
+
+CPU_ROWS = {2: 100_000_000, 3: 20_000_000, 4: 100_000, 5: 100_000_000}
+
+
+def cpu_baseline_config2(rows, seconds, threads):
+    """Both CPU variants BASELINE.md section 3 names, on the full config-2 table: (i) row-at-a-time through the boxed UDF
+    call chain, (ii) the columnar fold; each followed by the same host solve.  Returns the cpu_baseline object."""
+    from oracle import passes, spark_ml
+    guest, price, _ = passes.synth_generate(rows, d=1, threads=threads)
     params = spark_ml.LRParams(**LAB)
-    for _ in range(warmup):
-        spark_ml.linear_regression_fit([guest], price, params, dq=(guest, price), threads=threads)
-    times = []
-    t_all = time.perf_counter()
-    while len(times) < max_reps:
-        t0 = time.perf_counter()
-        m = spark_ml.linear_regression_fit([guest], price, params, dq=(guest, price), threads=threads)
-        times.append(time.perf_counter() - t0)
-        if time.perf_counter() - t_all >= min_seconds:
-            break
-    total = sum(times)
-    assert m.total_iterations >= 1
-    return sample_rows * len(times) / total, threads, len(times), total, times
+
+    def columnar():
+        return spark_ml.linear_regression_fit([guest], price, params, dq=(guest, price), threads=threads)
+
+    def rowwise():
+        mom = passes.lab_rowwise_moments(guest, price, threads=threads)
+        return spark_ml.wls_fit_from_moments(mom, 1, params)
+
+    out = {}
+    for name, fn in (("columnar", columnar), ("rowwise_scalar", rowwise)):
+        fn()  # warm-up (first OpenMP region spins the thread pool up)
+        times, t_all = [], time.perf_counter()
+        while True:
+            t0 = time.perf_counter()
+            fn()
+            times.append(time.perf_counter() - t0)
+            if time.perf_counter() - t_all >= seconds / 2:
+                break
+        out[name] = {"rows_per_sec": rows * len(times) / sum(times), "fits": len(times), "seconds": sum(times)}
+    return {
+        "value": out["columnar"]["rows_per_sec"], "unit": UNIT, "cores": threads, "kind": "port",
+        "sample": f"{out['columnar']['fits']} + {out['rowwise_scalar']['fits']} fits of the full {rows}-row table "
+                  f"(same generator/seeds), {out['columnar']['seconds'] + out['rowwise_scalar']['seconds']:.1f} s of CPU work",
+        "variants": out,
+        "note": "oracle/ (C passes with OpenMP + Python Breeze restatement); Spark local[*] cannot run here (no JVM). "
+                "value = the faster, columnar variant; rowwise_scalar goes one row at a time through the UDF call chain"}
 
 
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    sample = min(args.rows, args.cpu_sample_rows)
-    from oracle import passes, spark_ml
-
-    threads = passes.max_threads()
-    guest, price, _ = passes.synth_generate(sample, d=1, threads=threads)
-    params = spark_ml.LRParams(**LAB)
-
-    def step():
-        return spark_ml.linear_regression_fit([guest], price, params, dq=(guest, price), threads=threads)
-
-    for _ in range(args.warmup):
+    threads = cpu_threads()
+    cfg = args.config
+    rows = min(args.rows or CPU_ROWS[cfg], CPU_ROWS[cfg])
+    step, rows, how = cpu_step_fn(cfg, rows, threads if cfg != 5 else 1)
+    for _ in range(max(args.warmup, 1)):
         step()
     t0 = time.perf_counter()
     for _ in range(args.steps):
         step()
     dt = time.perf_counter() - t0
-    value = sample * args.steps / dt
-    what = f"{sample} rows per step of the same generator/seeds (bounded sample of the {args.rows}-row workload)"
+    value = rows * args.steps / dt
+    gpu_rows = args.rows or DEFAULT_ROWS[cfg]
+    what = (f"{rows} rows per step of the same generator/seeds" +
+            ("" if rows == gpu_rows else f" (bounded sample of the {gpu_rows}-row workload)"))
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
-        "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
-        "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": config(args.rows, {"cpu_sample_rows": sample}),
-        "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port", "sample": what,
+        "warmup": max(args.warmup, 1), "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True,
+        "scaling": "strong" if cfg == 3 else "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": config(cfg, gpu_rows),
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads if cfg != 5 else 1, "kind": "port", "sample": what,
+                         "how": how, "host_threads_available": threads,
+                         "omp_num_threads_env": os.environ.get("OMP_NUM_THREADS"),
                          "note": "Spark local[*] cannot run here (no JVM): this is oracle/, the C+Python restatement of "
-                                 "the reference's algorithm, OpenMP over row partitions"},
+                                 "the reference's algorithm; the thread count comes from the CPU affinity mask, not "
+                                 "from OMP_NUM_THREADS"},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -142,14 +215,6 @@ class ClockSampler:
         return {"sm_mhz": statistics.median(sm), "sm_max_mhz": max(mx), "reasons": sorted(reasons), "samples": len(sm)}
 
 
-def measured_hbm_peak():
-    try:
-        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
-            return float(json.load(f)["hbm_gbs"]), "MEASURED_PEAKS.json hbm_gbs (of measured)"
-    except Exception:
-        return FALLBACK_HBM_GBS, "B200_PROFILING.md fallback (of fallback)"
-
-
 def ncu_traffic_per_launch(kernel_key):
     """dram bytes per launch of the dominant kernel from the committed `ncu --set full` summary, if any."""
     try:
@@ -159,122 +224,349 @@ def ncu_traffic_per_launch(kernel_key):
         return None
 
 
-def run_ours(args):
-    import torch
-    import torch.distributed as dist
+def bind_to_gpu_numa_node(local_rank):
+    """Multi-rank runs: keep this rank (and therefore the pages of its pinned staging buffers, by first touch) on the
+    CPUs the GPU hangs off, so that the end-to-end H2D copies of the ranks do not all cross one socket."""
+    try:
+        bus = subprocess.run(["nvidia-smi", "--query-gpu=pci.bus_id", "--format=csv,noheader", "-i", str(local_rank)],
+                             capture_output=True, text=True, timeout=20).stdout.strip().lower()
+        if bus.startswith("00000000:"):
+            bus = bus[4:]
+        with open(f"/sys/bus/pci/devices/{bus}/local_cpulist") as f:
+            spec = f.read().strip()
+        cpus = set()
+        for part in spec.split(","):
+            a, _, b = part.partition("-")
+            cpus.update(range(int(a), int(b or a) + 1))
+        cpus &= os.sched_getaffinity(0)
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+            return spec
+    except Exception:
+        pass
+    return None
 
-    import sparkdq4ml_b200 as pkg
 
-    rank = int(os.environ.get("RANK", "0"))
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
-    if not torch.cuda.is_available():
-        raise SystemExit("bench.py needs a CUDA device: the product has no CPU fallback (use --impl reference for the CPU arm)")
-    torch.cuda.set_device(local_rank)
-    if world > 1:
-        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local_rank}"))
-    ctx = pkg.Context(local_rank).bind_torch_distributed()
-    n = args.rows
-    guest, price, _ = ctx.synth_generate(n, d=1, row0=rank * n)
-    df = pkg.Frame(ctx, {"guest": guest, "price": price}).with_fused_dq("guest", "price")
-    df = df.withColumn("label", df.col("price"))
-    df = pkg.VectorAssembler().setInputCols(["guest"]).setOutputCol("features").transform(df)
-    lr = pkg.LinearRegression().setMaxIter(LAB["max_iter"]).setRegParam(LAB["reg_param"]).setElasticNetParam(LAB["elastic_net_param"])
-    stream = torch.cuda.ExternalStream(ctx.stream, device=torch.device(f"cuda:{local_rank}"))
+class Bench:
+    def __init__(self, args):
+        import torch
+        import torch.distributed as dist
 
-    def barrier():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-        ctx.synchronize()
+        import sparkdq4ml_b200 as pkg
 
-    def timed(step_fn, steps):
+        self.torch, self.dist, self.pkg, self.args = torch, dist, pkg, args
+        self.rank = int(os.environ.get("RANK", "0"))
+        self.world = int(os.environ.get("WORLD_SIZE", "1"))
+        self.local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+        if not torch.cuda.is_available():
+            raise SystemExit("bench.py needs a CUDA device: the product has no CPU fallback (use --impl reference for the CPU arm)")
+        torch.cuda.set_device(self.local_rank)
+        self.dev = f"cuda:{self.local_rank}"
+        self.numa = None
+        if self.world > 1:
+            self.numa = bind_to_gpu_numa_node(self.local_rank)
+            os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+            dist.init_process_group("nccl", device_id=torch.device(self.dev))
+        self.ctx = pkg.Context(self.local_rank).bind_torch_distributed()
+        self.stream = torch.cuda.ExternalStream(self.ctx.stream, device=torch.device(self.dev))
+        self.peak, self.peak_src = measured_peaks()
+
+    def close(self):
+        self.ctx.close()
+        if self.world > 1:
+            self.dist.destroy_process_group()
+
+    def barrier(self):
+        if self.world > 1:
+            self.dist.barrier()
+        self.torch.cuda.synchronize()
+        self.ctx.synchronize()
+
+    def max_over_ranks(self, v):
+        t = self.torch.tensor([float(v)], dtype=self.torch.float64, device=self.dev)
+        if self.world > 1:
+            self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def sum_over_ranks(self, v):
+        t = self.torch.tensor([float(v)], dtype=self.torch.float64, device=self.dev)
+        if self.world > 1:
+            self.dist.all_reduce(t, op=self.dist.ReduceOp.SUM)
+        return float(t.item())
+
+    def timed(self, step_fn, steps):
+        """CUDA events on the ctx stream around `steps` calls, barrier + synchronize on both sides, max over ranks."""
+        torch = self.torch
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        barrier()
-        e0.record(stream)
+        self.barrier()
+        e0.record(self.stream)
+        out = None
         for _ in range(steps):
             out = step_fn()
-        e1.record(stream)
-        barrier()
-        ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=f"cuda:{local_rank}")
-        if world > 1:
-            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
-        return float(ms.item()), out
+        e1.record(self.stream)
+        self.barrier()
+        return self.max_over_ranks(e0.elapsed_time(e1)), out
 
-    # ---- device-resident arm (value): inputs already in HBM
-    model = None
-    for _ in range(max(args.warmup, 3)):
+    def free(self):
+        self.torch.cuda.empty_cache()
+
+    def frame(self, g, p, x, d):
+        pkg = self.pkg
+        cols = {"guest": g, "label": p}
+        names = ["guest"]
+        for k in range(d - 1):
+            cols[f"x{k + 1}"] = x[k]
+            names.append(f"x{k + 1}")
+        df = pkg.Frame(self.ctx, cols).with_fused_dq("guest", "label")
+        return pkg.VectorAssembler().setInputCols(names).setOutputCol("features").transform(df)
+
+    # -------------------------------------------------------------------------------------------- config 2 (headline)
+    def config2(self, rows, steps, warmup, with_e2e=True, sampler=True):
+        pkg, ctx, torch, args = self.pkg, self.ctx, self.torch, self.args
+        n = rows
+        guest, price, _ = ctx.synth_generate(n, d=1, row0=self.rank * n)
+        df = pkg.Frame(ctx, {"guest": guest, "price": price}).with_fused_dq("guest", "price")
+        df = df.withColumn("label", df.col("price"))
+        df = pkg.VectorAssembler().setInputCols(["guest"]).setOutputCol("features").transform(df)
+        lr = pkg.LinearRegression().setMaxIter(LAB["max_iter"]).setRegParam(LAB["reg_param"]).setElasticNetParam(LAB["elastic_net_param"])
+        model = None
+        for _ in range(warmup):
+            model = lr.fit(df)
+        # the timed region lasts only milliseconds: start the clock sampler first and keep the same step running
+        # untimed for a while so that nvidia-smi (50 ms period) sees the GPU under this load; every rank must run the
+        # same number of steps (each fit contains a collective), so rank 0 sizes the pre-roll and tells the others
+        smp = ClockSampler(self.local_rank) if (sampler and self.rank == 0) else None
+        t0 = time.perf_counter()
         model = lr.fit(df)
-    # the timed region lasts only milliseconds: start the clock sampler first and keep the same step running untimed
-    # for a while so that nvidia-smi (50 ms period) sees the GPU under this load, then go straight into the timed steps
-    sampler = ClockSampler(local_rank) if rank == 0 else None
-    # every rank must run the same number of steps (each fit contains a collective): rank 0 sizes the pre-roll from
-    # its warm-up speed and tells the others
-    t0 = time.perf_counter()
-    model = lr.fit(df)
-    per_step = max(time.perf_counter() - t0, 1e-5)
-    pre_steps = torch.tensor([min(int(args.preroll_seconds / per_step), 20000)], dtype=torch.int64, device=f"cuda:{local_rank}")
-    if world > 1:
-        dist.broadcast(pre_steps, src=0)
-    for _ in range(int(pre_steps.item())):
-        model = lr.fit(df)
-    ctx.enable_pass_timing(True)
-    l0 = ctx.launch_count
-    ms, model = timed(lambda: lr.fit(df), args.steps)
-    launches = ctx.launch_count - l0
-    pass_ms, passes = ctx.pass_timing()
-    ctx.enable_pass_timing(False)
-    clocks = sampler.stop() if sampler is not None else None
-    value = world * n * args.steps / (ms / 1e3)
+        per_step = max(time.perf_counter() - t0, 1e-5)
+        pre = torch.tensor([min(int(args.preroll_seconds / per_step), 20000)], dtype=torch.int64, device=self.dev)
+        if self.world > 1:
+            self.dist.broadcast(pre, src=0)
+        for _ in range(int(pre.item())):
+            model = lr.fit(df)
+        ctx.enable_pass_timing(True)
+        l0 = ctx.launch_count
+        ms, model = self.timed(lambda: lr.fit(df), steps)
+        launches = ctx.launch_count - l0
+        pass_ms, passes = ctx.pass_timing()
+        ctx.enable_pass_timing(False)
+        clocks = smp.stop() if smp is not None else None
+        res = {"rows": n, "ms": ms, "steps": steps, "value": self.world * n * steps / (ms / 1e3), "launches": int(launches),
+               "pass_ms_avg": pass_ms / max(passes, 1), "passes": int(passes), "clocks": clocks,
+               "fit": {"coefficient": float(model.coefficients()[0]), "intercept": model.intercept(),
+                       "total_iterations": model.summary().totalIterations(), "rows_after_dq": model.num_rows,
+                       "solver": model.solver_used}}
+        if with_e2e:
+            # end-to-end arm: HOST (pinned) columns through the same C-ABI call; H2D inside the timed region
+            gh = guest.cpu().pin_memory()
+            ph = price.cpu().pin_memory()
+            hdf = pkg.Frame(ctx, {"guest": gh, "price": ph}).with_fused_dq("guest", "price")
+            hdf = hdf.withColumn("label", hdf.col("price"))
+            hdf = pkg.VectorAssembler().setInputCols(["guest"]).setOutputCol("features").transform(hdf)
+            e2e_steps = max(1, min(steps, args.e2e_steps))
+            for _ in range(2):
+                hmodel = lr.fit(hdf)
+            e2e_ms, hmodel = self.timed(lambda: lr.fit(hdf), e2e_steps)
+            assert hmodel.coefficients().tobytes() == model.coefficients().tobytes()
+            res["e2e"] = {"value": self.world * n * e2e_steps / (e2e_ms / 1e3), "unit": UNIT,
+                          "h2d_bytes_per_step": BYTES_PER_ROW * n, "d2h_bytes_per_step": 6 * 8, "steps": e2e_steps,
+                          "ms_per_step": e2e_ms / e2e_steps, "numa_cpus": self.numa,
+                          "note": "pinned host columns -> dq4ml_linreg_fit; H2D staging + pass + D2H of the moments inside the timed region"}
+            del gh, ph, hdf
+        del guest, price, df
+        self.free()
+        return res
 
-    # ---- end-to-end arm: HOST (pinned) columns through the same C-ABI call; H2D inside the timed region
-    gh = guest.cpu().pin_memory()
-    ph = price.cpu().pin_memory()
-    hdf = pkg.Frame(ctx, {"guest": gh, "price": ph}).with_fused_dq("guest", "price")
-    hdf = hdf.withColumn("label", hdf.col("price"))
-    hdf = pkg.VectorAssembler().setInputCols(["guest"]).setOutputCol("features").transform(hdf)
-    e2e_steps = max(1, min(args.steps, args.e2e_steps))
-    for _ in range(2):
-        hmodel = lr.fit(hdf)
-    e2e_ms, hmodel = timed(lambda: lr.fit(hdf), e2e_steps)
-    e2e_value = world * n * e2e_steps / (e2e_ms / 1e3)
-    assert hmodel.coefficients().tobytes() == model.coefficients().tobytes()
+    # -------------------------------------------------------------------------------------------- config 3
+    def config3(self, global_rows, reps, d=16):
+        """STRONG scaling: the global table is sharded over the ranks.  Whole-fit rows/s and per-pass roofline."""
+        pkg, ctx = self.pkg, self.ctx
+        lo, hi = pkg.shard_bounds(global_rows, self.rank, self.world)
+        rows = hi - lo
+        g, p, x = ctx.synth_generate(rows, d=d, row0=lo)
+        df = self.frame(g, p, x, d)
+        lr = pkg.LinearRegression().setMaxIter(CONFIG3["max_iter"]).setRegParam(CONFIG3["reg_param"])
+        lr = lr.setElasticNetParam(CONFIG3["elastic_net_param"]).setSolver("l-bfgs")
+        bytes_per_row = 4 + 8 * d  # int32 guest + 15 f64 features + f64 label (= price); the DQ columns are guest and label
+        model = lr.fit(df)  # warm-up
+        best = None
+        for _ in range(reps):
+            ctx.enable_pass_timing(True)
+            l0 = ctx.launch_count
+            ms, model = self.timed(lambda: lr.fit(df), 1)
+            launches = ctx.launch_count - l0
+            times = ctx.pass_times()
+            ctx.enable_pass_timing(False)
+            if best is None or ms < best[0]:
+                best = (ms, times, launches)
+        ms, times, launches = best
+        summ_ms = self.max_over_ranks(times[0])
+        lsq = times[1:]
+        lsq_ms = self.max_over_ranks(sum(lsq) / max(len(lsq), 1))
+        shard_bytes = bytes_per_row * rows
+        res = {"global_rows": global_rows, "rows_this_rank": rows, "features": d, "scaling": "strong", "n_gpus": self.world,
+               "solver": model.solver_used, "params": CONFIG3, "total_iterations": model.summary().totalIterations(),
+               "data_passes": model.data_passes, "fit_seconds": ms / 1e3, "rows_per_sec_fit": global_rows / (ms / 1e3),
+               "gpu_launches": int(launches), "bytes_per_row_per_pass": bytes_per_row,
+               "summarizer_pass": {"kernel": f"SummCoreOp<{d}>", "ms": summ_ms,
+                                   "frac": shard_bytes / (summ_ms / 1e3) / 1e9 / self.peak},
+               "lsq_pass": {"kernel": f"LsqOp<{d}>", "ms_avg": lsq_ms, "passes": len(lsq),
+                            "gbs": shard_bytes / (lsq_ms / 1e3) / 1e9, "frac": shard_bytes / (lsq_ms / 1e3) / 1e9 / self.peak},
+               "coefficients_head": model.coefficients()[:4].tolist(), "intercept": model.intercept(),
+               "rows_after_dq": model.num_rows}
+        del g, p, x, df
+        self.free()
+        return res
 
-    if rank != 0:
-        if world > 1:
-            dist.destroy_process_group()
-        return
-    peak, peak_src = measured_hbm_peak()
-    per_launch_ms = pass_ms / max(passes, 1)
-    achieved = BYTES_PER_ROW * n / (per_launch_ms / 1e3) / 1e9
-    line = {
-        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
-        "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
-        "data": "synthetic", "config": config(n),
-        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": BYTES_PER_ROW * n, "d2h_bytes_per_step": 6 * 8,
-                "steps": e2e_steps, "ms_per_step": e2e_ms / e2e_steps,
-                "note": "pinned host columns -> dq4ml_linreg_fit; H2D staging + pass + D2H of the moments inside the timed region"},
-        "gpu_launches": int(launches),
-        "roofline": {"bound": "hbm", "kernel": "stream_reduce_kernel<WlsOp<1>,1,8,kDqLab> (fused DQ + WLS moments)",
-                     "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                     "traffic": ncu_traffic_per_launch("wls_moments_d1_lab"), "peak_source": peak_src,
-                     "algorithmic_bytes_per_launch": BYTES_PER_ROW * n, "avg_launch_ms": per_launch_ms,
-                     "launches_timed": int(passes)},
-        "clocks": clocks,
-        "fit": {"coefficient": float(model.coefficients()[0]), "intercept": model.intercept(),
-                "total_iterations": model.summary().totalIterations(), "rows_after_dq": model.num_rows,
-                "solver": model.solver_used},
-    }
-    if world == 1 and not args.no_cpu_baseline:
-        rate, threads, reps, secs, _ = cpu_fit_rate(min(n, args.cpu_sample_rows), args.cpu_seconds, 10**9)
-        line["cpu_baseline"] = {
-            "value": rate, "unit": UNIT, "cores": threads, "kind": "port",
-            "sample": f"{reps} fits of {min(n, args.cpu_sample_rows)} rows (same generator/seeds), {secs:.1f} s of CPU work",
-            "note": "oracle/ (C passes with OpenMP + Python Breeze restatement); Spark local[*] cannot run here (no JVM)"}
-    print(json.dumps(line), flush=True)
-    if world > 1:
-        dist.destroy_process_group()
+    # -------------------------------------------------------------------------------------------- config 4
+    def config4(self, rows, reps, tiers=("fp64", "tf32x3")):
+        """WEAK scaling (the 500 M x 256 table is 1 TB: 62.5 M rows per GPU).  Gram pass per tier + whole fit."""
+        pkg, ctx = self.pkg, self.ctx
+        from sparkdq4ml_b200 import ml
+        d = 256
+        g, p, x = ctx.synth_generate(rows, d=d, row0=self.rank * rows)
+        feats = [g] + [x[k] for k in range(d - 1)]
+        flop_per_row = d * (d + 1) + 4 * d  # SURVEY 8d: symmetric half of X^T X at 2 flop/MAC + X^T y + sums
+        bytes_per_row = 4 + 8 * d
+        df = self.frame(g, p, x, d)
+        lr = pkg.LinearRegression().setMaxIter(40).setRegParam(0.0).setSolver("normal")
+        res = {"rows_per_gpu": rows, "features": d, "scaling": "weak", "n_gpus": self.world,
+               "flop_per_row": flop_per_row, "bytes_per_row": bytes_per_row}
+        ref_coef = None
+        for tier in tiers:
+            ctx.set_gram_tier(tier)
+            ml.wls_moments(ctx, feats, p, dq=(g, p))  # warm-up
+            best = None
+            for _ in range(reps):
+                ctx.enable_pass_timing(True)
+                ml.wls_moments(ctx, feats, p, dq=(g, p))
+                t = ctx.pass_times()
+                ctx.enable_pass_timing(False)
+                best = t[0] if best is None else min(best, t[0])
+            pass_ms = self.max_over_ranks(best)
+            fit_ms, model = self.timed(lambda: lr.fit(df), 1)
+            coef = model.coefficients()
+            if ref_coef is None:
+                ref_coef = coef
+            res[tier] = {"pass_ms": pass_ms, "rows_per_sec_pass": self.world * rows / (pass_ms / 1e3),
+                         "algorithmic_tflops": flop_per_row * rows / (pass_ms / 1e3) / 1e12,
+                         "frac_of_fp64_peak": flop_per_row * rows / (pass_ms / 1e3) / 1e12 / FP64_PEAK_TFLOPS,
+                         "gbs": bytes_per_row * rows / (pass_ms / 1e3) / 1e9,
+                         "frac_of_hbm": bytes_per_row * rows / (pass_ms / 1e3) / 1e9 / self.peak,
+                         "fit_seconds": fit_ms / 1e3, "rows_per_sec_fit": self.world * rows / (fit_ms / 1e3),
+                         "solver": model.solver_used, "coefficients_head": coef[:4].tolist(), "intercept": model.intercept(),
+                         "max_coef_diff_vs_fp64_scale_rel": float(abs(coef - ref_coef).max() / max(abs(ref_coef).max(), 1e-300))}
+        ctx.set_gram_tier("fp64")
+        del g, p, x, feats, df
+        self.free()
+        return res
+
+    # -------------------------------------------------------------------------------------------- config 5
+    def config5(self, sizes, reps):
+        """The DQ section alone, row-sharded (sizes are rows PER GPU; output stays sharded, global offsets exchanged)."""
+        pkg, ctx, torch = self.pkg, self.ctx, self.torch
+        out = []
+        for n in sizes:
+            g, p, _ = ctx.synth_generate(n, d=1, row0=self.rank * n)
+            go = torch.empty_like(g)
+            po = torch.empty_like(p)
+            import ctypes as C
+            L = pkg.capi.lib()
+            n_out, n1 = C.c_int64(0), C.c_int64(0)
+
+            def call():
+                pkg.capi.check(L.dq4ml_dq_filter(ctx.handle, g.data_ptr(), p.data_ptr(), n, None, go.data_ptr(),
+                                                 po.data_ptr(), C.byref(n_out), C.byref(n1)))
+            call()  # warm-up (also sizes the tile-status scratch)
+            best = None
+            for _ in range(reps):
+                ms, _ = self.timed(call, 1)
+                best = ms if best is None else min(best, ms)
+            m = int(n_out.value)
+            t0 = time.perf_counter()
+            off, tot = pkg.dq_filter_global_offset(ctx, m)
+            off_ms = (time.perf_counter() - t0) * 1e3
+            bytes_alg = self.sum_over_ranks(12 * n + 12 * m)
+            dig = ctx.rows_digest(go[:m], po[:m], seed=5)
+            out.append({"rows_per_gpu": n, "n_gpus": self.world, "survivors_this_rank": m, "after_rule1_this_rank": int(n1.value),
+                        "survivors_global": tot, "global_offset_this_rank": off, "offset_exchange_ms": off_ms,
+                        "call_ms": best, "rows_per_sec": self.world * n / (best / 1e3),
+                        "gbs_per_gpu": bytes_alg / self.world / (best / 1e3) / 1e9,
+                        "frac": bytes_alg / self.world / (best / 1e3) / 1e9 / self.peak,
+                        "digest_rank0": [str(v) for v in dig],
+                        "note": "whole dq4ml_dq_filter call (memsets + kernel + 16 B D2H + sync), max over ranks"})
+            del g, p, go, po
+            self.free()
+        return out
+
+
+DEFAULT_ROWS = {2: 100_000_000, 3: 1_000_000_000, 4: 62_500_000, 5: 1_000_000_000}
+
+
+def run_ours(args):
+    b = Bench(args)
+    cfg = args.config
+    warmup = max(args.warmup, 3)
+    rows = args.rows or DEFAULT_ROWS[cfg]
+    line = {"metric": METRIC, "unit": UNIT, "n_gpus": b.world, "steps": args.steps, "warmup": warmup,
+            "higher_is_better": True, "vs_baseline": None, "dtype": "f64", "data": "synthetic"}
+    if cfg == 2:
+        r = b.config2(rows, args.steps, warmup)
+        achieved = BYTES_PER_ROW * rows / (r["pass_ms_avg"] / 1e3) / 1e9
+        line.update({
+            "value": r["value"], "ms_per_step": r["ms"] / args.steps, "scaling": "weak", "config": config(2, rows),
+            "e2e": r["e2e"], "gpu_launches": r["launches"],
+            "roofline": {"bound": "hbm", "kernel": "stream_reduce_kernel<WlsOp<1>,1,8,kDqLab> (fused DQ + WLS moments)",
+                         "achieved": achieved, "peak": b.peak, "unit": "GB/s", "frac": achieved / b.peak,
+                         "traffic": ncu_traffic_per_launch("wls_moments_d1_lab"), "peak_source": b.peak_src,
+                         "algorithmic_bytes_per_launch": BYTES_PER_ROW * rows, "avg_launch_ms": r["pass_ms_avg"],
+                         "launches_timed": r["passes"]},
+            "clocks": r["clocks"], "fit": r["fit"]})
+    elif cfg == 3:
+        r = b.config3(rows, max(args.steps, 1) if args.steps <= 5 else 3)
+        shard = r["rows_this_rank"] * r["bytes_per_row_per_pass"]
+        line.update({
+            "value": r["rows_per_sec_fit"], "ms_per_step": r["fit_seconds"] * 1e3, "steps": 1, "scaling": "strong",
+            "config": config(3, r["rows_this_rank"], {"global_rows": rows}), "gpu_launches": r["gpu_launches"],
+            "roofline": {"bound": "hbm", "kernel": "stream_reduce_kernel<LsqOp<16>,16,4,kDqLab>", "achieved": r["lsq_pass"]["gbs"],
+                         "peak": b.peak, "unit": "GB/s", "frac": r["lsq_pass"]["frac"], "traffic": ncu_traffic_per_launch("lsq_d16_lab"),
+                         "peak_source": b.peak_src, "algorithmic_bytes_per_launch": shard, "avg_launch_ms": r["lsq_pass"]["ms_avg"],
+                         "launches_timed": r["lsq_pass"]["passes"]},
+            "fit": r})
+    elif cfg == 4:
+        r = b.config4(rows, 2)
+        f = r["fp64"]
+        line.update({
+            "value": f["rows_per_sec_fit"], "ms_per_step": f["fit_seconds"] * 1e3, "steps": 1, "scaling": "weak",
+            "config": config(4, rows), "gpu_launches": 2,
+            "roofline": {"bound": "tensor", "kernel": "gram_tile_kernel (fp64 DMMA)", "achieved": f["algorithmic_tflops"],
+                         "peak": FP64_PEAK_TFLOPS, "unit": "TFLOP/s", "frac": f["frac_of_fp64_peak"], "traffic": None,
+                         "peak_source": "measured fp64 DMMA/DFMA peak (tools/fp64_peak.cu); MEASURED_PEAKS.json has no fp64 figure"},
+            "fit": r})
+    else:
+        r = b.config5([rows], 3)[0]
+        line.update({
+            "value": r["rows_per_sec"], "ms_per_step": r["call_ms"], "steps": 1, "scaling": "weak", "config": config(5, rows),
+            "gpu_launches": 1,
+            "roofline": {"bound": "hbm", "kernel": "dq_filter_compact_kernel", "achieved": r["gbs_per_gpu"], "peak": b.peak,
+                         "unit": "GB/s", "frac": r["frac"], "traffic": ncu_traffic_per_launch("dq_filter"), "peak_source": b.peak_src},
+            "fit": r})
+    if cfg == 2 and not args.no_extra:
+        extra = {}
+        t0 = time.perf_counter()
+        try:
+            extra["config3"] = b.config3(args.config3_rows, 2)
+            extra["config4"] = b.config4(args.config4_rows, 2)
+            extra["config5"] = b.config5([int(s) for s in args.config5_sizes.split(",")], 2)
+        except Exception as e:  # the headline line must survive a failure in the side measurements (and say so)
+            extra["error"] = f"{type(e).__name__}: {e}"
+        extra["seconds"] = time.perf_counter() - t0
+        line["extra"] = extra
+    if b.rank == 0:
+        if cfg == 2 and b.world == 1 and not args.no_cpu_baseline:
+            line["cpu_baseline"] = cpu_baseline_config2(rows, args.cpu_seconds, cpu_threads())
+        print(json.dumps(line), flush=True)
+    b.close()
 
 
 def main():
@@ -282,12 +574,16 @@ def main():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--rows", type=int, default=100_000_000, help="rows per GPU (weak scaling)")
+    ap.add_argument("--config", type=int, default=2, choices=[2, 3, 4, 5], help="BASELINE.json config (1-based); 2 = configs[1]")
+    ap.add_argument("--rows", type=int, default=0, help="rows per GPU (config 3: global rows); 0 = the config's own size")
     ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
     ap.add_argument("--e2e-steps", type=int, default=10)
-    ap.add_argument("--cpu-sample-rows", type=int, default=50_000_000)
-    ap.add_argument("--cpu-seconds", type=float, default=12.0)
+    ap.add_argument("--cpu-seconds", type=float, default=16.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extra", action="store_true", help="skip the config 3/4/5 side measurements")
+    ap.add_argument("--config3-rows", type=int, default=1_000_000_000)
+    ap.add_argument("--config4-rows", type=int, default=62_500_000)
+    ap.add_argument("--config5-sizes", type=str, default="100000000,1000000000,4000000000")
     ap.add_argument("--preroll-seconds", type=float, default=2.0, help="untimed steps under the clock sampler")
     args = ap.parse_args()
     if args.impl == "reference":

@@ -34,7 +34,7 @@
 extern "C" {
 #endif
 
-#define DQ4ML_ABI_VERSION 1
+#define DQ4ML_ABI_VERSION 2 /* 2: dq4ml_lr_params gained loss/epsilon; dq4ml_ctx_set_allreduce takes rank/world_size */
 
 typedef enum {
   DQ4ML_OK = 0,
@@ -83,9 +83,10 @@ typedef struct {
 } dq4ml_dq_fused;
 
 typedef enum { DQ4ML_SOLVER_AUTO = 0, DQ4ML_SOLVER_NORMAL = 1, DQ4ML_SOLVER_LBFGS = 2 } dq4ml_solver;
+typedef enum { DQ4ML_LOSS_SQUARED_ERROR = 0, DQ4ML_LOSS_HUBER = 1 } dq4ml_loss;
 
 /* org.apache.spark.ml.regression.LinearRegression params as the lab sets them (App:120-123) plus the Spark 2.4.4
- * defaults it leaves alone.  dq4ml_lr_params_default() = {100, 0.0, 0.0, 1e-6, 1, 1, AUTO}. */
+ * defaults it leaves alone.  dq4ml_lr_params_default() = {100, 0.0, 0.0, 1e-6, 1, 1, AUTO, SQUARED_ERROR, 1.35}. */
 typedef struct {
   int32_t max_iter;          /* setMaxIter        (App:121) */
   double reg_param;          /* setRegParam       (App:122) */
@@ -94,6 +95,8 @@ typedef struct {
   int32_t fit_intercept;
   int32_t standardization;
   int32_t solver;            /* dq4ml_solver */
+  int32_t loss;              /* dq4ml_loss: setLoss("squaredError" | "huber"); the lab leaves the default (App:120-123) */
+  double epsilon;            /* setEpsilon: the huber loss's shape parameter, > 1.0 (Spark default 1.35) */
 } dq4ml_lr_params;
 
 /* Sum-all-reduce of `count` doubles in place over all ranks; buf is HOST memory.  Return 0 on success. */
@@ -132,14 +135,19 @@ int dq4ml_ctx_set_gram_tier(dq4ml_ctx* ctx, int tier);
  * kernel time and the number of passes since it was enabled. */
 int dq4ml_ctx_enable_pass_timing(dq4ml_ctx* ctx, int enable);
 int dq4ml_ctx_pass_timing(dq4ml_ctx* ctx, double* total_ms, int64_t* passes);
+/* The individual kernel times behind that sum, in launch order (for an l-bfgs fit: the summarizer pass first, then one
+ * loss/gradient pass per evaluation): copies up to cap values to ms (HOST) and returns how many passes were timed. */
+int dq4ml_ctx_pass_times(dq4ml_ctx* ctx, double* ms, int32_t cap);
 
 /* Row-sharded training across GPUs: replaces Spark's treeAggregate merge of partition aggregators
  * (RDD.treeAggregate inside WeightedLeastSquares.fit / RDDLossFunction.calculate, reached from App:126).
  * Either bind an NCCL communicator (device-side ncclAllReduce on the ctx stream) ... */
 int dq4ml_nccl_unique_id(void* id128 /* 128 bytes, host */);
 int dq4ml_ctx_init_nccl(dq4ml_ctx* ctx, const void* id128, int rank, int world_size);
-/* ... or supply a host callback (e.g. gloo through the caller's runtime). */
-int dq4ml_ctx_set_allreduce(dq4ml_ctx* ctx, dq4ml_allreduce_fn fn, void* user);
+/* ... or supply a host callback (e.g. gloo through the caller's runtime) together with this process's position among
+ * the ranks: min / max statistics and the summarizer's centres travel through the sum in per-rank slots, so the library
+ * has to know rank and world_size (0 <= rank < world_size).  fn == NULL unbinds. */
+int dq4ml_ctx_set_allreduce(dq4ml_ctx* ctx, dq4ml_allreduce_fn fn, void* user, int rank, int world_size);
 /* Exposed for tests: sum `count` doubles (host buffer) over the ranks bound to ctx; identity when unbound. */
 int dq4ml_ctx_allreduce(dq4ml_ctx* ctx, double* buf, int64_t count);
 
@@ -181,6 +189,13 @@ int dq4ml_dq_filter(dq4ml_ctx* ctx, const int32_t* guest, const double* price, i
                     const dq4ml_dq_params* params, int32_t* guest_out, double* price_out, int64_t* n_out,
                     int64_t* n_after_rule1);
 
+/* Row-sharded DQ section: every rank compacts its own contiguous row shard with dq4ml_dq_filter and the output stays
+ * sharded (Spark: each partition of the filtered Dataset, App:78,90, stays where it is).  This collective -- every rank
+ * bound to the ctx must call it -- turns the local survivor counts into positions in the global, order-preserving
+ * output: offset (HOST) = survivors on all lower ranks, total (HOST, nullable) = survivors on all ranks.  Identity
+ * (offset 0, total n_out_local) when no ranks are bound. */
+int dq4ml_dq_filter_global_offset(dq4ml_ctx* ctx, int64_t n_out_local, int64_t* offset, int64_t* total);
+
 /* The same filter for callers that cannot let the library allocate.  No counterpart in the reference: it exists for
  * hosts where the GPU's memory is already owned by another allocator (an executor-wide memory pool, say), or where the
  * device-wide stall inside cudaMalloc/cudaFree is not tolerable.  It takes no dq4ml_ctx and calls no allocator of any
@@ -188,10 +203,12 @@ int dq4ml_dq_filter(dq4ml_ctx* ctx, const int32_t* guest, const double* price, i
  * (about 128 KB of every GPU that loads libdq4ml.so, held until the process exits), which caps one call at
  * DQ4ML_NOALLOC_MAX_ROWS rows -- larger inputs are refused with DQ4ML_ERR_UNSUPPORTED.
  *   - Call it with the device that owns the buffers current (cudaSetDevice); `stream` is a cudaStream_t (NULL = the
- *     default stream).  guest/price/guest_out/price_out must be DEVICE memory (inputs 16-byte aligned, outputs sized
- *     for n rows); n_out and n_after_rule1 (nullable) are HOST int64.  The call returns after `stream` has drained.
- *   - The first call on each device looks up the array's device address; make that first call before starting any
- *     stream capture.
+ *     default stream).  guest/price/guest_out/price_out must be DEVICE memory (outputs sized for n rows); n_out and
+ *     n_after_rule1 (nullable) are HOST int64.
+ *   - Every call copies the two row counts back to the host and waits for `stream` to drain before it returns
+ *     (cudaMemcpyAsync + cudaStreamSynchronize), so it must never be issued on a stream that is being captured.
+ *   - The first call on each device also looks up the array's device address (cudaGetSymbolAddress); make that first
+ *     call before any stream capture starts anywhere in the process.
  *   - All calls on a device share the one array, and it keeps whatever the previous call left there; each call
  *     re-zeroes the part it is about to use, on `stream`, before its kernel runs.  Two calls whose GPU work overlaps
  *     (different streams or threads) would race on it: serialise them.

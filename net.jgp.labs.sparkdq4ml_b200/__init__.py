@@ -8,7 +8,7 @@ from . import _capi as capi  # noqa: F401
 from .runtime import Context, shard_bounds  # noqa: F401
 from .dq import (  # noqa: F401
     DoubleType, MinimumPriceDataQualityService, PriceCorrelationDataQualityService, MinimumPriceDataQualityUdf,
-    PriceCorrelationDataQualityUdf, UDFRegistration, callUDF, dq_filter)
+    PriceCorrelationDataQualityUdf, UDFRegistration, callUDF, dq_filter, dq_filter_global_offset)
 from .ml import (  # noqa: F401
     Frame, VectorAssembler, LinearRegression, LinearRegressionModel, LinearRegressionTrainingSummary)
 from .app import DataQuality4MachineLearningApp, parse_lab_csv  # noqa: F401

@@ -20,6 +20,8 @@ ERR_INVALID, ERR_CUDA, ERR_NULL_VALUE, ERR_NO_DEVICE, ERR_SINGULAR, ERR_COMM, ER
 I32, F64 = 0, 1
 SOLVER_AUTO, SOLVER_NORMAL, SOLVER_LBFGS = 0, 1, 2
 SOLVERS = {"auto": SOLVER_AUTO, "normal": SOLVER_NORMAL, "l-bfgs": SOLVER_LBFGS}
+LOSSES = {"squaredError": 0, "huber": 1}
+ABI_VERSION = 2
 
 
 class Dq4mlError(RuntimeError):
@@ -51,7 +53,7 @@ class DqFused(C.Structure):
 class LrParams(C.Structure):
     _fields_ = [("max_iter", C.c_int32), ("reg_param", C.c_double), ("elastic_net_param", C.c_double),
                 ("tol", C.c_double), ("fit_intercept", C.c_int32), ("standardization", C.c_int32),
-                ("solver", C.c_int32)]
+                ("solver", C.c_int32), ("loss", C.c_int32), ("epsilon", C.c_double)]
 
 
 class SynthParams(C.Structure):
@@ -72,9 +74,10 @@ SIGNATURES = {
     "dq4ml_ctx_launch_count": (C.c_int64, [C.c_void_p]),
     "dq4ml_ctx_enable_pass_timing": (C.c_int, [C.c_void_p, C.c_int]),
     "dq4ml_ctx_pass_timing": (C.c_int, [C.c_void_p, C.POINTER(C.c_double), C.POINTER(C.c_int64)]),
+    "dq4ml_ctx_pass_times": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32]),
     "dq4ml_nccl_unique_id": (C.c_int, [C.c_void_p]),
     "dq4ml_ctx_init_nccl": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int]),
-    "dq4ml_ctx_set_allreduce": (C.c_int, [C.c_void_p, ALLREDUCE_FN, C.c_void_p]),
+    "dq4ml_ctx_set_allreduce": (C.c_int, [C.c_void_p, ALLREDUCE_FN, C.c_void_p, C.c_int, C.c_int]),
     "dq4ml_ctx_allreduce": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64]),
     "dq4ml_device_alloc": (C.c_int, [C.c_void_p, C.c_int64, C.POINTER(C.c_void_p)]),
     "dq4ml_device_free": (C.c_int, [C.c_void_p, C.c_void_p]),
@@ -89,6 +92,7 @@ SIGNATURES = {
                                                  C.c_void_p, C.POINTER(DqParams)]),
     "dq4ml_dq_filter": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.POINTER(DqParams), C.c_void_p,
                                   C.c_void_p, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]),
+    "dq4ml_dq_filter_global_offset": (C.c_int, [C.c_void_p, C.c_int64, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]),
     "dq4ml_dq_filter_noalloc": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.POINTER(DqParams), C.c_void_p,
                                           C.c_void_p, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]),
     "dq4ml_csv_parse": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_int64, C.POINTER(C.c_int64)]),
@@ -143,7 +147,7 @@ def lib():
             fn = getattr(L, name)
             fn.restype = res
             fn.argtypes = args
-        if L.dq4ml_abi_version() != 1:
+        if L.dq4ml_abi_version() != ABI_VERSION:
             raise ImportError("libdq4ml.so ABI version mismatch")
         _lib = L
     return _lib

@@ -34,6 +34,17 @@ void set_error(const char* fmt, ...) {
 }
 const char* get_error() { return g_error.c_str(); }
 
+void collect_pass_time(dq4ml_ctx* ctx) {  // call after the stream has been synchronised
+  if (!ctx->pass_event_pending) return;
+  ctx->pass_event_pending = false;
+  float ms = 0.f;
+  if (cudaEventElapsedTime(&ms, ctx->pass_ev0, ctx->pass_ev1) == cudaSuccess) {
+    ctx->pass_ms_total += ms;
+    ++ctx->pass_count;
+    if (ctx->pass_ms_list.size() < 65536) ctx->pass_ms_list.push_back(ms);
+  }
+}
+
 namespace {
 
 int cuda_fail(cudaError_t e, const char* what) {
@@ -168,8 +179,6 @@ int check_ctx(const dq4ml_ctx* ctx) {
   }
   return DQ4ML_OK;
 }
-
-void collect_pass_time(dq4ml_ctx* ctx);
 
 // ---- cross-rank sum of the result vector sitting in ctx->scratch.result; leaves it in ctx->h_result ----------------
 int finish_result(dq4ml_ctx* ctx, int64_t count, bool reduce = true) {
@@ -318,16 +327,6 @@ cudaError_t timed_stream_pass(dq4ml_ctx* ctx, StreamOpKind op, const DeviceCols&
   return e;
 }
 
-void collect_pass_time(dq4ml_ctx* ctx) {  // call after the stream has been synchronised
-  if (!ctx->pass_event_pending) return;
-  ctx->pass_event_pending = false;
-  float ms = 0.f;
-  if (cudaEventElapsedTime(&ms, ctx->pass_ev0, ctx->pass_ev1) == cudaSuccess) {
-    ctx->pass_ms_total += ms;
-    ++ctx->pass_count;
-  }
-}
-
 // WLS moments of a small-d table via the streaming kernel; result in `out` with the public layout.
 int wls_moments_small(dq4ml_ctx* ctx, const PassInputs& in, int64_t n, double* out) {
   const int d = in.cols.n;
@@ -357,10 +356,14 @@ int wls_moments_any(dq4ml_ctx* ctx, const PassInputs& in, int64_t n, double* out
     set_error("label column is required");
     return DQ4ML_ERR_INVALID;
   }
-  const bool tf32 = ctx->gram_tier == DQ4ML_GRAM_TF32X3 && gram_tf32_supported(in.width()) && n > 0;
-  if (in.width() <= 8 && in.weight == nullptr && !tf32) return wls_moments_small(ctx, in, n, out);
-  const int rc = tf32 ? gram_tf32_wls_moments(ctx, in.ptr, in.dtype, in.label, in.weight, in.dq, n, out)
-                      : gram_wls_moments(ctx, in.ptr, in.dtype, in.label, in.weight, in.dq, n, out);
+  // The choice between the three kernels must not depend on this rank's row count: the streaming kernel sums a
+  // bucket-padded vector across ranks and the two Gram kernels the public layout, so every rank has to take the same
+  // branch.  A rank whose shard is empty under the tf32 tier runs the fp64 Gram kernel over zero rows, which adds the
+  // same `len` doubles (all zero) to the cross-rank sum.
+  const bool tf32_tier = ctx->gram_tier == DQ4ML_GRAM_TF32X3 && gram_tf32_supported(in.width());
+  if (in.width() <= 8 && in.weight == nullptr && !tf32_tier) return wls_moments_small(ctx, in, n, out);
+  const int rc = (tf32_tier && n > 0) ? gram_tf32_wls_moments(ctx, in.ptr, in.dtype, in.label, in.weight, in.dq, n, out)
+                                      : gram_wls_moments(ctx, in.ptr, in.dtype, in.label, in.weight, in.dq, n, out);
   // WeightedLeastSquares.Aggregator.add: require(w >= 0.0).  A negative weight turns sqrt(w) into NaN in wSum.
   if (rc == DQ4ML_OK && in.weight != nullptr && !(out[1] == out[1])) {
     set_error("instance weight must be >= 0 and not NaN");
@@ -589,15 +592,18 @@ int reduce_eval_sums(dq4ml_ctx* ctx, double* s) {
   v[7 + 2 * ctx->rank + 1] = s[8];
   // +-inf (a rank without surviving rows) cannot ride a sum next to zeros of other ranks: send finite stand-ins
   const double big = 1.7e308;
-  if (!(v[7 + 2 * ctx->rank] < big)) v[7 + 2 * ctx->rank] = big;
-  if (!(v[7 + 2 * ctx->rank + 1] > -big)) v[7 + 2 * ctx->rank + 1] = -big;
+  if (v[7 + 2 * ctx->rank] > big) v[7 + 2 * ctx->rank] = big;            // a NaN stays a NaN (and survives the sum)
+  if (v[7 + 2 * ctx->rank + 1] < -big) v[7 + 2 * ctx->rank + 1] = -big;
   const int rc = host_allreduce(ctx, v.data(), static_cast<int64_t>(v.size()));
   if (rc != DQ4ML_OK) return rc;
   std::copy(v.begin(), v.begin() + 7, s);
+  // min skips NaN, max is NaN as soon as one rank's is (SQL ordering: NaN is the greatest double)
   double mn = big, mx = -big;
   for (int r = 0; r < world; ++r) {
-    mn = std::min(mn, v[7 + 2 * r]);
-    mx = std::max(mx, v[7 + 2 * r + 1]);
+    const double a = v[7 + 2 * r], b = v[7 + 2 * r + 1];
+    if (a == a && a < mn) mn = a;
+    if (b != b || mx != mx) mx = std::numeric_limits<double>::quiet_NaN();
+    else if (b > mx) mx = b;
   }
   s[7] = mn;
   s[8] = mx;
@@ -614,6 +620,8 @@ LrParams to_params(const dq4ml_lr_params* p) {
     q.fit_intercept = p->fit_intercept != 0;
     q.standardization = p->standardization != 0;
     q.solver = p->solver;
+    q.loss = p->loss;
+    q.epsilon = p->epsilon;
   }
   return q;
 }
@@ -623,6 +631,17 @@ int check_params(const LrParams& p) {
       p.solver > 2) {
     set_error("LinearRegression params out of range (maxIter >= 0, regParam >= 0, 0 <= elasticNetParam <= 1, tol >= 0)");
     return DQ4ML_ERR_INVALID;
+  }
+  if (p.loss != DQ4ML_LOSS_SQUARED_ERROR && p.loss != DQ4ML_LOSS_HUBER) {
+    set_error("unknown loss %d", p.loss);
+    return DQ4ML_ERR_INVALID;
+  }
+  if (p.loss == DQ4ML_LOSS_HUBER) {
+    // LinearRegression.train: require(solver != normal) and require(elasticNetParam == 0.0) for huber; epsilon > 1.0
+    if (p.solver == DQ4ML_SOLVER_NORMAL || p.elastic_net != 0.0 || !(p.epsilon > 1.0)) {
+      set_error("huber loss needs epsilon > 1, elasticNetParam == 0 (L2 only) and a solver other than 'normal'");
+      return DQ4ML_ERR_INVALID;
+    }
   }
   return DQ4ML_OK;
 }
@@ -741,6 +760,7 @@ int dq4ml_ctx_enable_pass_timing(dq4ml_ctx* ctx, int enable) {
   ctx->pass_event_pending = false;
   ctx->pass_ms_total = 0.0;
   ctx->pass_count = 0;
+  ctx->pass_ms_list.clear();
   return DQ4ML_OK;
 }
 
@@ -749,6 +769,16 @@ int dq4ml_ctx_pass_timing(dq4ml_ctx* ctx, double* total_ms, int64_t* passes) {
   if (total_ms != nullptr) *total_ms = ctx->pass_ms_total;
   if (passes != nullptr) *passes = ctx->pass_count;
   return DQ4ML_OK;
+}
+
+int dq4ml_ctx_pass_times(dq4ml_ctx* ctx, double* ms, int32_t cap) {
+  if (check_ctx(ctx) != DQ4ML_OK || (ms == nullptr && cap > 0) || cap < 0) {
+    set_error("pass_times: bad arguments");
+    return DQ4ML_ERR_INVALID;
+  }
+  const int32_t len = static_cast<int32_t>(ctx->pass_ms_list.size());
+  for (int32_t i = 0; i < len && i < cap; ++i) ms[i] = ctx->pass_ms_list[i];
+  return len;
 }
 
 int dq4ml_nccl_unique_id(void* id128) {
@@ -767,10 +797,30 @@ int dq4ml_ctx_init_nccl(dq4ml_ctx* ctx, const void* id128, int rank, int world_s
   return nccl_bind(ctx, id128, rank, world_size);
 }
 
-int dq4ml_ctx_set_allreduce(dq4ml_ctx* ctx, dq4ml_allreduce_fn fn, void* user) {
+int dq4ml_ctx_set_allreduce(dq4ml_ctx* ctx, dq4ml_allreduce_fn fn, void* user, int rank, int world_size) {
   if (check_ctx(ctx) != DQ4ML_OK) return DQ4ML_ERR_INVALID;
+  if (fn == nullptr) {  // unbind
+    ctx->allreduce_cb = nullptr;
+    ctx->allreduce_user = nullptr;
+    if (ctx->nccl == nullptr) {
+      ctx->rank = 0;
+      ctx->world = 1;
+    }
+    return DQ4ML_OK;
+  }
+  // min / max and the summarizer centres are laid out per rank, so the position of this rank must be known
+  if (world_size < 1 || rank < 0 || rank >= world_size) {
+    set_error("set_allreduce: bad rank %d / world size %d", rank, world_size);
+    return DQ4ML_ERR_INVALID;
+  }
+  if (ctx->nccl != nullptr) {
+    set_error("set_allreduce: an NCCL communicator is already bound to this ctx");
+    return DQ4ML_ERR_INVALID;
+  }
   ctx->allreduce_cb = fn;
   ctx->allreduce_user = user;
+  ctx->rank = rank;
+  ctx->world = world_size;
   return DQ4ML_OK;
 }
 
@@ -950,6 +1000,32 @@ int dq4ml_dq_filter(dq4ml_ctx* ctx, const int32_t* guest, const double* price, i
   return DQ4ML_OK;
 }
 
+int dq4ml_dq_filter_global_offset(dq4ml_ctx* ctx, int64_t n_out_local, int64_t* offset, int64_t* total) {
+  if (check_ctx(ctx) != DQ4ML_OK) return DQ4ML_ERR_INVALID;
+  if (n_out_local < 0 || offset == nullptr) {
+    set_error("dq_filter_global_offset: negative count or null output");
+    return DQ4ML_ERR_INVALID;
+  }
+  cudaSetDevice(ctx->device);
+  // an all-gather of the G survivor counts, carried by the one collective the ctx has: each rank fills its own slot of
+  // a zeroed vector and the sum all-reduce assembles it (counts stay far below 2^53, so doubles carry them exactly)
+  const int world = multi_rank(ctx) && ctx->world > 0 ? ctx->world : 1;
+  const int rank = world > 1 ? ctx->rank : 0;
+  std::vector<double> counts(static_cast<size_t>(world), 0.0);
+  counts[rank] = static_cast<double>(n_out_local);
+  const int rc = host_allreduce(ctx, counts.data(), world);
+  if (rc != DQ4ML_OK) return rc;
+  int64_t before = 0, all = 0;
+  for (int r = 0; r < world; ++r) {
+    const int64_t c = static_cast<int64_t>(counts[r]);
+    if (r < rank) before += c;
+    all += c;
+  }
+  *offset = before;
+  if (total != nullptr) *total = all;
+  return DQ4ML_OK;
+}
+
 // ------------------------------------------------------------------------------------------------------------ LinearRegression
 
 dq4ml_lr_params dq4ml_lr_params_default(void) {
@@ -961,6 +1037,8 @@ dq4ml_lr_params dq4ml_lr_params_default(void) {
   p.fit_intercept = 1;
   p.standardization = 1;
   p.solver = DQ4ML_SOLVER_AUTO;
+  p.loss = DQ4ML_LOSS_SQUARED_ERROR;
+  p.epsilon = 1.35;
   return p;
 }
 
@@ -991,10 +1069,14 @@ int dq4ml_wls_solve(const double* moments, int32_t d, const dq4ml_lr_params* par
   dq4ml_lr_params defaults = dq4ml_lr_params_default();
   const LrParams q = params ? p : to_params(&defaults);
   if (check_params(q) != DQ4ML_OK) return DQ4ML_ERR_INVALID;
+  if (q.loss == DQ4ML_LOSS_HUBER) {
+    set_error("wls_solve: the normal-equation solver has no huber loss (Spark: huber requires solver l-bfgs)");
+    return DQ4ML_ERR_INVALID;
+  }
   try {
-    auto* m = new dq4ml_lr_model;
+    auto m = std::make_unique<dq4ml_lr_model>();
     m->m = wls_fit_from_moments(moments, d, q);
-    *out = m;
+    *out = m.release();
     return DQ4ML_OK;
   } catch (const SolveError& e) {
     set_error("%s", e.what.c_str());
@@ -1070,7 +1152,8 @@ int dq4ml_summarize(dq4ml_ctx* ctx, const dq4ml_columns* features, const double*
         double v = all[k];
         for (int w = 1; w < world; ++w) {
           const double o = all[static_cast<size_t>(w) * nacc + k];
-          v = kind == 0 ? v + o : (kind == 1 ? ((v != v || o != o) ? v + o : std::min(v, o)) : ((v != v || o != o) ? v + o : std::max(v, o)));
+          if (kind == 0) v += o;  // min / max skip NaNs like MultivariateOnlineSummarizer.add (`currMin > value` is false on NaN)
+          else if (o == o) v = (v != v) ? o : (kind == 1 ? std::min(v, o) : std::max(v, o));
         }
         r[k] = v;
       }
@@ -1132,6 +1215,10 @@ int dq4ml_linreg_fit_weighted(dq4ml_ctx* ctx, const dq4ml_columns* features, con
   dq4ml_lr_params defaults = dq4ml_lr_params_default();
   const LrParams p = to_params(params != nullptr ? params : &defaults);
   if (check_params(p) != DQ4ML_OK) return DQ4ML_ERR_INVALID;
+  if (p.loss == DQ4ML_LOSS_HUBER) {
+    set_error("huber loss is not built yet");
+    return DQ4ML_ERR_UNSUPPORTED;
+  }
   CallScope scope(ctx);
   const int d = features->n_cols;
   // LinearRegression.train: squared-error loss goes to WeightedLeastSquares when solver is normal, or auto with
@@ -1349,7 +1436,9 @@ int dq4ml_linreg_evaluate(dq4ml_ctx* ctx, const dq4ml_lr_model* m, const dq4ml_c
   const double dof = cnt - static_cast<double>(m->m.coefficients.size()) - k_int;
   metrics[10] = dof;
   metrics[11] = 1.0 - (1.0 - r2) * (cnt - k_int) / dof;
-  metrics[12] = cnt > 0 ? s[7] : 0.0;   // devianceResiduals: min and max residual
+  // devianceResiduals: SQL min / max of the residual column (NaN ordered greatest: max is NaN if any residual is, min
+  // only if all are -- the kernel's NaN-skipping min is then still at its identity)
+  metrics[12] = cnt > 0 ? ((s[8] != s[8] && !(s[7] < 1.7e308)) ? s[8] : s[7]) : 0.0;
   metrics[13] = cnt > 0 ? s[8] : 0.0;
   metrics[14] = sr;
   metrics[15] = sry;

@@ -9,6 +9,7 @@
 #include <cstdio>
 #include <string>
 #include <unordered_map>
+#include <vector>
 
 #include "../../include/dq4ml.h"
 #include "kernels.hpp"
@@ -48,6 +49,7 @@ struct dq4ml_ctx {
   cudaEvent_t pass_ev0 = nullptr, pass_ev1 = nullptr;
   double pass_ms_total = 0.0;
   int64_t pass_count = 0;
+  std::vector<float> pass_ms_list;  // one entry per timed pass since timing was enabled (capped)
   // ranks
   dq4ml::NcclBinding* nccl = nullptr;
   int rank = 0, world = 1;
@@ -59,6 +61,9 @@ namespace dq4ml {
 
 constexpr size_t kResultDoubles = 1 << 16;  // fits the packed Gram of d = 256 (33 411 doubles)
 constexpr size_t kPartialsBytes = 8u << 20;
+
+// api.cpp: after the ctx stream has been synchronised, folds the pending pass-timing event pair into the ctx counters
+void collect_pass_time(dq4ml_ctx* ctx);
 
 // dist.cpp
 int nccl_unique_id(void* id128);

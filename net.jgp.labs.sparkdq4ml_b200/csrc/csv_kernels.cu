@@ -15,6 +15,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <string>
+#include <utility>
 #include <vector>
 
 #include "context.hpp"
@@ -266,18 +267,22 @@ extern "C" int dq4ml_csv_parse(dq4ml_ctx* ctx, const char* data, int64_t len, in
     set_error("csv_parse: %lld records but room for %lld", static_cast<long long>(total), static_cast<long long>(cap));
     return DQ4ML_ERR_INVALID;
   }
-  // exact host path for the (rare) decimals outside the one-rounding fast path
+  // exact host path for the (rare) decimals outside the one-rounding fast path.  Every copy below goes through
+  // ctx->stream (a non-blocking stream is not ordered against the legacy default stream) and is drained before returning.
   std::vector<long long> slow(static_cast<size_t>(total));
   if (total > 0) {
-    if ((e = cudaMemcpy(slow.data(), d_slow, static_cast<size_t>(total) * 8, cudaMemcpyDeviceToHost)) != cudaSuccess) return cuda_err(e, "csv D2H");
+    if ((e = cudaMemcpyAsync(slow.data(), d_slow, static_cast<size_t>(total) * 8, cudaMemcpyDeviceToHost, ctx->stream)) != cudaSuccess) return cuda_err(e, "csv D2H");
+    if ((e = cudaStreamSynchronize(ctx->stream)) != cudaSuccess) return cuda_err(e, "csv D2H");
   }
   std::vector<char> host_copy;
+  std::vector<std::pair<int64_t, double>> fixups;
   for (int64_t r = 0; r < total; ++r) {
     if (slow[r] < 0) continue;
     if (host_copy.empty()) {
       host_copy.resize(static_cast<size_t>(len));
       if (data_dev) {
-        if ((e = cudaMemcpy(host_copy.data(), data, static_cast<size_t>(len), cudaMemcpyDeviceToHost)) != cudaSuccess) return cuda_err(e, "csv D2H");
+        if ((e = cudaMemcpyAsync(host_copy.data(), data, static_cast<size_t>(len), cudaMemcpyDeviceToHost, ctx->stream)) != cudaSuccess) return cuda_err(e, "csv D2H");
+        if ((e = cudaStreamSynchronize(ctx->stream)) != cudaSuccess) return cuda_err(e, "csv D2H");
       } else {
         std::memcpy(host_copy.data(), data, static_cast<size_t>(len));
       }
@@ -293,9 +298,12 @@ extern "C" int dq4ml_csv_parse(dq4ml_ctx* ctx, const char* data, int64_t len, in
       set_error("csv_parse: malformed record %lld (decimal field `%s`)", static_cast<long long>(r), field.c_str());
       return DQ4ML_ERR_INVALID;
     }
-    if ((e = cudaMemcpy(d_price + r, &v, 8, cudaMemcpyHostToDevice)) != cudaSuccess) return cuda_err(e, "csv fix-up");
+    fixups.emplace_back(r, v);
   }
-  if (!g_dev && total > 0 && (e = cudaMemcpy(guest_out, d_guest, static_cast<size_t>(total) * 4, cudaMemcpyDeviceToHost)) != cudaSuccess) return cuda_err(e, "csv D2H");
-  if (!p_dev && total > 0 && (e = cudaMemcpy(price_out, d_price, static_cast<size_t>(total) * 8, cudaMemcpyDeviceToHost)) != cudaSuccess) return cuda_err(e, "csv D2H");
+  for (const auto& f : fixups)  // `fixups` outlives the copies: the stream is drained below
+    if ((e = cudaMemcpyAsync(d_price + f.first, &f.second, 8, cudaMemcpyHostToDevice, ctx->stream)) != cudaSuccess) return cuda_err(e, "csv fix-up");
+  if (!g_dev && total > 0 && (e = cudaMemcpyAsync(guest_out, d_guest, static_cast<size_t>(total) * 4, cudaMemcpyDeviceToHost, ctx->stream)) != cudaSuccess) return cuda_err(e, "csv D2H");
+  if (!p_dev && total > 0 && (e = cudaMemcpyAsync(price_out, d_price, static_cast<size_t>(total) * 8, cudaMemcpyDeviceToHost, ctx->stream)) != cudaSuccess) return cuda_err(e, "csv D2H");
+  if ((e = cudaStreamSynchronize(ctx->stream)) != cudaSuccess) return cuda_err(e, "csv drain");
   return DQ4ML_OK;
 }

@@ -89,13 +89,21 @@ __device__ __forceinline__ void load_i32(const int* col, int64_t row, int (&v)[R
   }
 }
 
-enum ReduceKind { kSum = 0, kMin = 1, kMax = 2 };
+// kMin / kMax skip NaNs, which is what both of their Spark counterparts do for everything but one case:
+// MultivariateOnlineSummarizer.add updates with `currMax < value` / `currMin > value` (false on NaN), and the SQL
+// min()/max() behind LinearRegressionSummary.devianceResiduals order NaN above every number, so min() never returns it
+// (unless nothing else is there) while max() always does -- that one case is kMaxNan.
+enum ReduceKind { kSum = 0, kMin = 1, kMax = 2, kMaxNan = 3 };
 
-__device__ __forceinline__ double combine(int kind, double a, double b) {
-  // fmin/fmax would drop NaNs; a NaN that survived DQ must poison min/max exactly like it poisons the sums
+__host__ __device__ __forceinline__ double combine(int kind, double a, double b) {
   if (kind == kSum) return a + b;
-  if (kind == kMin) return (a != a || b != b) ? (a + b) : (a < b ? a : b);
-  return (a != a || b != b) ? (a + b) : (a > b ? a : b);
+  if (kind == kMin) return (b != b) ? a : ((a != a) ? b : (a < b ? a : b));
+  if (kind == kMax) return (b != b) ? a : ((a != a) ? b : (a > b ? a : b));
+  return (a != a || b != b) ? (a + b) : (a > b ? a : b);  // kMaxNan: a NaN wins
+}
+
+__host__ __device__ constexpr double reduce_identity(int kind) {
+  return kind == kMin ? __builtin_huge_val() : ((kind == kMax || kind == kMaxNan) ? -__builtin_huge_val() : 0.0);
 }
 
 __device__ __forceinline__ double warp_reduce(double v, int kind) {

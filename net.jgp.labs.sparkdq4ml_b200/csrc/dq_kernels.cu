@@ -487,8 +487,9 @@ extern "C" int dq4ml_dq_filter_noalloc(void* stream, const int32_t* guest, const
     set_error("dq_filter_noalloc: in-place compaction is not supported");
     return DQ4ML_ERR_INVALID;
   }
-  if (((reinterpret_cast<uintptr_t>(guest) | reinterpret_cast<uintptr_t>(price)) & 15u) != 0) {
-    set_error("dq_filter_noalloc: input columns must be 16-byte aligned device memory");
+  if ((reinterpret_cast<uintptr_t>(guest) & 3u) != 0 || (reinterpret_cast<uintptr_t>(price) & 7u) != 0 ||
+      (reinterpret_cast<uintptr_t>(guest_out) & 3u) != 0 || (reinterpret_cast<uintptr_t>(price_out) & 7u) != 0) {
+    set_error("dq_filter_noalloc: columns must be naturally aligned (int32: 4 bytes, double: 8 bytes)");
     return DQ4ML_ERR_INVALID;
   }
   *n_out = 0;
@@ -504,7 +505,8 @@ extern "C" int dq4ml_dq_filter_noalloc(void* stream, const int32_t* guest, const
   const dq4ml_dq_params p = params != nullptr ? *params : dq4ml_dq_params_default();
   int64_t launched = 0;
   // The array still holds the previous call's words: launch_dq_filter zeroes the counters and the first
-  // ceil(n / 2048) look-back words on `s` (cudaMemsetAsync, no allocation) before the kernel reads them.
+  // ceil(n / 4096) look-back words (one per tile of kFilterTile rows) on `s` (cudaMemsetAsync, no allocation) before
+  // the kernel reads them.
   e = launch_dq_filter(guest, price, n, p, guest_out, price_out, scratch + kNoAllocHeaderWords, scratch, s, &launched);
   unsigned long long counts[2] = {0, 0};
   if (e == cudaSuccess) e = cudaMemcpyAsync(counts, scratch, sizeof(counts), cudaMemcpyDeviceToHost, s);

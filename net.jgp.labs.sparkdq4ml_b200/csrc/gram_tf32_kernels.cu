@@ -759,14 +759,7 @@ int gram_tf32_wls_moments(dq4ml_ctx* ctx, const std::vector<const void*>& col_pt
   }
   if ((e = cudaMemcpyAsync(ctx->gram_host, d_out, out_bytes, cudaMemcpyDeviceToHost, ctx->stream)) != cudaSuccess) return fail(e, "gram D2H");
   if ((e = cudaStreamSynchronize(ctx->stream)) != cudaSuccess) return fail(e, "tf32 gram pass");
-  if (ctx->pass_event_pending) {
-    ctx->pass_event_pending = false;
-    float ms = 0.f;
-    if (cudaEventElapsedTime(&ms, ctx->pass_ev0, ctx->pass_ev1) == cudaSuccess) {
-      ctx->pass_ms_total += ms;
-      ++ctx->pass_count;
-    }
-  }
+  collect_pass_time(ctx);
   if (ctx->nccl == nullptr && ctx->allreduce_cb != nullptr) {
     if (ctx->allreduce_cb(ctx->allreduce_user, ctx->gram_host, len) != 0) {
       set_error("all-reduce callback failed");

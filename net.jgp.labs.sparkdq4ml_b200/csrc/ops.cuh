@@ -106,7 +106,7 @@ struct SummFullOp {
     return k == 0 ? kSum : ((k - 1) % PER == 2 ? kMin : ((k - 1) % PER == 3 ? kMax : kSum));
   }
   __host__ __device__ static constexpr double identity(int k) {
-    return kind(k) == kMin ? __builtin_huge_val() : (kind(k) == kMax ? -__builtin_huge_val() : 0.0);
+    return reduce_identity(kind(k));
   }
 
   __device__ __forceinline__ double row(double (&acc)[NACC], const double* c, const double (&x)[DMAX], double,
@@ -140,10 +140,14 @@ struct GradOp {
   __host__ __device__ static constexpr double identity(int) { return 0.0; }
   __host__ __device__ static constexpr int kind(int) { return kSum; }
 
+  // This pass runs without the DQ columns: a row the rules dropped is recognised by its difference, which the row pass
+  // wrote as exactly 0, and its features (possibly NaN/Inf garbage, 0 * NaN = NaN) are kept out of the sums.  A kept row
+  // whose difference is exactly 0 contributes 0 either way.
   __device__ __forceinline__ double row(double (&acc)[NACC], const double*, const double (&x)[DMAX], double y, bool,
                                         int) const {
+    const bool live = y != 0.0;
 #pragma unroll
-    for (int j = 0; j < DMAX; ++j) acc[j] = fma(y, x[j], acc[j]);
+    for (int j = 0; j < DMAX; ++j) acc[j] = fma(y, live ? x[j] : 0.0, acc[j]);
     return 0.0;
   }
 };
@@ -223,7 +227,7 @@ struct WResidOp {
   static constexpr int NACC = 3;
   static constexpr int NCONST = 0;
   static constexpr bool HAS_OUT = false;
-  __host__ __device__ static constexpr int kind(int k) { return k == 1 ? kMin : (k == 2 ? kMax : kSum); }
+  __host__ __device__ static constexpr int kind(int k) { return k == 1 ? kMin : (k == 2 ? kMaxNan : kSum); }
   __host__ __device__ static constexpr double identity(int k) {
     return k == 1 ? __builtin_huge_val() : (k == 2 ? -__builtin_huge_val() : 0.0);
   }
@@ -233,7 +237,7 @@ struct WResidOp {
     acc[0] = fma(w * r, r, acc[0]);
     const double s = sqrt(w) * r;
     acc[1] = combine(kMin, acc[1], keep ? s : __builtin_huge_val());
-    acc[2] = combine(kMax, acc[2], keep ? s : -__builtin_huge_val());
+    acc[2] = combine(kMaxNan, acc[2], keep ? s : -__builtin_huge_val());
     return 0.0;
   }
 };
@@ -249,7 +253,7 @@ struct EvalOp {
   double coef[DMAX];
   double intercept;
   int mode;
-  __host__ __device__ static constexpr int kind(int k) { return k == 7 ? kMin : (k == 8 ? kMax : kSum); }
+  __host__ __device__ static constexpr int kind(int k) { return k == 7 ? kMin : (k == 8 ? kMaxNan : kSum); }
   __host__ __device__ static constexpr double identity(int k) {
     return k == 7 ? __builtin_huge_val() : (k == 8 ? -__builtin_huge_val() : 0.0);
   }
@@ -270,7 +274,7 @@ struct EvalOp {
     acc[5] += res;
     acc[6] = fma(res, y, acc[6]);
     acc[7] = combine(kMin, acc[7], keep ? res : __builtin_huge_val());
-    acc[8] = combine(kMax, acc[8], keep ? res : -__builtin_huge_val());
+    acc[8] = combine(kMaxNan, acc[8], keep ? res : -__builtin_huge_val());
     return mode == 0 ? yhat : res;
   }
 };

@@ -24,6 +24,8 @@ struct LrParams {
   bool fit_intercept = true;
   bool standardization = true;
   int solver = 0;  // 0 auto, 1 normal, 2 l-bfgs
+  int loss = 0;    // 0 squaredError, 1 huber
+  double epsilon = 1.35;
 };
 
 struct LrModel {

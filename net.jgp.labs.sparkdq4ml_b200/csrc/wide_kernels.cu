@@ -30,7 +30,7 @@ struct WideArgs {
 };
 
 constexpr int kWideAcc = 9;
-__device__ __forceinline__ int wide_kind(int k) { return k == 7 ? kMin : (k == 8 ? kMax : kSum); }
+__device__ __forceinline__ int wide_kind(int k) { return k == 7 ? kMin : (k == 8 ? kMaxNan : kSum); }
 
 __global__ void __launch_bounds__(kBlock) wide_rows_kernel(const WideArgs a) {
   double acc[kWideAcc] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0, __builtin_huge_val(), -__builtin_huge_val()};
@@ -95,7 +95,7 @@ __global__ void __launch_bounds__(kBlock) wide_rows_kernel(const WideArgs a) {
     acc[5] += r0 + r1;
     acc[6] = fma(r0, ys0, fma(r1, ys1, acc[6]));
     acc[7] = combine(kMin, acc[7], combine(kMin, k0 ? r0 : __builtin_huge_val(), k1 ? r1 : __builtin_huge_val()));
-    acc[8] = combine(kMax, acc[8], combine(kMax, k0 ? r0 : -__builtin_huge_val(), k1 ? r1 : -__builtin_huge_val()));
+    acc[8] = combine(kMaxNan, acc[8], combine(kMaxNan, k0 ? r0 : -__builtin_huge_val(), k1 ? r1 : -__builtin_huge_val()));
     if (a.row_out != nullptr) {
       const double o0 = a.mode == 0 ? pred0 : r0, o1 = a.mode == 0 ? pred1 : r1;
       if (pair) stg_stream_d2(a.row_out + row, make_double2(o0, o1));
@@ -117,7 +117,7 @@ __global__ void __launch_bounds__(kBlock) wide_rows_kernel(const WideArgs a) {
   __threadfence();
   for (int k = 0; k < kWideAcc; ++k) {
     const int kind = wide_kind(k);
-    double v = kind == kMin ? __builtin_huge_val() : (kind == kMax ? -__builtin_huge_val() : 0.0);
+    double v = reduce_identity(kind);
     for (unsigned b = threadIdx.x; b < gridDim.x; b += kBlock) v = combine(kind, v, __ldcg(a.partials + static_cast<size_t>(b) * kWideAcc + k));
     v = block_reduce(v, kind, s_red);
     if (threadIdx.x == 0) a.result[k] = v;

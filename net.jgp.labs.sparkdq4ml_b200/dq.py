@@ -136,3 +136,11 @@ def dq_filter(ctx, guest, price, params=None):
                                            capi.buf_ptr(po), C.byref(n_out), C.byref(n1)))
     m = int(n_out.value)
     return go[:m], po[:m], int(n1.value)
+
+
+def dq_filter_global_offset(ctx, n_out_local):
+    """Row-sharded DQ section (one rank per GPU): collective; returns (offset of this rank's survivors in the global
+    order-preserving output, total survivors over all ranks)."""
+    off, tot = C.c_int64(0), C.c_int64(0)
+    capi.check(capi.lib().dq4ml_dq_filter_global_offset(ctx.handle, int(n_out_local), C.byref(off), C.byref(tot)))
+    return int(off.value), int(tot.value)

@@ -103,6 +103,26 @@ class LinearRegression:
         self._fit_intercept, self._standardization, self._solver = True, True, "auto"
         self._features_col, self._label_col, self._prediction_col = "features", "label", "prediction"
         self._weight_col = None
+        self._loss, self._epsilon = "squaredError", 1.35
+
+    def setLoss(self, v):
+        """"squaredError" (default) or "huber" (Spark 2.3+: robust regression, l-bfgs only, L2 regularisation only)."""
+        if v not in capi.LOSSES:
+            raise ValueError(f"loss must be one of {sorted(capi.LOSSES)}")
+        self._loss = v
+        return self
+
+    def getLoss(self):
+        return self._loss
+
+    def setEpsilon(self, v):
+        if not float(v) > 1.0:
+            raise ValueError("epsilon must be > 1.0")
+        self._epsilon = float(v)
+        return self
+
+    def getEpsilon(self):
+        return self._epsilon
 
     def setWeightCol(self, v):
         """Instance weights (Spark: unset / empty = every weight 1.0; the lab never sets it)."""
@@ -170,7 +190,8 @@ class LinearRegression:
 
     def _c_params(self):
         return capi.LrParams(self._max_iter, self._reg_param, self._elastic_net, self._tol, int(self._fit_intercept),
-                             int(self._standardization), capi.SOLVERS[self._solver])
+                             int(self._standardization), capi.SOLVERS[self._solver], capi.LOSSES[self._loss],
+                             self._epsilon)
 
     def fit(self, df: Frame) -> "LinearRegressionModel":
         feats = df.columns[self._features_col]

@@ -68,6 +68,12 @@ class Context:
         capi.check(capi.lib().dq4ml_ctx_pass_timing(self._h, C.byref(ms), C.byref(cnt)))
         return float(ms.value), int(cnt.value)
 
+    def pass_times(self):
+        """Kernel time (ms) of every aggregation pass since enable_pass_timing, in launch order."""
+        buf = np.zeros(4096, dtype=np.float64)
+        n = capi.check(capi.lib().dq4ml_ctx_pass_times(self._h, buf.ctypes.data, buf.size))
+        return buf[:min(n, buf.size)].tolist()
+
     # ---- ranks -------------------------------------------------------------------------------------------------
     def bind_torch_distributed(self, use_nccl=None):
         """Row-sharded mode: binds this ctx to the torch.distributed world (one process per GPU).
@@ -97,8 +103,13 @@ class Context:
             self.set_allreduce(torch_allreduce_callback())
         return self
 
-    def set_allreduce(self, fn):
-        """fn(numpy float64 array) sums it in place over ranks."""
+    def set_allreduce(self, fn, rank=None, world_size=None):
+        """fn(numpy float64 array) sums it in place over ranks; rank / world_size (default: this Context's, as set by
+        bind_torch_distributed) tell the library which per-rank slot of the min / max and centre vectors is its own."""
+        if rank is not None:
+            self.rank = int(rank)
+        if world_size is not None:
+            self.world_size = int(world_size)
 
         def _cb(_user, ptr, count):
             try:
@@ -109,7 +120,7 @@ class Context:
                 return 1
 
         self._cb = capi.ALLREDUCE_FN(_cb)
-        capi.check(capi.lib().dq4ml_ctx_set_allreduce(self._h, self._cb, None))
+        capi.check(capi.lib().dq4ml_ctx_set_allreduce(self._h, self._cb, None, self.rank, self.world_size))
 
     def allreduce(self, a: np.ndarray):
         a = np.ascontiguousarray(a, dtype=np.float64)

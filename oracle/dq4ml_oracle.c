@@ -193,6 +193,92 @@ void orc_wls_moments(const orc_column* features, int32_t d, const double* label,
   free(parts);
 }
 
+/* ------------------------------------------------------------------ row-at-a-time variant of the lab's pipeline
+ * The columnar fold above is the strong CPU baseline.  This one keeps the shape Spark executes for each partition of
+ * the lab's job: one row at a time through the boxed UDF call chain
+ *   MinimumPriceDataQualityUdf.call (MinUdf:11-13) -> MinimumPriceDataQualityService.checkMinimumPrice (MinSvc:7-13)
+ *   -> filter price_no_min > 0 (App:77-78)
+ *   -> PriceCorrelationDataQualityUdf.call (CorrUdf:11-16, null guard) -> checkPriceRange (CorrSvc:5-10)
+ *   -> filter price_correct_correl > 0 (App:89-90)
+ *   -> label alias + VectorAssembler (App:101-113: a dense vector per row) -> Aggregator.add
+ * with every stage an out-of-line call on boxed (pointer) values, nothing fused or vectorised by the compiler.
+ * Results equal orc_wls_moments with the DQ columns given (same adds in the same order per partition). */
+typedef struct { double v; int is_null; } boxed_double;
+typedef struct { int32_t v; int is_null; } boxed_int;
+
+static __attribute__((noinline)) int rw_udf_min_price(const boxed_double* t1, boxed_double* out) {
+  if (t1->is_null) return -1; /* NullPointerException on unboxing (MinUdf:12) */
+  out->v = orc_check_minimum_price(t1->v);
+  out->is_null = 0;
+  return 0;
+}
+static __attribute__((noinline)) void rw_udf_price_corr(const boxed_double* price, const boxed_int* guest, boxed_double* out) {
+  out->is_null = 0;
+  if (price->is_null || guest->is_null) { out->v = -1.0; return; } /* CorrUdf:12-14 */
+  out->v = orc_check_price_range(price->v, guest->v);
+}
+static __attribute__((noinline)) int rw_filter_gt_zero(const boxed_double* c) { return !c->is_null && orc_spark_gt_zero(c->v); }
+static __attribute__((noinline)) void rw_assemble(const boxed_int* guest, double* vec) { vec[0] = (double)guest->v; } /* App:106-113 */
+static __attribute__((noinline)) void rw_aggregator_add(double* out, int32_t d, const double* x, double l, double w) {
+  double* aSum = out + 5;
+  double* abSum = aSum + d;
+  double* aaSum = abSum + d;
+  out[0] += 1.0;
+  out[1] += w;
+  out[2] += w * w;
+  out[3] += w * l;
+  out[4] += w * l * l;
+  const double wl = w * l;
+  for (int32_t j = 0; j < d; ++j) aSum[j] += w * x[j];
+  for (int32_t j = 0; j < d; ++j) abSum[j] += wl * x[j];
+  int64_t p = 0;
+  for (int32_t j = 0; j < d; ++j) {
+    const double t = w * x[j];
+    for (int32_t k = 0; k <= j; ++k) aaSum[p++] += x[k] * t;
+  }
+}
+
+typedef int (*rw_udf1_fn)(const boxed_double*, boxed_double*);
+typedef void (*rw_udf2_fn)(const boxed_double*, const boxed_int*, boxed_double*);
+
+static void rw_partition(const int32_t* guest, const double* price, int64_t lo, int64_t hi, double* out,
+                         rw_udf1_fn volatile udf1, rw_udf2_fn volatile udf2) {
+  double vec[1];
+  for (int64_t i = lo; i < hi; ++i) {
+    boxed_double p0 = {price[i], 0}, p1, p2;
+    boxed_int g = {guest[i], 0};
+    if (udf1(&p0, &p1) != 0) continue;      /* callUDF("minimumPriceRule", price)            App:69 */
+    if (!rw_filter_gt_zero(&p1)) continue;  /* WHERE price_no_min > 0                         App:77-78 */
+    udf2(&p1, &g, &p2);                     /* callUDF("priceCorrelationRule", price, guest)  App:87 */
+    if (!rw_filter_gt_zero(&p2)) continue;  /* WHERE price_correct_correl > 0                 App:89-90 */
+    rw_assemble(&g, vec);
+    rw_aggregator_add(out, 1, vec, p2.v, 1.0);
+  }
+}
+
+void orc_lab_rowwise_moments(const int32_t* guest, const double* price, int64_t n, int threads, double* out /* 8 */) {
+  const int64_t len = 8;
+  threads = pick_threads(threads, n);
+  memset(out, 0, (size_t)len * sizeof(double));
+  double* parts = (double*)calloc((size_t)(len + 16) * threads, sizeof(double));
+#pragma omp parallel num_threads(threads)
+  {
+#ifdef _OPENMP
+    int t = omp_get_thread_num();
+    int T = omp_get_num_threads();
+#else
+    int t = 0, T = 1;
+#endif
+    double acc[8 + 16];
+    memset(acc, 0, sizeof(acc));
+    rw_partition(guest, price, n * t / T, n * (t + 1) / T, acc, rw_udf_min_price, rw_udf_price_corr);
+    memcpy(parts + (int64_t)t * (len + 16), acc, sizeof(double) * (size_t)len);
+  }
+  for (int t = 0; t < threads; ++t)
+    for (int64_t k = 0; k < len; ++k) out[k] += parts[(int64_t)t * (len + 16) + k];
+  free(parts);
+}
+
 /* ------------------------------------------------------------------ MultivariateOnlineSummarizer */
 
 typedef struct {

@@ -56,6 +56,11 @@ int orc_dq_keep(int32_t guest, double price);
  * field 0 -> int32, field 1 -> double.  Returns #records or -1 on malformed input. */
 int64_t orc_csv_parse(const char* buf, int64_t len, int32_t* guest, double* price, int64_t cap);
 
+/* ---- the lab's whole d = 1 pipeline, one row at a time through the boxed UDF call chain (MinUdf:11-13 -> MinSvc:7-13,
+ * App:77-78, CorrUdf:11-16 -> CorrSvc:5-10, App:89-90, App:101-113) into the WLS aggregator: the "row-at-a-time
+ * scalar" CPU-baseline variant.  out[8] has the orc_wls_moments layout for d = 1 and equals it. */
+void orc_lab_rowwise_moments(const int32_t* guest, const double* price, int64_t n, int threads, double* out);
+
 /* ---- WeightedLeastSquares.Aggregator (Spark 2.4.4), w = 1 ----
  * out layout: [count, wSum, wwSum, bSum, bbSum, aSum[d], abSum[d], aaSum[d(d+1)/2]]
  * aaSum is packed upper, column-major (BLAS dspr 'U').

@@ -79,12 +79,25 @@ def lib():
         L.orc_rows_digest.restype = None
         L.orc_rows_digest.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_uint64, C.c_void_p]
         L.orc_max_threads.restype = C.c_int
+        L.orc_lab_rowwise_moments.restype = None
+        L.orc_lab_rowwise_moments.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_void_p]
         _lib = L
     return _lib
 
 
 def max_threads() -> int:
+    """What OpenMP would use by default.  Under torchrun this is 1 (it exports OMP_NUM_THREADS=1): callers that want the
+    machine use host_threads()."""
     return int(lib().orc_max_threads())
+
+
+def host_threads() -> int:
+    """Hardware threads this process may run on (its CPU affinity mask), independent of OMP_NUM_THREADS -- the thread
+    count of Spark's local[*] master (DataQuality4MachineLearningApp.java:40)."""
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except (AttributeError, OSError):
+        return max(1, os.cpu_count() or 1)
 
 
 def _ptr(a):
@@ -179,6 +192,16 @@ def wls_moments(features, label, dq=None, threads=1):
     return out
 
 
+def lab_rowwise_moments(guest, price, threads=1):
+    """The lab's d = 1 pipeline one row at a time through the boxed UDF call chain (the row-at-a-time CPU-baseline
+    variant); same layout and values as wls_moments([guest], price, dq=(guest, price))."""
+    guest = np.ascontiguousarray(guest, dtype=np.int32)
+    price = np.ascontiguousarray(price, dtype=np.float64)
+    out = np.zeros(8, dtype=np.float64)
+    lib().orc_lab_rowwise_moments(guest.ctypes.data, price.ctypes.data, guest.size, threads, out.ctypes.data)
+    return out
+
+
 def summarizer(features, label, dq=None, threads=1):
     d = len(features)
     label = np.ascontiguousarray(label, dtype=np.float64)
@@ -229,7 +252,7 @@ def predict_metrics(features, label, coef, intercept, dq=None, threads=1, want_p
 def synth_generate(n, d=1, row0=0, seed_data=20200601, seed_anom=7, p_low=0.01, p_high=0.01, threads=0):
     """Returns guest:int32[n], price:f64[n], extra:f64[d-1, n]."""
     if threads <= 0:
-        threads = max_threads()
+        threads = host_threads()
     sp = SynthParams(seed_data, seed_anom, p_low, p_high, d)
     guest = np.empty(n, dtype=np.int32)
     price = np.empty(n, dtype=np.float64)

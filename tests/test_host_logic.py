@@ -22,7 +22,7 @@ def declared_symbols():
 
 def test_library_loads_and_exports_every_declared_symbol(pkg):
     L = pkg.capi.lib()
-    assert L.dq4ml_abi_version() == 1
+    assert L.dq4ml_abi_version() == 2
     syms = declared_symbols()
     assert len(syms) >= 40
     raw = C.CDLL(pkg.capi.LIB_PATH)

@@ -60,7 +60,8 @@ def test_noalloc_filter_matches_regular_filter_on_two_calls_in_a_row(pkg, ctx):
 def test_noalloc_filter_edge_sizes_and_limit(pkg, ctx):
     L = pkg.capi.lib()
     torch.cuda.set_device(0)
-    for n in (0, 1, 2047, 2048, 2049):
+    # around the 4096-row tile boundary, and one input whose look-back has to walk over more than 256 tiles
+    for n in (0, 1, 2047, 2048, 2049, 4095, 4096, 4097, 4096 * 257 + 1):
         guest = torch.arange(n, dtype=torch.int32, device="cuda") % 36
         price = (torch.arange(n, dtype=torch.float64, device="cuda") * 7.5) % 160.0
         ref_g, ref_p, ref_n1 = _call_regular(pkg, ctx, guest, price)
@@ -75,3 +76,34 @@ def test_noalloc_filter_edge_sizes_and_limit(pkg, ctx):
                                    C.byref(n_out), None)
     assert rc == pkg.capi.ERR_UNSUPPORTED
     assert b"DQ4ML_NOALLOC_MAX_ROWS" in L.dq4ml_last_error()
+
+
+@pytest.mark.parametrize("n", [MAX_ROWS, MAX_ROWS - 4095])
+def test_noalloc_filter_at_the_row_limit(pkg, ctx, n):
+    """The largest accepted input uses the last look-back word of the built-in array (n = 2^26 is exactly 16384 tiles);
+    2^26 - 4095 ends on a tile holding a single row."""
+    L = pkg.capi.lib()
+    torch.cuda.set_device(0)
+    guest, price = ctx.synth_generate(n, d=1, row0=3, p_low=0.05, p_high=0.05)[:2]
+    ref_g, ref_p, ref_n1 = _call_regular(pkg, ctx, guest, price)
+    rc, go, po, m, n1 = _call_noalloc(L, guest, price)
+    assert rc == 0, L.dq4ml_last_error()
+    assert (m, n1) == (ref_g.shape[0], ref_n1)
+    assert torch.equal(go[:m], ref_g) and torch.equal(po[:m].view(torch.int64), ref_p.view(torch.int64))
+    # and once more: the words the first call left behind must not leak into the second
+    rc, go2, po2, m2, n12 = _call_noalloc(L, guest, price)
+    assert rc == 0 and (m2, n12) == (m, n1)
+    assert torch.equal(go2[:m], ref_g) and torch.equal(po2[:m].view(torch.int64), ref_p.view(torch.int64))
+
+
+def test_noalloc_filter_unaligned_slices(pkg, ctx):
+    """The kernel uses scalar loads: a column that starts in the middle of a 16-byte line is as good as any other."""
+    L = pkg.capi.lib()
+    torch.cuda.set_device(0)
+    guest, price = ctx.synth_generate(100_003, d=1, row0=11, p_low=0.2, p_high=0.2)[:2]
+    g1, p1 = guest[1:], price[1:]  # 4- and 8-byte aligned only
+    ref_g, ref_p, ref_n1 = _call_regular(pkg, ctx, g1.clone(), p1.clone())
+    rc, go, po, m, n1 = _call_noalloc(L, g1, p1)
+    assert rc == 0, L.dq4ml_last_error()
+    assert (m, n1) == (ref_g.shape[0], ref_n1)
+    assert torch.equal(go[:m], ref_g) and torch.equal(po[:m].view(torch.int64), ref_p.view(torch.int64))
