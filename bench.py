@@ -308,6 +308,8 @@ class Bench:
         return self.max_over_ranks(e0.elapsed_time(e1)), out
 
     def free(self):
+        import gc
+        gc.collect()  # a model and its training summary reference each other (and, through the frame, the columns)
         self.torch.cuda.empty_cache()
 
     def frame(self, g, p, x, d):
@@ -372,8 +374,8 @@ class Bench:
                           "h2d_bytes_per_step": BYTES_PER_ROW * n, "d2h_bytes_per_step": 6 * 8, "steps": e2e_steps,
                           "ms_per_step": e2e_ms / e2e_steps, "numa_cpus": self.numa,
                           "note": "pinned host columns -> dq4ml_linreg_fit; H2D staging + pass + D2H of the moments inside the timed region"}
-            del gh, ph, hdf
-        del guest, price, df
+            del gh, ph, hdf, hmodel
+        del guest, price, df, model
         self.free()
         return res
 
@@ -414,7 +416,7 @@ class Bench:
                             "gbs": shard_bytes / (lsq_ms / 1e3) / 1e9, "frac": shard_bytes / (lsq_ms / 1e3) / 1e9 / self.peak},
                "coefficients_head": model.coefficients()[:4].tolist(), "intercept": model.intercept(),
                "rows_after_dq": model.num_rows}
-        del g, p, x, df
+        del g, p, x, df, model
         self.free()
         return res
 
@@ -457,7 +459,7 @@ class Bench:
                          "solver": model.solver_used, "coefficients_head": coef[:4].tolist(), "intercept": model.intercept(),
                          "max_coef_diff_vs_fp64_scale_rel": float(abs(coef - ref_coef).max() / max(abs(ref_coef).max(), 1e-300))}
         ctx.set_gram_tier("fp64")
-        del g, p, x, feats, df
+        del g, p, x, feats, df, model
         self.free()
         return res
 

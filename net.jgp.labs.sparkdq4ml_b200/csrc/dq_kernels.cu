@@ -1,10 +1,19 @@
 // dq_kernels.cu -- the DQ section of the lab (DataQuality4MachineLearningApp.java:68-90) as sm_100a kernels:
 // the two UDF columns, and rule1 -> filter -> rule2 -> filter fused into one stable compaction pass.
 // Plus the synthetic-data generator and the row digest used by the benchmarks/tests.
+#include <cstdlib>
+
 #include "device_utils.cuh"
 #include "kernels.hpp"
 
 namespace dq4ml {
+
+// filter_kernels.cu
+bool dq_filter_stream_usable(const int32_t* guest, const double* price);
+cudaError_t launch_dq_filter_stream(const int32_t* guest, const double* price, int64_t n, const DqThresholds& t,
+                                    int32_t* guest_out, double* price_out, unsigned long long* tile_state,
+                                    unsigned long long* counters, int sm_count, cudaStream_t stream);
+
 namespace {
 
 __host__ DqThresholds thresholds(const dq4ml_dq_params& p) {
@@ -375,8 +384,21 @@ cudaError_t launch_dq_filter(const int32_t* guest, const double* price, int64_t 
   if (e != cudaSuccess) return e;
   const int64_t tiles = (n + kFilterTile - 1) / kFilterTile;
   static bool smem_opt_in[64] = {false};
+  static int sm_counts[64] = {0};
   int dev = 0;
   if ((e = cudaGetDevice(&dev)) != cudaSuccess) return e;
+  // the persistent TMA-ring kernel (filter_kernels.cu) whenever the columns allow bulk copies; DQ4ML_FILTER_LEGACY=1
+  // forces the one-CTA-per-tile kernel below (kept for columns that are not 16-byte aligned, and for A/B timing)
+  static const bool legacy = getenv("DQ4ML_FILTER_LEGACY") != nullptr;
+  if (!legacy && dq_filter_stream_usable(guest, price)) {
+    int sms = 148;
+    if (dev >= 0 && dev < 64) {
+      if (sm_counts[dev] == 0 && (e = cudaDeviceGetAttribute(&sm_counts[dev], cudaDevAttrMultiProcessorCount, dev)) != cudaSuccess) return e;
+      sms = sm_counts[dev];
+    }
+    ++*launches;
+    return launch_dq_filter_stream(guest, price, n, thresholds(p), guest_out, price_out, tile_state, counters, sms, stream);
+  }
   if (dev >= 0 && dev < 64 && !smem_opt_in[dev]) {
     e = cudaFuncSetAttribute(dq_filter_compact_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(kFilterSmem));
     if (e != cudaSuccess) return e;

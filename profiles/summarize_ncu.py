@@ -42,6 +42,17 @@ def main():
                     rec[w] = {"value": float(r[i].replace(",", "")), "unit": units[i]}
                 except ValueError:
                     pass
+        # warp-stall breakdown (WarpStateStats / SourceCounters sections): sampled stall reasons, largest first
+        stalls = {}
+        for i, name in enumerate(hdr):
+            if name.startswith("smsp__pcsamp_warps_issue_stalled_") and not name.endswith("_not_issued"):
+                try:
+                    stalls[name[len("smsp__pcsamp_warps_issue_stalled_"):]] = float(r[i].replace(",", ""))
+                except ValueError:
+                    pass
+        tot = sum(stalls.values())
+        if tot > 0:
+            rec["warp_stall_share"] = {k: round(v / tot, 4) for k, v in sorted(stalls.items(), key=lambda kv: -kv[1]) if v / tot >= 0.005}
         launches.append(rec)
     here = os.path.dirname(os.path.abspath(__file__))
     json.dump({"report": os.path.basename(rep), "launches": launches}, open(os.path.join(here, f"{rnd}_{key}_full.json"), "w"), indent=1)
@@ -50,6 +61,9 @@ def main():
         m = rec[name]
         return m["value"] * UNIT_SCALE.get(m["unit"], 1)
 
+    if not all("dram__bytes_read.sum" in l for l in launches):  # a sections-only capture (stall reasons): no traffic to record
+        print(json.dumps(launches[0], indent=1))
+        return
     traffic = [si(l, "dram__bytes_read.sum") + si(l, "dram__bytes_write.sum") for l in launches]
     dur = [si(l, "gpu__time_duration.sum") for l in launches]
     summ_path = os.path.join(here, "ncu_summary.json")

@@ -3,10 +3,14 @@ import numpy as np
 import pytest
 import torch
 
-from conftest import RTOL, rel_err
+from conftest import RTOL, rel_err, scale_err
 from oracle import passes, spark_ml
 
 pytestmark = pytest.mark.gpu
+
+# Wide fits (d = 40 ... 256) are held to the same 1e-9 as everything else: the largest error measured on any fit of this
+# file is 7e-12 (profiles/r2_parity_errors.jsonl).
+TOL_WIDE = RTOL
 
 
 def to_dev(*arrs):
@@ -25,6 +29,17 @@ def estimator(pkg, p):
     lr.setFitIntercept(p.get("fit_intercept", True)).setStandardization(p.get("standardization", True))
     lr.setSolver(p.get("solver", "auto"))
     return lr
+
+
+def check_fit(parity_log, tag, model, ref_coef, ref_intercept, ref_hist, tol):
+    """Whole-fit parity in the measure DESIGN.md states: objective history and intercept relative, coefficients relative
+    to the largest coefficient (an L1 term leaves some at or next to zero, where element-wise relative error means
+    nothing).  The measured errors go to the parity log."""
+    e_hist = rel_err(model.summary().objectiveHistory(), ref_hist)
+    e_coef = scale_err(model.coefficients(), ref_coef)
+    e_int = rel_err(model.intercept(), ref_intercept)
+    parity_log(tag, "objectiveHistory rel / coef scale-rel / intercept rel", [e_hist, e_coef, e_int])
+    assert e_hist < tol and e_coef < tol and e_int < tol, (tag, e_hist, e_coef, e_int)
 
 
 @pytest.mark.parametrize("d", [1, 2, 3, 4, 7, 8])
@@ -109,7 +124,7 @@ def test_lab_app_on_reference_fixtures(pkg, ctx, golden, lab_csv, name, fused):
 
 @pytest.mark.parametrize("fit_name", ["lab_wls_lasso", "ols_cholesky", "ridge_cholesky", "enet_wls", "nostd_enet_wls",
                                       "lab_lbfgs_lasso", "enet_lbfgs", "ols_lbfgs", "nointercept_lbfgs"])
-def test_fit_synth_small_all_solvers(pkg, ctx, golden, fit_name):
+def test_fit_synth_small_all_solvers(pkg, ctx, golden, parity_log, fit_name):
     """d = 4 with fused DQ: every solver branch against the golden fits (oracle) and scikit-learn."""
     doc = golden("synth_small")
     ref = doc["fits"][fit_name]
@@ -126,10 +141,13 @@ def test_fit_synth_small_all_solvers(pkg, ctx, golden, fit_name):
     assert model.solver_used == ref["solver_used"]
     s = model.summary()
     assert s.totalIterations() == ref["total_iterations"]
-    assert rel_err(s.objectiveHistory(), ref["objective_history"]) < 1e-8
-    np.testing.assert_allclose(model.coefficients(), ref["coefficients"], rtol=1e-8, atol=1e-10)
-    np.testing.assert_allclose(model.intercept(), ref["intercept"], rtol=1e-8, atol=1e-10)
-    assert rel_err(s.rootMeanSquaredError(), ref["rmse"]) < 1e-8 and rel_err(s.r2(), ref["r2"]) < 1e-8
+    if abs(ref["intercept"]) > 0:
+        check_fit(parity_log, "synth_small/" + fit_name, model, ref["coefficients"], ref["intercept"], ref["objective_history"], RTOL)
+    else:  # fitIntercept = false
+        assert model.intercept() == 0.0
+        assert rel_err(s.objectiveHistory(), ref["objective_history"]) < RTOL
+        assert scale_err(model.coefficients(), ref["coefficients"]) < RTOL
+    assert rel_err(s.rootMeanSquaredError(), ref["rmse"]) < RTOL and rel_err(s.r2(), ref["r2"]) < RTOL
     if "sklearn_coefficients" in ref:
         np.testing.assert_allclose(model.coefficients(), ref["sklearn_coefficients"], rtol=2e-5, atol=2e-6)
 
@@ -159,11 +177,14 @@ def test_summarizer_and_lsq_passes_vs_oracle(pkg, ctx, d):
         np.testing.assert_allclose(gg, rg, rtol=1e-9, atol=1e-9 * np.abs(rg).max())
 
 
-def test_config3_shape_d16_owlqn_fused(pkg, ctx):
-    """BASELINE config 3 at a test-sized n: 16 features through VectorAssembler, l-bfgs solver, elasticNet 0.5."""
+@pytest.mark.parametrize("reg_param", [1.0, 0.3])
+def test_config3_shape_d16_owlqn_fused(pkg, ctx, parity_log, reg_param):
+    """BASELINE config 3 at a test-sized n: 16 features through VectorAssembler, l-bfgs solver, elasticNet 0.5;
+    regParam 1 is what the benchmark runs (tests/test_gpu_multirank.py repeats it at 10^7 rows), 0.3 keeps more
+    coefficients alive."""
     n, d = 400_000, 16
     guest, price, feats = synth(n, d)
-    params = dict(max_iter=40, reg_param=0.3, elastic_net_param=0.5, solver="l-bfgs")
+    params = dict(max_iter=40, reg_param=reg_param, elastic_net_param=0.5, solver="l-bfgs")
     ref = spark_ml.linear_regression_fit(feats, price, spark_ml.LRParams(**params), dq=(guest, price), threads=8)
     g, p, x = ctx.synth_generate(n, d=d)
     cols = {"guest": g, "label": p}
@@ -177,9 +198,7 @@ def test_config3_shape_d16_owlqn_fused(pkg, ctx):
     assert model.solver_used == ref.solver_used == "owlqn"
     s = model.summary()
     assert s.totalIterations() == ref.total_iterations and model.data_passes == ref.data_passes
-    assert rel_err(s.objectiveHistory(), ref.objective_history) < 1e-8
-    np.testing.assert_allclose(model.coefficients(), ref.coefficients, rtol=1e-7, atol=1e-9)
-    np.testing.assert_allclose(model.intercept(), ref.intercept, rtol=1e-8)
+    check_fit(parity_log, f"config3_shape_reg{reg_param}", model, ref.coefficients, ref.intercept, ref.objective_history, RTOL)
 
 
 def test_host_buffers_equal_device_buffers(pkg, ctx):
@@ -283,7 +302,7 @@ def test_gram_nan_and_inf_rows(pkg, ctx):
 @pytest.mark.parametrize("params", [dict(max_iter=40, reg_param=0.0, elastic_net_param=0.0, solver="normal"),
                                     dict(max_iter=40, reg_param=0.1, elastic_net_param=0.0),
                                     dict(max_iter=40, reg_param=0.05, elastic_net_param=0.5)])
-def test_config4_shape_d256_normal_equations(pkg, ctx, params):
+def test_config4_shape_d256_normal_equations(pkg, ctx, parity_log, params):
     """BASELINE config 4 at a test-sized n: 256 features, normal-equation solver (Cholesky, or OWL-QN over the Gram when
     an L1 term is present), DQ fused."""
     n, d = 60_000, 256
@@ -300,9 +319,8 @@ def test_config4_shape_d256_normal_equations(pkg, ctx, params):
     model = estimator(pkg, params).fit(df)
     assert model.solver_used == ref.solver_used and model.num_rows == int(passes.wls_moments([guest], price, dq=(guest, price))[0])
     assert model.summary().totalIterations() == ref.total_iterations
-    np.testing.assert_allclose(model.coefficients(), ref.coefficients, rtol=1e-6, atol=1e-8)
-    np.testing.assert_allclose(model.intercept(), ref.intercept, rtol=1e-7)
-    assert rel_err(model.summary().objectiveHistory(), ref.objective_history) < 1e-7
+    check_fit(parity_log, f"config4_shape_{params['solver'] if 'solver' in params else 'auto'}_reg{params['reg_param']}_en{params['elastic_net_param']}",
+              model, ref.coefficients, ref.intercept, ref.objective_history, TOL_WIDE)
 
 
 # ---------------------------------------------------------------------------------------------- wide tables beyond the Gram
@@ -348,7 +366,7 @@ def test_wide_transform_evaluate_and_lsq_vs_oracle(pkg, ctx, d, n):
     np.testing.assert_allclose(gg, rg, rtol=1e-9, atol=1e-9 * np.abs(rg).max())
 
 
-def test_wide_lbfgs_fit_d40(pkg, ctx):
+def test_wide_lbfgs_fit_d40(pkg, ctx, parity_log):
     """solver = l-bfgs on a 40-column table: grouped summarizer + two-pass loss/gradient under OWL-QN."""
     n, d = 50_000, 40
     guest, price, feats = wide_table(n, d)
@@ -364,9 +382,7 @@ def test_wide_lbfgs_fit_d40(pkg, ctx):
     model = estimator(pkg, params).fit(df)
     assert model.solver_used == ref.solver_used == "owlqn"
     assert model.summary().totalIterations() == ref.total_iterations
-    assert rel_err(model.summary().objectiveHistory(), ref.objective_history) < 1e-8
-    np.testing.assert_allclose(model.coefficients(), ref.coefficients, rtol=1e-6, atol=1e-9)
-    np.testing.assert_allclose(model.intercept(), ref.intercept, rtol=1e-8)
+    check_fit(parity_log, "wide_lbfgs_d40", model, ref.coefficients, ref.intercept, ref.objective_history, TOL_WIDE)
 
 
 @pytest.mark.parametrize("d", [3, 40])

@@ -12,7 +12,10 @@ from oracle import passes, spark_ml
 pytestmark = pytest.mark.gpu
 
 COV_TOL = 5e-6   # |G - G_ref| / (n sigma_i sigma_j)
-FIT_TOL = 1e-5
+FIT_TOL = 1e-5   # the tier's stated tolerance: intercept relative; coefficients relative to the largest coefficient
+# (measured on these cases: <= 1.0e-6 scale-relative, <= 1.2e-6 on the intercept, profiles/r2_parity_errors.jsonl)
+COEF_FLOOR = 0.05      # per-coefficient relative error is checked for coefficients of at least 5 % of the largest one ...
+PER_COEF_TOL = 5e-5    # ... where the tf32 Gram's absolute error is up to 20x larger in relative terms (measured 1.8e-5)
 
 
 @pytest.fixture()
@@ -92,7 +95,7 @@ def test_tf32_spans_many_drains(pkg, tf32):
     (130, 40_003, dict(reg_param=0.05, standardization=False)),
 ])
 @pytest.mark.parametrize("weighted", [False, True])
-def test_tf32_fit_vs_oracle(pkg, tf32, d, n, params, weighted):
+def test_tf32_fit_vs_oracle(pkg, tf32, parity_log, d, n, params, weighted):
     guest, price, feats = table(n, d)
     base = dict(max_iter=100, reg_param=0.0, elastic_net_param=0.0, tol=1e-9, fit_intercept=True, standardization=True,
                 solver="normal")
@@ -117,9 +120,16 @@ def test_tf32_fit_vs_oracle(pkg, tf32, d, n, params, weighted):
     if weighted:
         lr.setWeightCol("w")
     model = lr.fit(df)
-    scale = max(1.0, float(np.max(np.abs(ref.coefficients))))
-    assert float(np.max(np.abs(model.coefficients() - ref.coefficients))) / scale < FIT_TOL
-    assert abs(model.intercept() - ref.intercept) / max(1.0, abs(ref.intercept)) < FIT_TOL
+    # "1e-5 relative" per coefficient, with an explicit absolute floor: a coefficient smaller than COEF_FLOOR times the
+    # largest one is compared on the floor's scale (the tf32 products of the Gram carry an absolute, not a relative, error)
+    refc = np.asarray(ref.coefficients)
+    diff = np.abs(model.coefficients() - refc)
+    cmax = float(np.max(np.abs(refc)))
+    per_coef = float(np.max(diff / np.maximum(np.abs(refc), COEF_FLOOR * cmax)))
+    e_int = abs(model.intercept() - ref.intercept) / abs(ref.intercept)
+    parity_log(f"tf32_fit_d{d}_n{n}_w{int(weighted)}_{params}", "per-coef rel (floor) / scale-rel / intercept rel",
+               [per_coef, float(np.max(diff)) / cmax, e_int])
+    assert float(np.max(diff)) / cmax < FIT_TOL and e_int < FIT_TOL and per_coef < PER_COEF_TOL
     assert model.num_rows == int(spark_ml._dq_keep_mask((guest, price), n).sum())
 
 
