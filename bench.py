@@ -346,10 +346,14 @@ class Bench:
             self.dist.broadcast(pre, src=0)
         for _ in range(int(pre.item())):
             model = lr.fit(df)
-        ctx.enable_pass_timing(True)
         l0 = ctx.launch_count
         ms, model = self.timed(lambda: lr.fit(df), steps)
         launches = ctx.launch_count - l0
+        # the roofline leg: the same steps again, now with every pass kernel bracketed by CUDA events on the ctx stream
+        # (kept out of the timed region above: two event records and an event wait per pass cost ~10 us of a 200 us step)
+        ctx.enable_pass_timing(True)
+        for _ in range(steps):
+            lr.fit(df)
         pass_ms, passes = ctx.pass_timing()
         ctx.enable_pass_timing(False)
         clocks = smp.stop() if smp is not None else None

@@ -22,6 +22,8 @@
  *     (the kernels use 256-bit loads); a row range of an aligned column stays aligned when it starts on a multiple of
  *     8 rows.
  *   - a dq4ml_ctx owns one CUDA device, one stream and its scratch buffers; use one ctx per thread (or lock).
+ *     That stream is non-blocking (it does not synchronise with the legacy default stream): device inputs must be
+ *     complete when an entry point is called, and every entry point returns after its own work has finished.
  *   - there is no CPU fallback: entry points that need a GPU fail with DQ4ML_ERR_NO_DEVICE without one.
  *     Entry points marked [host-only] never touch the GPU.
  */
@@ -200,7 +202,7 @@ int dq4ml_dq_filter_global_offset(dq4ml_ctx* ctx, int64_t n_out_local, int64_t* 
  * hosts where the GPU's memory is already owned by another allocator (an executor-wide memory pool, say), or where the
  * device-wide stall inside cudaMalloc/cudaFree is not tolerable.  It takes no dq4ml_ctx and calls no allocator of any
  * kind: the compaction kernel's look-back words and row counters live in a fixed array compiled into the library
- * (about 128 KB of every GPU that loads libdq4ml.so, held until the process exits), which caps one call at
+ * (about 256 KB of every GPU that loads libdq4ml.so, held until the process exits), which caps one call at
  * DQ4ML_NOALLOC_MAX_ROWS rows -- larger inputs are refused with DQ4ML_ERR_UNSUPPORTED.
  *   - Call it with the device that owns the buffers current (cudaSetDevice); `stream` is a cudaStream_t (NULL = the
  *     default stream).  guest/price/guest_out/price_out must be DEVICE memory (outputs sized for n rows); n_out and
@@ -263,7 +265,11 @@ int dq4ml_lsq_loss_grad(dq4ml_ctx* ctx, const dq4ml_columns* features, const dou
                         double* out);
 
 /* LinearRegression.fit(dataset) (App:126): solver selection, aggregation passes on the GPU, optimiser on the host.
- * features = the VectorAssembler table, label = the "label" column (App:101).  dq may be NULL. */
+ * features = the VectorAssembler table, label = the "label" column (App:101).  dq may be NULL.
+ * loss = DQ4ML_LOSS_HUBER (the lab leaves Spark's default, squaredError, at App:120-123; SURVEY.md 8f lists huber as a
+ * next parameter): summarizer pass for the feature scales, one HuberAggregator pass per evaluation, Breeze LBFGSB on the
+ * host over [coefficients, intercept, sigma] with sigma > 0; needs elasticNetParam == 0, epsilon > 1, solver != normal
+ * (as Spark requires) and at most 32 feature columns (31 with a weight column). */
 int dq4ml_linreg_fit(dq4ml_ctx* ctx, const dq4ml_columns* features, const double* label, int64_t n,
                      const dq4ml_lr_params* params, const dq4ml_dq_fused* dq, dq4ml_lr_model** out);
 
@@ -282,6 +288,7 @@ double dq4ml_linreg_model_intercept(const dq4ml_lr_model* m);             /* mod
 int32_t dq4ml_linreg_model_total_iterations(const dq4ml_lr_model* m);     /* totalIterations()  App:134 */
 int dq4ml_linreg_model_objective_history(const dq4ml_lr_model* m, double* hist, int32_t cap); /* App:135-136 */
 int32_t dq4ml_linreg_model_data_passes(const dq4ml_lr_model* m);          /* aggregation passes the fit ran */
+double dq4ml_linreg_model_scale(const dq4ml_lr_model* m);                 /* model.scale(): huber's sigma, else 1.0 */
 int64_t dq4ml_linreg_model_num_rows(const dq4ml_lr_model* m);             /* rows that entered the fit */
 const char* dq4ml_linreg_model_solver_used(const dq4ml_lr_model* m);
 double dq4ml_linreg_predict1(const dq4ml_lr_model* m, const double* x /* d */); /* model.predict(Vector) App:150-151 */

@@ -117,6 +117,7 @@ SIGNATURES = {
     "dq4ml_linreg_model_total_iterations": (C.c_int32, [C.c_void_p]),
     "dq4ml_linreg_model_objective_history": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32]),
     "dq4ml_linreg_model_data_passes": (C.c_int32, [C.c_void_p]),
+    "dq4ml_linreg_model_scale": (C.c_double, [C.c_void_p]),
     "dq4ml_linreg_model_num_rows": (C.c_int64, [C.c_void_p]),
     "dq4ml_linreg_model_solver_used": (C.c_char_p, [C.c_void_p]),
     "dq4ml_linreg_predict1": (C.c_double, [C.c_void_p, C.c_void_p]),

@@ -2,7 +2,9 @@
 // kernel launches, the cross-rank sum, and the hand-off to the host solvers.  There is deliberately no CPU code path
 // for the data passes: without a CUDA device these entry points fail with DQ4ML_ERR_NO_DEVICE.
 #include <algorithm>
+#include <atomic>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <limits>
 #include <memory>
@@ -180,24 +182,112 @@ int check_ctx(const dq4ml_ctx* ctx) {
   return DQ4ML_OK;
 }
 
-// ---- cross-rank sum of the result vector sitting in ctx->scratch.result; leaves it in ctx->h_result ----------------
-int finish_result(dq4ml_ctx* ctx, int64_t count, bool reduce = true) {
-  if (static_cast<size_t>(count) > kResultDoubles) {
+// ---- how a streaming pass hands its result vector to the host ---------------------------------------------------------
+// arm_epilogue() before the launch decides the route, finish_result() after it collects the vector into ctx->h_result:
+//   (a) epilogue, one rank or host-callback ranks: the last CTA writes mapped host memory, the host polls a word;
+//   (b) epilogue, NCCL-bound ranks with peer mailboxes: the same, after the in-kernel exchange over NVLink
+//       (fold in rank order, or gather of all ranks' vectors);
+//   (c) NCCL-bound ranks without mailboxes (IPC unavailable, DQ4ML_XRANK=nccl): ncclAllReduce + copy + synchronise.
+int host_allreduce(dq4ml_ctx* ctx, double* buf, int64_t count);
+
+struct PassOpts {
+  bool reduce = true;    // sum (fold) over the bound ranks
+  bool gather = false;   // instead of folding, give the host every rank's vector (world x len doubles)
+  int extra_consts = 0;  // device constants appended to the vector (the summarizer's centres)
+  bool timed = true;     // counts as an aggregation pass for dq4ml_ctx_enable_pass_timing
+};
+
+void arm_epilogue(dq4ml_ctx* ctx, const PassOpts& o) {
+  XrEpilogue& ep = ctx->scratch.ep;
+  ep = XrEpilogue{};
+  ep.extra_consts = o.extra_consts;
+  ctx->ep_armed = false;
+  ctx->ep_world = 1;
+  static const bool disabled = [] {  // A/B switch: DQ4ML_EPILOGUE=off keeps copy + stream synchronisation on every pass
+    const char* env = std::getenv("DQ4ML_EPILOGUE");
+    return env != nullptr && std::strcmp(env, "off") == 0;
+  }();
+  if (disabled) return;
+  const bool cross = (o.reduce || o.gather) && ctx->nccl != nullptr && ctx->world > 1;
+  if (cross) {
+    if (!nccl_mailboxes(ctx, &ep)) return;  // route (c): the kernel leaves the vector in scratch.result
+    ep.gather = o.gather ? 1 : 0;
+    ep.xr_seq = ++ctx->xr_seq;
+    ctx->ep_world = ctx->world;
+  }
+  ep.host_out = ctx->h_result_dev;
+  ep.host_flag = ctx->h_flag_dev;
+  ep.host_seq = ++ctx->host_seq;
+  ctx->ep_armed = true;
+}
+
+int wait_host_flag(dq4ml_ctx* ctx) {
+  const unsigned long long want = ctx->scratch.ep.host_seq;
+  for (unsigned spins = 0;; ++spins) {
+    const unsigned long long v = *ctx->h_flag;
+    if (v == want) break;
+    if (v == ~0ull) {
+      cudaStreamSynchronize(ctx->stream);
+      set_error("cross-rank epilogue timed out waiting for a peer's result vector");
+      return DQ4ML_ERR_COMM;
+    }
+    if ((spins & 4095u) == 4095u) {  // a failed launch / kernel never raises the flag: look at the stream now and then
+      const cudaError_t e = cudaStreamQuery(ctx->stream);
+      if (e == cudaSuccess) {
+        if (*ctx->h_flag == want) break;
+        set_error("the pass finished without publishing its result");
+        return DQ4ML_ERR_CUDA;
+      }
+      if (e != cudaErrorNotReady) return cuda_fail(e, "streaming pass");
+    }
+#if defined(__x86_64__) || defined(__i386__)
+    __builtin_ia32_pause();
+#endif
+  }
+  std::atomic_thread_fence(std::memory_order_acquire);
+  return DQ4ML_OK;
+}
+
+// Collects `count` doubles of the pass just launched into ctx->h_result (summed over ranks when the pass was armed with
+// reduce; world x count doubles, rank-major, when it was armed with gather).  *gathered_world (nullable) receives the
+// number of rank vectors now in h_result for a gather pass.
+int finish_result(dq4ml_ctx* ctx, int64_t count, const PassOpts& o = PassOpts{}) {
+  const bool multi = ctx->nccl != nullptr || ctx->allreduce_cb != nullptr;
+  const int world = multi && ctx->world > 0 ? ctx->world : 1;
+  if (static_cast<size_t>(count) * (o.gather ? world : 1) > kResultDoubles) {
     set_error("result vector too long (%lld)", static_cast<long long>(count));
     return DQ4ML_ERR_UNSUPPORTED;
   }
-  if (reduce && ctx->nccl != nullptr) {
-    const int rc = nccl_allreduce_device(ctx, ctx->scratch.result, count);
+  bool have_all_ranks = false;  // h_result already holds the cross-rank fold / gather
+  if (ctx->ep_armed) {
+    ctx->ep_armed = false;
+    const int rc = wait_host_flag(ctx);
+    if (ctx->pass_event_pending) cudaEventSynchronize(ctx->pass_ev1);
+    collect_pass_time(ctx);
     if (rc != DQ4ML_OK) return rc;
-  }
-  CU(cudaMemcpyAsync(ctx->h_result, ctx->scratch.result, sizeof(double) * count, cudaMemcpyDeviceToHost, ctx->stream));
-  CU(cudaStreamSynchronize(ctx->stream));
-  collect_pass_time(ctx);
-  if (reduce && ctx->nccl == nullptr && ctx->allreduce_cb != nullptr) {
-    if (ctx->allreduce_cb(ctx->allreduce_user, ctx->h_result, count) != 0) {
-      set_error("all-reduce callback failed");
-      return DQ4ML_ERR_COMM;
+    have_all_ranks = ctx->ep_world > 1;
+  } else {
+    if (o.reduce && !o.gather && ctx->nccl != nullptr) {
+      const int rc = nccl_allreduce_device(ctx, ctx->scratch.result, count);
+      if (rc != DQ4ML_OK) return rc;
+      have_all_ranks = true;
     }
+    CU(cudaMemcpyAsync(ctx->h_result, ctx->scratch.result, sizeof(double) * count, cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    collect_pass_time(ctx);
+  }
+  if (have_all_ranks || world == 1 || !(o.reduce || o.gather)) return DQ4ML_OK;
+  if (o.gather) {  // every rank's vector through a zero-padded sum (host callback, or NCCL without mailboxes)
+    std::vector<double> all(static_cast<size_t>(count) * world, 0.0);
+    std::copy(ctx->h_result, ctx->h_result + count, all.begin() + static_cast<size_t>(ctx->rank) * count);
+    const int rc = host_allreduce(ctx, all.data(), static_cast<int64_t>(all.size()));
+    if (rc != DQ4ML_OK) return rc;
+    std::copy(all.begin(), all.end(), ctx->h_result);
+    return DQ4ML_OK;
+  }
+  if (ctx->allreduce_cb != nullptr && ctx->allreduce_cb(ctx->allreduce_user, ctx->h_result, count) != 0) {
+    set_error("all-reduce callback failed");
+    return DQ4ML_ERR_COMM;
   }
   return DQ4ML_OK;
 }
@@ -314,16 +404,19 @@ int gather_inputs(dq4ml_ctx* ctx, const dq4ml_columns* features, const double* l
 
 // ---- the aggregation passes (device inputs) -------------------------------------------------------------------------
 
-// launch_stream_pass bracketed by CUDA events on the ctx stream when pass timing is on
-cudaError_t timed_stream_pass(dq4ml_ctx* ctx, StreamOpKind op, const DeviceCols& cols, const double* label,
-                              const DeviceDq& dq, int64_t n, const void* host_consts, double* row_out) {
-  if (ctx->pass_timing) cudaEventRecord(ctx->pass_ev0, ctx->stream);
+// One streaming pass: arms the epilogue, brackets the kernel with CUDA events on the ctx stream when pass timing is on.
+cudaError_t run_stream_pass(dq4ml_ctx* ctx, StreamOpKind op, const DeviceCols& cols, const double* label, const DeviceDq& dq,
+                            int64_t n, const void* host_consts, double* row_out, const PassOpts& o = PassOpts{}) {
+  arm_epilogue(ctx, o);
+  const bool timed = ctx->pass_timing && o.timed;
+  if (timed) cudaEventRecord(ctx->pass_ev0, ctx->stream);
   const cudaError_t e = launch_stream_pass(op, cols, label, dq, n, host_consts, row_out, ctx->scratch, ctx->stream,
                                            &ctx->launches);
-  if (ctx->pass_timing) {
+  if (timed) {
     cudaEventRecord(ctx->pass_ev1, ctx->stream);
     ctx->pass_event_pending = true;
   }
+  if (e != cudaSuccess) ctx->ep_armed = false;
   return e;
 }
 
@@ -332,7 +425,7 @@ int wls_moments_small(dq4ml_ctx* ctx, const PassInputs& in, int64_t n, double* o
   const int d = in.cols.n;
   const int b = stream_bucket(d > 0 ? d : 1);
   const int nacc = stream_nacc(kOpWls, b);
-  cudaError_t e = timed_stream_pass(ctx, kOpWls, in.cols, in.label, in.dq, n, nullptr, nullptr);
+  cudaError_t e = run_stream_pass(ctx, kOpWls, in.cols, in.label, in.dq, n, nullptr, nullptr);
   if (e != cudaSuccess) return cuda_fail(e, "wls moments pass");
   const int rc = finish_result(ctx, nacc);
   if (rc != DQ4ML_OK) return rc;
@@ -380,6 +473,50 @@ int weighted_width_check(const PassInputs& in) {
   return DQ4ML_OK;
 }
 
+// ---- merging summarizers across ranks ---------------------------------------------------------------------------------
+// Every rank accumulates shifted power sums S1 = sum w (v - c), S2 = sum w (v - c)^2 around ITS OWN provisional centre c
+// (the head of its shard of the column), and publishes c next to them.  The host turns each rank's triple into
+// (W, mean, M2 = sum w (v - mean)^2) and merges the ranks in rank order with the pairwise update of Chan et al. -- the
+// same thing MultivariateOnlineSummarizer.merge does to the partition summarizers in Spark.  No rank needs to know
+// another rank's centre before the pass, so the pass costs one launch and one hand-over, like every other pass.
+struct Moments {
+  double w = 0.0, mean = 0.0, m2 = 0.0;
+  void merge(double wb, double centre, double s1, double s2) {
+    if (!(wb > 0.0)) return;
+    const double mean_b = centre + s1 / wb, m2_b = s2 - s1 * s1 / wb;
+    if (!(w > 0.0)) {
+      w = wb;
+      mean = mean_b;
+      m2 = m2_b;
+      return;
+    }
+    const double tot = w + wb, delta = mean_b - mean;
+    mean += delta * wb / tot;
+    m2 += m2_b + delta * delta * w * wb / tot;
+    w = tot;
+  }
+};
+
+// Launches the provisional-centre kernel and the summarizer pass `op` over one column group and leaves every rank's
+// vector [accumulators (nacc), centres (b + 1)] in ctx->h_result, rank-major.  Returns the number of rank vectors.
+int summarizer_pass(dq4ml_ctx* ctx, StreamOpKind op, const DeviceCols& cols, const double* label, const DeviceDq& dq,
+                    int64_t n, int b, int n_centres, bool timed, int* world_out, int* len_out) {
+  cudaError_t e = launch_column_heads(cols, label, b, n, ctx->scratch, ctx->stream, &ctx->launches);
+  if (e != cudaSuccess) return cuda_fail(e, "column heads");
+  PassOpts o;
+  o.gather = true;
+  o.extra_consts = n_centres;
+  o.timed = timed;
+  e = run_stream_pass(ctx, op, cols, label, dq, n, nullptr, nullptr, o);
+  if (e != cudaSuccess) return cuda_fail(e, "summarizer pass");
+  const int len = stream_nacc(op, b) + n_centres;
+  const int rc = finish_result(ctx, len, o);
+  if (rc != DQ4ML_OK) return rc;
+  *world_out = multi_rank(ctx) && ctx->world > 0 ? ctx->world : 1;
+  *len_out = len;
+  return DQ4ML_OK;
+}
+
 // Weighted summarizer for the l-bfgs branch: count (rows with w != 0), weighted mean and the unbiased weighted variance
 // MultivariateOnlineSummarizer.variance returns, sum(w (v - mean)^2) / (W - sum(w^2) / W).
 int summarize_core_weighted(dq4ml_ctx* ctx, const PassInputs& in, int64_t n, ColumnStats* st) {
@@ -389,40 +526,33 @@ int summarize_core_weighted(dq4ml_ctx* ctx, const PassInputs& in, int64_t n, Col
   st->mean.assign(d + 1, 0.0);
   st->variance.assign(d + 1, 0.0);
   const int b = stream_bucket(d + 1);
-  cudaError_t e = launch_column_heads(in.wcols, in.label, b, n, ctx->scratch, ctx->stream, &ctx->launches);
-  if (e != cudaSuccess) return cuda_fail(e, "column heads");
-  std::vector<double> centres(b + 1, 0.0);
-  CU(cudaMemcpyAsync(ctx->h_result, ctx->scratch.consts, sizeof(double) * (b + 1), cudaMemcpyDeviceToHost, ctx->stream));
-  CU(cudaStreamSynchronize(ctx->stream));
-  std::copy(ctx->h_result, ctx->h_result + b + 1, centres.begin());
-  if (multi_rank(ctx)) {
-    rc = host_allreduce(ctx, centres.data(), b + 1);
-    if (rc != DQ4ML_OK) return rc;
-    for (double& c : centres) c /= ctx->world > 0 ? ctx->world : 1;
-    CU(cudaMemcpyAsync(ctx->scratch.consts, centres.data(), sizeof(double) * (b + 1), cudaMemcpyHostToDevice, ctx->stream));
-  }
-  e = timed_stream_pass(ctx, kOpSummCoreW, in.wcols, in.label, in.dq, n, nullptr, nullptr);
-  if (e != cudaSuccess) return cuda_fail(e, "weighted summarizer pass");
-  rc = finish_result(ctx, stream_nacc(kOpSummCoreW, b));
+  int world = 1, len = 0;
+  rc = summarizer_pass(ctx, kOpSummCoreW, in.wcols, in.label, in.dq, n, b, b + 1, true, &world, &len);
   if (rc != DQ4ML_OK) return rc;
-  const double* r = ctx->h_result;
-  const double w_sum = r[1], ww_sum = r[2];
+  const int nacc = stream_nacc(kOpSummCoreW, b);
+  double count = 0.0, w_sum = 0.0, ww_sum = 0.0;
+  std::vector<Moments> mom(d + 1);
+  for (int r = 0; r < world; ++r) {
+    const double* v = ctx->h_result + static_cast<size_t>(r) * len;
+    const double* c = v + nacc;  // centres: slot j of the table (slot 0 is the weight itself), the label at slot b
+    count += v[0];
+    w_sum += v[1];
+    ww_sum += v[2];
+    for (int j = 0; j < d; ++j) mom[j].merge(v[1], c[1 + j], v[1 + 2 * (1 + j)], v[2 + 2 * (1 + j)]);
+    mom[d].merge(v[1], c[b], v[1 + 2 * b], v[2 + 2 * b]);
+  }
   if (!(w_sum == w_sum) || w_sum < 0.0) {
     set_error("instance weight must be >= 0 and not NaN");
     return DQ4ML_ERR_INVALID;
   }
-  st->count = r[0];
+  st->count = count;
   const double denom = w_sum > 0.0 ? w_sum - ww_sum / w_sum : 0.0;
-  auto read_out = [&](int slot, int out) {
-    const double s1 = r[1 + 2 * slot], s2 = r[2 + 2 * slot];
+  for (int j = 0; j <= d; ++j) {
     if (w_sum > 0.0) {
-      st->mean[out] = centres[slot] + s1 / w_sum;
-      const double m2n = s2 - s1 * s1 / w_sum;
-      st->variance[out] = denom > 0.0 ? std::max(m2n / denom, 0.0) : 0.0;
+      st->mean[j] = mom[j].mean;
+      st->variance[j] = denom > 0.0 ? std::max(mom[j].m2 / denom, 0.0) : 0.0;
     }
-  };
-  for (int c = 0; c < d; ++c) read_out(1 + c, c);
-  read_out(b, d);
+  }
   return DQ4ML_OK;
 }
 
@@ -433,35 +563,28 @@ int summarize_group(dq4ml_ctx* ctx, const DeviceCols& cols, const double* label,
                     int label_out, ColumnStats* st) {
   const int d = cols.n;
   const int b = stream_bucket(d > 0 ? d : 1);
-  cudaError_t e = launch_column_heads(cols, label, b, n, ctx->scratch, ctx->stream, &ctx->launches);
-  if (e != cudaSuccess) return cuda_fail(e, "column heads");
-  std::vector<double> centres(b + 1, 0.0);
-  CU(cudaMemcpyAsync(ctx->h_result, ctx->scratch.consts, sizeof(double) * (b + 1), cudaMemcpyDeviceToHost, ctx->stream));
-  CU(cudaStreamSynchronize(ctx->stream));
-  std::copy(ctx->h_result, ctx->h_result + b + 1, centres.begin());
-  if (multi_rank(ctx)) {  // every rank must shift by the same centres for the power sums to be addable
-    int rc = host_allreduce(ctx, centres.data(), b + 1);
-    if (rc != DQ4ML_OK) return rc;
-    for (double& c : centres) c /= ctx->world > 0 ? ctx->world : 1;
-    CU(cudaMemcpyAsync(ctx->scratch.consts, centres.data(), sizeof(double) * (b + 1), cudaMemcpyHostToDevice, ctx->stream));
-  }
-  e = timed_stream_pass(ctx, kOpSummCore, cols, label, dq, n, nullptr, nullptr);
-  if (e != cudaSuccess) return cuda_fail(e, "summarizer pass");
-  const int rc = finish_result(ctx, stream_nacc(kOpSummCore, b));
+  int world = 1, len = 0;
+  const int rc = summarizer_pass(ctx, kOpSummCore, cols, label, dq, n, b, b + 1, true, &world, &len);
   if (rc != DQ4ML_OK) return rc;
-  const double* r = ctx->h_result;
-  const double cnt = r[0];
+  const int nacc = stream_nacc(kOpSummCore, b);
+  double cnt = 0.0;
+  std::vector<Moments> mom(d + 1);
+  for (int r = 0; r < world; ++r) {
+    const double* v = ctx->h_result + static_cast<size_t>(r) * len;
+    const double* c = v + nacc;
+    cnt += v[0];
+    for (int j = 0; j < d; ++j) mom[j].merge(v[0], c[j], v[1 + 2 * j], v[2 + 2 * j]);
+    mom[d].merge(v[0], c[b], v[1 + 2 * b], v[2 + 2 * b]);
+  }
   st->count = cnt;
   auto read_out = [&](int slot, int out) {
-    const double s1 = r[1 + 2 * slot], s2 = r[2 + 2 * slot];
     if (cnt > 0) {
-      st->mean[out] = centres[slot] + s1 / cnt;
-      const double m2n = s2 - s1 * s1 / cnt;
-      st->variance[out] = cnt > 1 ? std::max(m2n / (cnt - 1.0), 0.0) : 0.0;
+      st->mean[out] = mom[slot].mean;
+      st->variance[out] = cnt > 1 ? std::max(mom[slot].m2 / (cnt - 1.0), 0.0) : 0.0;
     }
   };
   for (int c = 0; c < d; ++c) read_out(c, first + c);
-  if (label != nullptr && label_out >= 0) read_out(b, label_out);
+  if (label != nullptr && label_out >= 0) read_out(d, label_out);
   return DQ4ML_OK;
 }
 
@@ -502,7 +625,7 @@ int lsq_pass(dq4ml_ctx* ctx, const PassInputs& in, int64_t n, const double* coef
     }
     c.offset = fit_intercept ? ymean / ystd - s : 0.0;
     c.inv_ystd = 1.0 / ystd;
-    cudaError_t e = timed_stream_pass(ctx, kOpLsqW, in.wcols, in.label, in.dq, n, &c, nullptr);
+    cudaError_t e = run_stream_pass(ctx, kOpLsqW, in.wcols, in.label, in.dq, n, &c, nullptr);
     if (e != cudaSuccess) return cuda_fail(e, "weighted loss/gradient pass");
     rc = finish_result(ctx, stream_nacc(kOpLsqW, b));
     if (rc != DQ4ML_OK) return rc;
@@ -542,9 +665,11 @@ int lsq_pass(dq4ml_ctx* ctx, const PassInputs& in, int64_t n, const double* coef
         g.ptr[j] = in.ptr[c0 + j];
         g.dtype[j] = in.dtype[c0 + j];
       }
-      cudaError_t e = timed_stream_pass(ctx, kOpGrad, g, diff_scratch, DeviceDq{}, n, nullptr, nullptr);
+      PassOpts local;
+      local.reduce = false;  // the groups are summed over ranks together, below
+      cudaError_t e = run_stream_pass(ctx, kOpGrad, g, diff_scratch, DeviceDq{}, n, nullptr, nullptr, local);
       if (e != cudaSuccess) return cuda_fail(e, "gradient pass");
-      rc = finish_result(ctx, stream_nacc(kOpGrad, stream_bucket(g.n)), false);
+      rc = finish_result(ctx, stream_nacc(kOpGrad, stream_bucket(g.n)), local);
       if (rc != DQ4ML_OK) return rc;
       for (int j = 0; j < g.n; ++j) all[2 + c0 + j] = -ctx->h_result[j];
     }
@@ -570,7 +695,7 @@ int lsq_pass(dq4ml_ctx* ctx, const PassInputs& in, int64_t n, const double* coef
   }
   c.offset = fit_intercept ? ymean / ystd - s : 0.0;
   c.inv_ystd = 1.0 / ystd;
-  cudaError_t e = timed_stream_pass(ctx, kOpLsq, in.cols, in.label, in.dq, n, &c, nullptr);
+  cudaError_t e = run_stream_pass(ctx, kOpLsq, in.cols, in.label, in.dq, n, &c, nullptr);
   if (e != cudaSuccess) return cuda_fail(e, "loss/gradient pass");
   const int rc = finish_result(ctx, stream_nacc(kOpLsq, b));
   if (rc != DQ4ML_OK) return rc;
@@ -578,6 +703,41 @@ int lsq_pass(dq4ml_ctx* ctx, const PassInputs& in, int64_t n, const double* coef
   *loss_sum = r[0];
   *weight_sum = r[1];
   for (int j = 0; j < d; ++j) grad_sum[j] = fstd[j] != 0.0 ? r[2 + j] / fstd[j] : 0.0;
+  return DQ4ML_OK;
+}
+
+// One HuberAggregator evaluation at params = [coefficients (d), intercept (if fitted), sigma]: raw sums in the same
+// layout.  The weight, when there is one, rides as column 0 of the streamed table (so d <= kMaxCols - 1 then).
+int huber_pass(dq4ml_ctx* ctx, const PassInputs& in, int64_t n, const double* params, const double* fstd, bool fit_intercept,
+               double epsilon, double* loss_sum, double* weight_sum, double* grad_sum) {
+  const int d = in.width();
+  const bool weighted = in.weight != nullptr;
+  if (weighted) {
+    const int rc = weighted_width_check(in);
+    if (rc != DQ4ML_OK) return rc;
+  }
+  if (d + (weighted ? 1 : 0) > kMaxCols) {
+    set_error("huber loss handles at most %d feature columns (%d with a weight column); got %d", kMaxCols, kMaxCols - 1, d);
+    return DQ4ML_ERR_UNSUPPORTED;
+  }
+  const int off = weighted ? 1 : 0;
+  const int b = stream_bucket(d + off > 0 ? d + off : 1);
+  HuberConsts c{};
+  for (int j = 0; j < d; ++j) c.eff[off + j] = fstd[j] != 0.0 ? params[j] / fstd[j] : 0.0;
+  c.intercept = fit_intercept ? params[d] : 0.0;
+  c.sigma = params[d + (fit_intercept ? 1 : 0)];
+  c.epsilon = epsilon;
+  cudaError_t e = run_stream_pass(ctx, weighted ? kOpHuberW : kOpHuber, weighted ? in.wcols : in.cols, in.label, in.dq, n, &c, nullptr);
+  if (e != cudaSuccess) return cuda_fail(e, "huber loss/gradient pass");
+  const int rc = finish_result(ctx, stream_nacc(kOpHuber, b));
+  if (rc != DQ4ML_OK) return rc;
+  const double* r = ctx->h_result;
+  *loss_sum = r[0];
+  *weight_sum = r[1];
+  for (int j = 0; j < d; ++j) grad_sum[j] = fstd[j] != 0.0 ? r[4 + off + j] / fstd[j] : 0.0;
+  int k = d;
+  if (fit_intercept) grad_sum[k++] = r[2];
+  grad_sum[k] = r[3];
   return DQ4ML_OK;
 }
 
@@ -710,7 +870,13 @@ int dq4ml_ctx_create(int device, dq4ml_ctx** out) {
   p += counters_b;
   ctx->d_err = reinterpret_cast<int*>(p);
   ctx->scratch.sm_count = ctx->sm_count;
-  if ((e = cudaMallocHost(reinterpret_cast<void**>(&ctx->h_result), result_b)) != cudaSuccess) return fail(e, "pinned result");
+  // result vector + the word the host polls: pinned AND mapped, so the last CTA of a pass can write them directly
+  if ((e = cudaHostAlloc(reinterpret_cast<void**>(&ctx->h_result), result_b + 256, cudaHostAllocMapped | cudaHostAllocPortable)) != cudaSuccess)
+    return fail(e, "pinned result");
+  std::memset(ctx->h_result, 0, result_b + 256);
+  if ((e = cudaHostGetDevicePointer(reinterpret_cast<void**>(&ctx->h_result_dev), ctx->h_result, 0)) != cudaSuccess) return fail(e, "mapped result");
+  ctx->h_flag = reinterpret_cast<volatile unsigned long long*>(reinterpret_cast<char*>(ctx->h_result) + result_b);
+  ctx->h_flag_dev = reinterpret_cast<unsigned long long*>(reinterpret_cast<char*>(ctx->h_result_dev) + result_b);
   if ((e = cudaEventCreate(&ctx->pass_ev0)) != cudaSuccess) return fail(e, "event");
   if ((e = cudaEventCreate(&ctx->pass_ev1)) != cudaSuccess) return fail(e, "event");
   if ((e = cudaStreamSynchronize(ctx->stream)) != cudaSuccess) return fail(e, "sync");
@@ -1118,62 +1284,40 @@ int dq4ml_summarize(dq4ml_ctx* ctx, const dq4ml_columns* features, const double*
       g.dtype[j] = dtypes[c0 + j];
     }
     const int b = stream_bucket(g.n);
-    cudaError_t e = launch_column_heads(g, nullptr, b, n, ctx->scratch, ctx->stream, &ctx->launches);
-    if (e != cudaSuccess) return cuda_fail(e, "column heads");
-    std::vector<double> centres(b, 0.0);
-    CU(cudaMemcpyAsync(ctx->h_result, ctx->scratch.consts, sizeof(double) * b, cudaMemcpyDeviceToHost, ctx->stream));
-    CU(cudaStreamSynchronize(ctx->stream));
-    std::copy(ctx->h_result, ctx->h_result + b, centres.begin());
-    if (multi_rank(ctx)) {
-      rc = host_allreduce(ctx, centres.data(), b);
-      if (rc != DQ4ML_OK) return rc;
-      for (double& c : centres) c /= ctx->world > 0 ? ctx->world : 1;
-      CU(cudaMemcpyAsync(ctx->scratch.consts, centres.data(), sizeof(double) * b, cudaMemcpyHostToDevice, ctx->stream));
-    }
-    e = launch_stream_pass(kOpSummFull, g, nullptr, in.dq, n, nullptr, nullptr, ctx->scratch, ctx->stream, &ctx->launches);
-    if (e != cudaSuccess) return cuda_fail(e, "summarizer pass");
+    int world = 1, len = 0;
+    rc = summarizer_pass(ctx, kOpSummFull, g, nullptr, in.dq, n, b, b, false, &world, &len);
+    if (rc != DQ4ML_OK) return rc;
     const int nacc = stream_nacc(kOpSummFull, b);
-    std::vector<double> r(nacc);
-    if (!multi_rank(ctx)) {
-      rc = finish_result(ctx, nacc);
-      if (rc != DQ4ML_OK) return rc;
-      std::copy(ctx->h_result, ctx->h_result + nacc, r.begin());
-    } else {
-      // min / max are not sums: gather every rank's vector through a zero-padded sum, then fold on the host
-      CU(cudaMemcpyAsync(ctx->h_result, ctx->scratch.result, sizeof(double) * nacc, cudaMemcpyDeviceToHost, ctx->stream));
-      CU(cudaStreamSynchronize(ctx->stream));
-      const int world = ctx->world > 0 ? ctx->world : 1;
-      std::vector<double> all(static_cast<size_t>(nacc) * world, 0.0);
-      std::copy(ctx->h_result, ctx->h_result + nacc, all.begin() + static_cast<size_t>(ctx->rank) * nacc);
-      rc = host_allreduce(ctx, all.data(), static_cast<int64_t>(all.size()));
-      if (rc != DQ4ML_OK) return rc;
-      for (int k = 0; k < nacc; ++k) {
-        const int kind = k == 0 ? 0 : ((k - 1) % 7 == 2 ? 1 : ((k - 1) % 7 == 3 ? 2 : 0));
-        double v = all[k];
-        for (int w = 1; w < world; ++w) {
-          const double o = all[static_cast<size_t>(w) * nacc + k];
-          if (kind == 0) v += o;  // min / max skip NaNs like MultivariateOnlineSummarizer.add (`currMin > value` is false on NaN)
-          else if (o == o) v = (v != v) ? o : (kind == 1 ? std::min(v, o) : std::max(v, o));
-        }
-        r[k] = v;
-      }
-    }
-    count = r[0];
+    // per column: shifted sums merged as moments; min / max folded (they skip NaNs like MultivariateOnlineSummarizer.add,
+    // whose `currMin > value` is false on NaN); numNonzeros, normL1 and the sum of squares added
+    count = 0.0;
+    for (int r = 0; r < world; ++r) count += ctx->h_result[static_cast<size_t>(r) * len];
     for (int j = 0; j < g.n; ++j) {
-      const double* a = &r[1 + 7 * j];
+      Moments m;
+      double mn = std::numeric_limits<double>::infinity(), mx = -std::numeric_limits<double>::infinity();
+      double nnz = 0.0, l1 = 0.0, sq = 0.0;
+      for (int r = 0; r < world; ++r) {
+        const double* v = ctx->h_result + static_cast<size_t>(r) * len;
+        const double* a = v + 1 + 7 * j;
+        m.merge(v[0], v[nacc + j], a[0], a[1]);
+        if (a[2] < mn) mn = a[2];
+        if (a[3] > mx) mx = a[3];
+        nnz += a[4];
+        l1 += a[5];
+        sq += a[6];
+      }
       double* o = out + 3 + 7 * (c0 + j);
       if (count > 0) {
-        o[0] = centres[j] + a[0] / count;
-        const double m2n = a[1] - a[0] * a[0] / count;
-        o[1] = count > 1 ? std::max(m2n / (count - 1.0), 0.0) : 0.0;
-        o[2] = a[2];
-        o[3] = a[3];
+        o[0] = m.mean;
+        o[1] = count > 1 ? std::max(m.m2 / (count - 1.0), 0.0) : 0.0;
+        o[2] = mn;
+        o[3] = mx;
       } else {
         o[0] = o[1] = o[2] = o[3] = 0.0;
       }
-      o[4] = a[4];
-      o[5] = a[5];
-      o[6] = std::sqrt(a[6]);
+      o[4] = nnz;
+      o[5] = l1;
+      o[6] = std::sqrt(sq);
     }
   }
   out[0] = out[1] = out[2] = count;
@@ -1215,15 +1359,12 @@ int dq4ml_linreg_fit_weighted(dq4ml_ctx* ctx, const dq4ml_columns* features, con
   dq4ml_lr_params defaults = dq4ml_lr_params_default();
   const LrParams p = to_params(params != nullptr ? params : &defaults);
   if (check_params(p) != DQ4ML_OK) return DQ4ML_ERR_INVALID;
-  if (p.loss == DQ4ML_LOSS_HUBER) {
-    set_error("huber loss is not built yet");
-    return DQ4ML_ERR_UNSUPPORTED;
-  }
   CallScope scope(ctx);
   const int d = features->n_cols;
   // LinearRegression.train: squared-error loss goes to WeightedLeastSquares when solver is normal, or auto with
   // numFeatures <= WeightedLeastSquares.MAX_NUM_FEATURES (4096); otherwise the summarizer + L-BFGS/OWL-QN branch.
-  const bool wls = p.solver == DQ4ML_SOLVER_NORMAL || (p.solver == DQ4ML_SOLVER_AUTO && d <= 4096);
+  const bool huber = p.loss == DQ4ML_LOSS_HUBER;  // always the summarizer + aggregator branch
+  const bool wls = !huber && (p.solver == DQ4ML_SOLVER_NORMAL || (p.solver == DQ4ML_SOLVER_AUTO && d <= 4096));
   PassInputs in;
   const bool wide_lbfgs = !wls && d > kMaxCols;  // needs one scratch column for the per-row scaled difference
   int rc = gather_inputs(ctx, features, label, n, dq, &in, wide_lbfgs ? static_cast<size_t>(n) * 8 : 0, 1 << 20, weight);
@@ -1236,6 +1377,21 @@ int dq4ml_linreg_fit_weighted(dq4ml_ctx* ctx, const dq4ml_columns* features, con
       rc = wls_moments_any(ctx, in, n, mom.data());
       if (rc != DQ4ML_OK) return rc;
       model->m = wls_fit_from_moments(mom.data(), d, p);
+    } else if (huber) {
+      if (d + (in.weight != nullptr ? 1 : 0) > kMaxCols) {
+        set_error("huber loss handles at most %d feature columns (%d with a weight column); got %d", kMaxCols, kMaxCols - 1, d);
+        return DQ4ML_ERR_UNSUPPORTED;
+      }
+      ColumnStats st;
+      rc = in.weight != nullptr ? summarize_core_weighted(ctx, in, n, &st) : summarize_core(ctx, in, n, &st);
+      if (rc != DQ4ML_OK) return rc;
+      HuberPassFn pass = [&](const Vec& par, const Vec& fstd, double& loss_sum, double& weight_sum, Vec& grad_sum) {
+        grad_sum.assign(par.size(), 0.0);
+        const int r = huber_pass(ctx, in, n, par.data(), fstd.data(), p.fit_intercept, p.epsilon, &loss_sum, &weight_sum,
+                                 grad_sum.data());
+        if (r != DQ4ML_OK) throw SolveError{r, get_error()};
+      };
+      model->m = huber_path_fit(st, d, p, pass);
     } else {
       ColumnStats st;
       rc = in.weight != nullptr ? summarize_core_weighted(ctx, in, n, &st) : summarize_core(ctx, in, n, &st);
@@ -1287,6 +1443,7 @@ int dq4ml_linreg_model_objective_history(const dq4ml_lr_model* m, double* hist, 
   return len;
 }
 int32_t dq4ml_linreg_model_data_passes(const dq4ml_lr_model* m) { return m ? m->m.data_passes : 0; }
+double dq4ml_linreg_model_scale(const dq4ml_lr_model* m) { return m ? m->m.scale : std::numeric_limits<double>::quiet_NaN(); }
 int64_t dq4ml_linreg_model_num_rows(const dq4ml_lr_model* m) { return m ? m->m.num_rows : 0; }
 const char* dq4ml_linreg_model_solver_used(const dq4ml_lr_model* m) { return m ? m->m.solver_used.c_str() : ""; }
 
@@ -1377,15 +1534,21 @@ static int eval_common(dq4ml_ctx* ctx, const dq4ml_lr_model* m, const dq4ml_colu
   for (int j = 0; j < in.cols.n; ++j) c.coef[j] = m->m.coefficients[j];
   c.intercept = m->m.intercept;
   c.mode = mode;
-  cudaError_t e = launch_stream_pass(kOpEval, in.cols, in.label, in.dq, n, &c, static_cast<double*>(ob.dev), ctx->scratch,
-                                     ctx->stream, &ctx->launches);
+  // with peer mailboxes the nine accumulators are folded over the ranks inside the kernel, each by its own kind (sums
+  // add, the residual extremes take min / NaN-aware max); otherwise they come back per rank and are folded on the host
+  PassOpts o;
+  o.reduce = sums != nullptr && multi_rank(ctx) && ctx->nccl != nullptr && nccl_mailboxes(ctx, &ctx->scratch.ep);
+  o.timed = false;
+  cudaError_t e = run_stream_pass(ctx, kOpEval, in.cols, in.label, in.dq, n, &c, static_cast<double*>(ob.dev), o);
   if (e != cudaSuccess) return cuda_fail(e, "predict/evaluate pass");
   if (ob.staged && n > 0) CU(cudaMemcpyAsync(row_out_user, ob.dev, static_cast<size_t>(n) * 8, cudaMemcpyDeviceToHost, ctx->stream));
-  rc = finish_result(ctx, 9, false);
+  const bool folded = o.reduce;
+  rc = finish_result(ctx, 9, o);
   if (rc != DQ4ML_OK) return rc;
+  if (ob.staged && n > 0) CU(cudaStreamSynchronize(ctx->stream));  // the epilogue's hand-over does not wait for the copy
   if (sums != nullptr) {
     std::copy(ctx->h_result, ctx->h_result + 9, sums);
-    return reduce_eval_sums(ctx, sums);
+    return folded ? DQ4ML_OK : reduce_eval_sums(ctx, sums);
   }
   return DQ4ML_OK;
 }
@@ -1458,10 +1621,12 @@ int dq4ml_weighted_residual_stats(dq4ml_ctx* ctx, const double* residuals, const
   PassInputs in;
   int rc = gather_inputs(ctx, &table, nullptr, n, dq, &in, 0, 1, weight);
   if (rc != DQ4ML_OK) return rc;
-  cudaError_t e = launch_stream_pass(kOpWResid, in.wcols, nullptr, in.dq, n, nullptr, nullptr, ctx->scratch, ctx->stream,
-                                     &ctx->launches);
+  PassOpts local;
+  local.reduce = false;
+  local.timed = false;
+  cudaError_t e = run_stream_pass(ctx, kOpWResid, in.wcols, nullptr, in.dq, n, nullptr, nullptr, local);
   if (e != cudaSuccess) return cuda_fail(e, "weighted residual pass");
-  rc = finish_result(ctx, 3, false);
+  rc = finish_result(ctx, 3, local);
   if (rc != DQ4ML_OK) return rc;
   // the cross-rank fold reuses the evaluate path: slots 0..6 are sums, 7 / 8 the min / max
   double s[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};

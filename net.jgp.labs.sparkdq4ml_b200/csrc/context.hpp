@@ -29,7 +29,14 @@ struct dq4ml_ctx {
   cudaStream_t stream = nullptr;
   dq4ml::Scratch scratch{};
   char* scratch_base = nullptr;
-  double* h_result = nullptr;  // pinned, kResultDoubles
+  double* h_result = nullptr;  // pinned + mapped, kResultDoubles; the epilogue of a streaming pass writes it from the GPU
+  double* h_result_dev = nullptr;              // the same buffer as the device sees it
+  volatile unsigned long long* h_flag = nullptr;  // pinned + mapped word the host polls (epilogue.cuh)
+  unsigned long long* h_flag_dev = nullptr;
+  unsigned long long host_seq = 0;  // passes published to the host so far
+  unsigned long long xr_seq = 0;    // cross-rank (mailbox) passes so far: advances in lock step on every rank
+  bool ep_armed = false;            // the pass just launched publishes through the epilogue
+  int ep_world = 1;                 // ... folded / gathered over this many ranks inside the kernel
   unsigned long long* d_counters = nullptr;
   int* d_err = nullptr;
   unsigned long long* d_tile_state = nullptr;
@@ -71,5 +78,8 @@ int nccl_bind(dq4ml_ctx* ctx, const void* id128, int rank, int world);
 void nccl_unbind(dq4ml_ctx* ctx);
 // In-stream sum all-reduce of `count` doubles at device pointer `buf` (no-op when no communicator is bound).
 int nccl_allreduce_device(dq4ml_ctx* ctx, double* buf, int64_t count);
+// Peer mailboxes of the bound ranks (epilogue.cuh): fills ep->peer / world / rank and returns true when every rank could
+// map every other rank's mailbox at bind time; false = the per-pass vectors go through ncclAllReduce instead.
+bool nccl_mailboxes(const dq4ml_ctx* ctx, XrEpilogue* ep);
 
 }  // namespace dq4ml

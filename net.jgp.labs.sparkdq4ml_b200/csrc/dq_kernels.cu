@@ -371,7 +371,9 @@ cudaError_t launch_udf_price_corr(const double* price, const int32_t* guest, con
 }
 
 size_t dq_filter_state_bytes(int64_t n) {
-  const int64_t tiles = (n + kFilterTile - 1) / kFilterTile;
+  // one status word per tile of the kernel with the smaller tile (the persistent kernel, 2048 rows); the
+  // one-CTA-per-tile kernel uses the first half of them
+  const int64_t tiles = (n + kFilterStateTile - 1) / kFilterStateTile;
   return static_cast<size_t>(tiles > 0 ? tiles : 1) * sizeof(unsigned long long);
 }
 
@@ -447,9 +449,9 @@ cudaError_t launch_column_heads(const DeviceCols& cols, const double* label, int
 // dq4ml_dq_filter, needs a dq4ml_ctx (whose creation allocates scratch) and grows its tile-status buffer with
 // cudaMalloc; this one takes no ctx and touches no allocator at all.
 //
-// Where the scratch lives instead: the look-back words of the compaction kernel (one 64-bit word per 4096-row tile)
+// Where the scratch lives instead: the look-back words of the compaction kernel (one 64-bit word per 2048-row tile)
 // plus the two row counters sit in the file-scope device array below.  It is part of the library image, so every GPU
-// that loads libdq4ml.so carries these ~128 KB until the process exits, whether or not this entry point is ever used.
+// that loads libdq4ml.so carries these ~256 KB until the process exits, whether or not this entry point is ever used.
 // That fixed size is what bounds the call: at most DQ4ML_NOALLOC_MAX_ROWS rows per call.
 #include <mutex>
 
@@ -459,7 +461,7 @@ namespace dq4ml {
 namespace {
 
 constexpr int64_t kNoAllocMaxRows = DQ4ML_NOALLOC_MAX_ROWS;
-constexpr int64_t kNoAllocMaxTiles = (kNoAllocMaxRows + kFilterTile - 1) / kFilterTile;
+constexpr int64_t kNoAllocMaxTiles = (kNoAllocMaxRows + kFilterStateTile - 1) / kFilterStateTile;
 constexpr int kNoAllocHeaderWords = 32;  // words [0,1] = the two row counters; the rest of the first 256 bytes is unused
 constexpr int kNoAllocMaxDevices = 64;
 
@@ -527,7 +529,7 @@ extern "C" int dq4ml_dq_filter_noalloc(void* stream, const int32_t* guest, const
   const dq4ml_dq_params p = params != nullptr ? *params : dq4ml_dq_params_default();
   int64_t launched = 0;
   // The array still holds the previous call's words: launch_dq_filter zeroes the counters and the first
-  // ceil(n / 4096) look-back words (one per tile of kFilterTile rows) on `s` (cudaMemsetAsync, no allocation) before
+  // ceil(n / 2048) look-back words (one per tile of kFilterStateTile rows) on `s` (cudaMemsetAsync, no allocation) before
   // the kernel reads them.
   e = launch_dq_filter(guest, price, n, p, guest_out, price_out, scratch + kNoAllocHeaderWords, scratch, s, &launched);
   unsigned long long counts[2] = {0, 0};

@@ -25,6 +25,21 @@ struct DeviceDq {
   dq4ml_dq_params params{};
 };
 
+// How the last CTA of a streaming pass hands its result vector over (epilogue.cuh): to mapped pinned host memory, after
+// an exchange through the peer mailboxes when several ranks are bound.
+constexpr int kXrMaxRanks = 16;
+constexpr int kXrSlotDoubles = 128;  // longest published vector: SummCoreOp<32> = 67 sums + 33 centres
+struct XrEpilogue {
+  double* host_out = nullptr;              // device alias of the pinned result buffer; nullptr = leave it in scratch.result
+  unsigned long long* host_flag = nullptr; // the word the host polls
+  unsigned long long host_seq = 0;         // value that word takes when this pass's vector is complete
+  int world = 1, rank = 0;                 // world > 1: exchange through the mailboxes below
+  int gather = 0;                          // 0: fold the ranks' vectors in rank order; 1: hand the host all of them
+  int extra_consts = 0;                    // append this many of the pass's device constants to the vector
+  unsigned long long xr_seq = 0;           // number of this cross-rank pass (identical on every rank)
+  unsigned char* peer[kXrMaxRanks] = {};   // rank r's mailbox as mapped into this process; peer[rank] is our own
+};
+
 // Scratch a ctx lends to the launchers.
 struct Scratch {
   double* partials;        // grid x NACC doubles
@@ -33,18 +48,25 @@ struct Scratch {
   double* result;          // >= 4096 doubles
   double* consts;          // >= 64 doubles
   int sm_count;
+  XrEpilogue ep;           // armed per pass by api.cpp
 };
 
 enum StreamOpKind {
   kOpWls = 0, kOpLsq = 1, kOpSummCore = 2, kOpSummFull = 3, kOpEval = 4, kOpGrad = 5,
   // weighted variants: column 0 of the table is the instance weight, the features follow (so at most kMaxCols - 1 of them)
-  kOpSummCoreW = 6, kOpLsqW = 7, kOpWResid = 8
+  kOpSummCoreW = 6, kOpLsqW = 7, kOpWResid = 8,
+  // huber loss (LinearRegression.setLoss("huber")): HuberAggregator, plain and with the weight as column 0
+  kOpHuber = 9, kOpHuberW = 10
 };
 
 struct LsqConsts {
   double eff[kMaxCols];
   double offset;
   double inv_ystd;
+};
+struct HuberConsts {
+  double eff[kMaxCols];  // coefficient / featuresStd per column of the streamed table (0 for the weight column)
+  double intercept, sigma, epsilon;
 };
 struct EvalConsts {
   double coef[kMaxCols];
@@ -77,6 +99,7 @@ cudaError_t launch_udf_price_corr(const double* price, const int32_t* guest, con
 
 // Stable filter-compaction (single pass, decoupled look-back).  tile_state: dq_filter_state_bytes(n) bytes of scratch
 // that the launcher zeroes itself; counters: 2 x uint64 device ([0] survivors, [1] rows after rule 1).
+constexpr int64_t kFilterStateTile = 2048;  // rows per status word (the tile of the persistent filter kernel)
 size_t dq_filter_state_bytes(int64_t n);
 cudaError_t launch_dq_filter(const int32_t* guest, const double* price, int64_t n, const dq4ml_dq_params& p,
                              int32_t* guest_out, double* price_out, unsigned long long* tile_state,

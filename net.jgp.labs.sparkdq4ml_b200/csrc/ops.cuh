@@ -242,6 +242,76 @@ struct WResidOp {
   }
 };
 
+// ml.optim.aggregator.HuberAggregator.add (Spark 2.3+, LinearRegression.setLoss("huber")): the label is NOT standardised,
+// features enter as value / featuresStd.  margin = x.(c / std) + intercept, r = label - margin; inside |r| <= sigma eps
+// the row adds (sigma + r^2 / sigma) / 2 to the loss, -(r / sigma) x_j / std_j to the coefficient gradients, -(r / sigma)
+// to the intercept's and (1 - (r / sigma)^2) / 2 to sigma's; outside it adds (sigma + 2 eps |r| - sigma eps^2) / 2,
+// -+eps x_j / std_j, -+eps and (1 - eps^2) / 2.  Accumulators: loss, count, d/d intercept, d/d sigma, then the column
+// sums of factor * x_j (the host applies the common 1 / std_j).
+template <int DMAX>
+struct HuberOp {
+  static constexpr int NACC = 4 + DMAX;
+  static constexpr int NCONST = 0;
+  static constexpr bool HAS_OUT = false;
+  double eff[DMAX];
+  double intercept, sigma, epsilon;
+  __host__ __device__ static constexpr double identity(int) { return 0.0; }
+  __host__ __device__ static constexpr int kind(int) { return kSum; }
+
+  __device__ __forceinline__ double row(double (&acc)[NACC], const double*, const double (&x)[DMAX], double y,
+                                        bool keep, int) const {
+    double margin = intercept;
+#pragma unroll
+    for (int j = 0; j < DMAX; ++j) margin = fma(x[j], eff[j], margin);
+    const double r = y - margin, rs = r / sigma;
+    const bool inner = fabs(r) <= sigma * epsilon;
+    const double loss = inner ? 0.5 * (sigma + r * rs) : 0.5 * (sigma + 2.0 * epsilon * fabs(r) - sigma * epsilon * epsilon);
+    const double factor = keep ? (inner ? -rs : (r >= 0.0 ? -epsilon : epsilon)) : 0.0;
+    const double dsig = inner ? 0.5 * (1.0 - rs * rs) : 0.5 * (1.0 - epsilon * epsilon);
+    acc[0] += keep ? loss : 0.0;
+    acc[1] += keep ? 1.0 : 0.0;
+    acc[2] += factor;
+    acc[3] += keep ? dsig : 0.0;
+#pragma unroll
+    for (int j = 0; j < DMAX; ++j) acc[4 + j] = fma(factor, x[j], acc[4 + j]);
+    return 0.0;
+  }
+};
+
+// The same with instance weights: column 0 of the table is the weight (eff[0] = 0), rows of weight 0 are skipped like
+// HuberAggregator.add does; accumulator 1 is the weight sum.
+template <int DMAX>
+struct HuberWOp {
+  static constexpr int NACC = 4 + DMAX;
+  static constexpr int NCONST = 0;
+  static constexpr bool HAS_OUT = false;
+  double eff[DMAX];
+  double intercept, sigma, epsilon;
+  __host__ __device__ static constexpr double identity(int) { return 0.0; }
+  __host__ __device__ static constexpr int kind(int) { return kSum; }
+
+  __device__ __forceinline__ double row(double (&acc)[NACC], const double*, const double (&x)[DMAX], double y,
+                                        bool keep, int) const {
+    const double w = x[0];
+    const bool on = keep && w != 0.0;
+    double margin = intercept;
+#pragma unroll
+    for (int j = 1; j < DMAX; ++j) margin = fma(x[j], eff[j], margin);
+    const double r = y - margin, rs = r / sigma;
+    const bool inner = fabs(r) <= sigma * epsilon;
+    const double loss = inner ? 0.5 * (sigma + r * rs) : 0.5 * (sigma + 2.0 * epsilon * fabs(r) - sigma * epsilon * epsilon);
+    const double factor = on ? w * (inner ? -rs : (r >= 0.0 ? -epsilon : epsilon)) : 0.0;
+    const double dsig = inner ? 0.5 * (1.0 - rs * rs) : 0.5 * (1.0 - epsilon * epsilon);
+    acc[0] += on ? w * loss : 0.0;
+    acc[1] += keep ? (w >= 0.0 ? w : __longlong_as_double(0x7ff8000000000000LL)) : 0.0;  // require(weight >= 0.0)
+    acc[2] += factor;
+    acc[3] += on ? w * dsig : 0.0;
+#pragma unroll
+    for (int j = 1; j < DMAX; ++j) acc[4 + j] = fma(factor, on ? x[j] : 0.0, acc[4 + j]);
+    return 0.0;
+  }
+};
+
 // LinearRegressionModel.transform + RegressionMetrics / LinearRegressionSummary sums in one pass: yhat = x.beta + b;
 // residual r = y - yhat; accumulators n, sum r^2, sum y, sum y^2, sum |r|, sum r, sum r*y, min r, max r (the last four
 // feed explainedVariance and devianceResiduals).  Per-row output: prediction (mode 0) or residual (mode 1).

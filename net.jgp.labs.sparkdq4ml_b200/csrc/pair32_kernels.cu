@@ -171,7 +171,7 @@ template <int OP, int DQMODE, int PH, int BLK>
 __global__ void __launch_bounds__(BLK, 1)
     pair32_kernel(const PairConsts c, const ColTable cols, const int d, const double* __restrict__ label, const DqArgs dq,
                   const int64_t n, const int hs, const double* __restrict__ centres, double* __restrict__ partials,
-                  unsigned int* __restrict__ ticket, double* __restrict__ result) {
+                  unsigned int* __restrict__ ticket, double* __restrict__ result, const XrEpilogue ep) {
   constexpr int NT = PairShape<OP, PH>::NT;
   constexpr int kPairTile = (BLK / 2) * PR;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, h = lane & 1;
@@ -226,6 +226,8 @@ __global__ void __launch_bounds__(BLK, 1)
     if (threadIdx.x == 0) result[out] = v;
   }
   if (threadIdx.x == 0) *ticket = 0u;  // ready for the next launch on this stream
+  // the vector has the 32-column bucket's public layout (LsqOp<32>: 34 sums; SummCoreOp<32>: 67 sums + 33 centres)
+  xr_publish(ep, result, OP == kPairLsq ? 2 + 32 : 1 + 2 * 33, centres, [](int) { return static_cast<int>(kSum); });
 }
 
 template <int OP, int PH, int BLK>
@@ -240,11 +242,11 @@ cudaError_t launch_shape(int dq_mode, const PairConsts& c, const ColTable& cols,
   const unsigned gsz = static_cast<unsigned>(grid);
   const int hs = (d + 1) / 2;  // columns per lane: the table is split evenly over the pair
   if (dq_mode == kDqNone)
-    pair32_kernel<OP, kDqNone, PH, BLK><<<gsz, BLK, 0, stream>>>(c, cols, d, label, dq, n, hs, scratch.consts, scratch.partials, scratch.ticket, scratch.result);
+    pair32_kernel<OP, kDqNone, PH, BLK><<<gsz, BLK, 0, stream>>>(c, cols, d, label, dq, n, hs, scratch.consts, scratch.partials, scratch.ticket, scratch.result, scratch.ep);
   else if (dq_mode == kDqSeparate)
-    pair32_kernel<OP, kDqSeparate, PH, BLK><<<gsz, BLK, 0, stream>>>(c, cols, d, label, dq, n, hs, scratch.consts, scratch.partials, scratch.ticket, scratch.result);
+    pair32_kernel<OP, kDqSeparate, PH, BLK><<<gsz, BLK, 0, stream>>>(c, cols, d, label, dq, n, hs, scratch.consts, scratch.partials, scratch.ticket, scratch.result, scratch.ep);
   else
-    pair32_kernel<OP, kDqLab, PH, BLK><<<gsz, BLK, 0, stream>>>(c, cols, d, label, dq, n, hs, scratch.consts, scratch.partials, scratch.ticket, scratch.result);
+    pair32_kernel<OP, kDqLab, PH, BLK><<<gsz, BLK, 0, stream>>>(c, cols, d, label, dq, n, hs, scratch.consts, scratch.partials, scratch.ticket, scratch.result, scratch.ep);
   return cudaGetLastError();
 }
 

@@ -302,7 +302,391 @@ class QuasiNewton {
   bool owlqn_;
 };
 
+// ---------------------------------------------------------------------------------------------------------------------
+// Bound-constrained quasi-Newton: breeze.optimize.LBFGSB (Byrd, Lu, Nocedal & Zhu), which LinearRegression.train runs
+// for loss = huber so that the scale sigma stays positive.  Hessian approximation in compact form,
+// B = theta I - W M W^T with W = [Y, theta S]; every step: generalized Cauchy point along the projected steepest-descent
+// path, then (from the second iteration on) an unconstrained minimisation over the variables that are free at the Cauchy
+// point, then a strong-Wolfe line search capped at the largest feasible step.  Small dense algebra only (2m <= 20).
+struct Dense {  // row-major
+  int rows = 0, cols = 0;
+  Vec a;
+  Dense() = default;
+  Dense(int r, int c) : rows(r), cols(c), a(static_cast<size_t>(r) * c, 0.0) {}
+  double& at(int i, int j) { return a[static_cast<size_t>(i) * cols + j]; }
+  double at(int i, int j) const { return a[static_cast<size_t>(i) * cols + j]; }
+};
+
+Vec mat_vec(const Dense& m, const Vec& v) {
+  Vec out(m.rows, 0.0);
+  for (int i = 0; i < m.rows; ++i) {
+    double acc = 0.0;
+    for (int j = 0; j < m.cols; ++j) acc += m.at(i, j) * v[j];
+    out[i] = acc;
+  }
+  return out;
+}
+Vec mat_t_vec(const Dense& m, const Vec& v) {
+  Vec out(m.cols, 0.0);
+  for (int i = 0; i < m.rows; ++i)
+    for (int j = 0; j < m.cols; ++j) out[j] += m.at(i, j) * v[i];
+  return out;
+}
+
+// Solves A X = B in place by Gaussian elimination with partial pivoting (B holds nrhs columns); false if singular.
+bool lu_solve(Dense a, Dense& b) {
+  const int n = a.rows;
+  for (int k = 0; k < n; ++k) {
+    int piv = k;
+    for (int i = k + 1; i < n; ++i)
+      if (std::fabs(a.at(i, k)) > std::fabs(a.at(piv, k))) piv = i;
+    if (a.at(piv, k) == 0.0 || std::isnan(a.at(piv, k))) return false;
+    if (piv != k) {
+      for (int j = 0; j < n; ++j) std::swap(a.at(k, j), a.at(piv, j));
+      for (int j = 0; j < b.cols; ++j) std::swap(b.at(k, j), b.at(piv, j));
+    }
+    for (int i = k + 1; i < n; ++i) {
+      const double f = a.at(i, k) / a.at(k, k);
+      if (f == 0.0) continue;
+      for (int j = k; j < n; ++j) a.at(i, j) -= f * a.at(k, j);
+      for (int j = 0; j < b.cols; ++j) b.at(i, j) -= f * b.at(k, j);
+    }
+  }
+  for (int j = 0; j < b.cols; ++j)
+    for (int i = n - 1; i >= 0; --i) {
+      double acc = b.at(i, j);
+      for (int k = i + 1; k < n; ++k) acc -= a.at(i, k) * b.at(k, j);
+      b.at(i, j) = acc / a.at(i, i);
+    }
+  return true;
+}
+
+class BoundedQuasiNewton {
+ public:
+  BoundedQuasiNewton(const CostFn& f, Vec lower, Vec upper, int max_iter, double tol, int m)
+      : f_(f), lo_(std::move(lower)), hi_(std::move(upper)), max_iter_(max_iter), tol_(tol), m_(m) {}
+
+  QnResult run(Vec x0) {
+    const int n = static_cast<int>(x0.size());
+    QnResult res;
+    Point s;
+    s.x = std::move(x0);
+    s.value = f_(s.x, s.grad);
+    reset_curvature(n);
+    const double initial = s.value;
+    std::deque<double> recent{std::numeric_limits<double>::infinity()};
+    bool failed_once = false, search_failed = false;
+    for (;;) {
+      res.adjusted_values.push_back(s.value);
+      if (const char* why = stop_reason(s, recent, initial, search_failed)) {
+        res.stop_reason = why;
+        break;
+      }
+      try {
+        Vec c;
+        Vec target = cauchy_point(s, &c);
+        if (s.iter > 0) target = subspace_minimum(s, target, c);
+        Vec dir(n);
+        for (int i = 0; i < n; ++i) dir[i] = target[i] - s.x[i];
+        const double alpha = capped_wolfe_step(s, dir);
+        Point nx;
+        nx.x = clamped_step(s.x, dir, alpha);
+        nx.value = f_(nx.x, nx.grad);
+        nx.iter = s.iter + 1;
+        Vec sk(n), yk(n);
+        for (int i = 0; i < n; ++i) {
+          sk[i] = nx.x[i] - s.x[i];
+          yk[i] = nx.grad[i] - s.grad[i];
+        }
+        absorb_pair(sk, yk);
+        recent.push_back(nx.value);
+        while (recent.size() > 20) recent.pop_front();
+        failed_once = false;
+        s = std::move(nx);
+      } catch (const QnFailure&) {
+        if (!failed_once) {
+          failed_once = true;
+          reset_curvature(n);
+        } else {
+          search_failed = true;
+        }
+      }
+    }
+    res.x = s.x;
+    res.evaluations = f_.evals();
+    return res;
+  }
+
+ private:
+  struct Point {
+    Vec x, grad;
+    double value = 0.0;
+    int iter = 0;
+  };
+
+  void reset_curvature(int n) {
+    theta_ = 1.0;
+    w_ = Dense(n, 1);
+    mm_ = Dense(1, 1);
+    ys_.clear();
+    ss_.clear();
+  }
+
+  // LBFGSB.defaultConvergenceCheck: projected-gradient step below 1e-5 (infinity norm), or the FirstOrderMinimizer tests
+  const char* stop_reason(const Point& s, const std::deque<double>& recent, double initial, bool search_failed) const {
+    double pg = 0.0;
+    for (size_t i = 0; i < s.x.size(); ++i) {
+      double v = s.x[i] - s.grad[i];
+      v = v <= lo_[i] ? lo_[i] : (hi_[i] <= v ? hi_[i] : v);
+      pg = std::max(pg, std::fabs(v - s.x[i]));
+    }
+    if (pg < 1e-5) return "projected gradient converged";
+    if (max_iter_ >= 0 && s.iter >= max_iter_) return "max iterations";
+    if (recent.size() >= 2) {
+      const double mx = *std::max_element(recent.begin(), recent.end());
+      if (std::fabs(s.value - mx) <= tol_ * initial) return "function values converged";
+    }
+    if (norm2(s.grad) <= std::max(tol_ * s.value, 1e-8)) return "gradient converged";
+    if (search_failed) return "line search failed";
+    return nullptr;
+  }
+
+  // Algorithm CP.  Returns the Cauchy point; *c_out = W^T (x_cauchy - x).
+  Vec cauchy_point(const Point& s, Vec* c_out) const {
+    const int n = static_cast<int>(s.x.size());
+    const Vec &x = s.x, &g = s.grad;
+    Vec d(n, 0.0), t(n, std::numeric_limits<double>::max());
+    for (int i = 0; i < n; ++i) {
+      if (g[i] == 0.0) continue;
+      const double ti = g[i] < 0.0 ? (x[i] - hi_[i]) / g[i] : (x[i] - lo_[i]) / g[i];
+      d[i] = ti == 0.0 ? 0.0 : -g[i];
+      t[i] = ti;
+    }
+    Vec xc = x;
+    Vec p = mat_t_vec(w_, d);
+    Vec c(mm_.rows, 0.0);
+    double f1 = dot(g, d);
+    double f2 = -theta_ * f1 - dot(p, mat_vec(mm_, p));
+    double dt_min = -(f1 / f2);
+    double old_t = 0.0;
+    std::vector<int> order(n);
+    for (int i = 0; i < n; ++i) order[i] = i;
+    std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return t[a] < t[b]; });
+    int i = 0;
+    while (i < n && t[order[i]] == 0.0) ++i;
+    if (i < n) {
+      int b = order[i];
+      double min_t = t[b], delta_t = min_t - old_t;
+      while (delta_t <= dt_min && i < n) {
+        xc[b] = d[b] > 0.0 ? hi_[b] : lo_[b];
+        const double zb = xc[b] - x[b];
+        for (size_t k = 0; k < c.size(); ++k) c[k] += p[k] * delta_t;
+        Vec wb(w_.cols);
+        for (int k = 0; k < w_.cols; ++k) wb[k] = w_.at(b, k);
+        const double gb = g[b];
+        f1 += delta_t * f2 + gb * gb + theta_ * gb * zb - gb * dot(wb, mat_vec(mm_, c));
+        f2 += -theta_ * gb * gb - 2.0 * (gb * dot(wb, mat_vec(mm_, p))) - gb * gb * dot(wb, mat_vec(mm_, wb));
+        for (size_t k = 0; k < p.size(); ++k) p[k] += wb[k] * gb;
+        d[b] = 0.0;
+        dt_min = -f1 / f2;
+        old_t = min_t;
+        ++i;
+        if (i < n) {
+          b = order[i];
+          min_t = t[b];
+          delta_t = min_t - old_t;
+        }
+      }
+    }
+    dt_min = std::max(dt_min, 0.0);
+    old_t += dt_min;
+    for (int k = i; k < n; ++k) xc[order[k]] = x[order[k]] + old_t * d[order[k]];
+    for (size_t k = 0; k < c.size(); ++k) c[k] += p[k] * dt_min;
+    *c_out = c;
+    return xc;
+  }
+
+  // Direct primal method over the variables that are free at the Cauchy point, shortened by Byrd et al.'s alpha* so that
+  // the result stays feasible.  (Breeze 0.13.2's findAlpha, as far as it can be recalled without the jar, never
+  // shortens the step; an infeasible subspace minimum then trips `require(init <= bound)` in its line search and the fit
+  // dies.  Wherever Breeze succeeds, alpha* = 1 and this is the same algorithm.)
+  Vec subspace_minimum(const Point& s, const Vec& xc, const Vec& c) const {
+    const int n = static_cast<int>(s.x.size());
+    const double inv_theta = 1.0 / theta_;
+    std::vector<int> free_idx;
+    for (int i = 0; i < n; ++i)
+      if (xc[i] != hi_[i] && xc[i] != lo_[i]) free_idx.push_back(i);
+    const int nf = static_cast<int>(free_idx.size()), k2 = w_.cols;
+    Dense wz(k2, nf);
+    for (int j = 0; j < nf; ++j)
+      for (int k = 0; k < k2; ++k) wz.at(k, j) = w_.at(free_idx[j], k);
+    const Vec mc = mat_vec(mm_, c);
+    const Vec wmc = mat_vec(w_, mc);
+    Vec rc(nf);
+    for (int j = 0; j < nf; ++j) {
+      const int i = free_idx[j];
+      rc[j] = s.grad[i] + (xc[i] - s.x[i]) * theta_ - wmc[i];
+    }
+    Vec v = mat_vec(mm_, mat_vec(wz, rc));
+    Dense nmat(k2, k2);  // I - M (WZ WZ^T) / theta
+    Dense wzwz(k2, k2);
+    for (int a = 0; a < k2; ++a)
+      for (int b = 0; b < k2; ++b) {
+        double acc = 0.0;
+        for (int j = 0; j < nf; ++j) acc += wz.at(a, j) * wz.at(b, j);
+        wzwz.at(a, b) = acc * inv_theta;
+      }
+    for (int a = 0; a < k2; ++a)
+      for (int b = 0; b < k2; ++b) {
+        double acc = 0.0;
+        for (int k = 0; k < k2; ++k) acc += mm_.at(a, k) * wzwz.at(k, b);
+        nmat.at(a, b) = (a == b ? 1.0 : 0.0) - acc;
+      }
+    Dense rhs(k2, 1);
+    for (int a = 0; a < k2; ++a) rhs.at(a, 0) = v[a];
+    if (!lu_solve(nmat, rhs)) throw QnFailure{"singular subspace system"};
+    for (int a = 0; a < k2; ++a) v[a] = rhs.at(a, 0);
+    const Vec wzv = mat_t_vec(wz, v);
+    Vec du(nf);
+    for (int j = 0; j < nf; ++j) du[j] = -(rc[j] * inv_theta + wzv[j] * inv_theta * inv_theta);
+    double alpha = 1.0;  // the largest step <= 1 along du that stays inside the bounds
+    for (int j = 0; j < nf; ++j) {
+      const int i = free_idx[j];
+      if (du[j] > 0.0) alpha = std::min(alpha, (hi_[i] - xc[i]) / du[j]);
+      else if (du[j] < 0.0) alpha = std::min(alpha, (lo_[i] - xc[i]) / du[j]);
+    }
+    Vec out = xc;
+    for (int j = 0; j < nf; ++j) out[free_idx[j]] += alpha * du[j];
+    return out;
+  }
+
+  void absorb_pair(const Vec& sk, const Vec& yk) {
+    std::deque<Vec> ys = ys_, ss = ss_;
+    if (static_cast<int>(ys.size()) >= m_) {
+      ys.pop_front();
+      ss.pop_front();
+    }
+    ys.push_back(yk);
+    ss.push_back(sk);
+    const double sy = dot(sk, yk), yy = dot(yk, yk);
+    if (!(2.2e-16 * yy < std::fabs(sy))) return;  // curvature too small: the pair is not absorbed at all
+    ys_ = std::move(ys);
+    ss_ = std::move(ss);
+    const int k = static_cast<int>(ys_.size()), n = static_cast<int>(sk.size());
+    theta_ = yy / sy;
+    w_ = Dense(n, 2 * k);
+    for (int i = 0; i < n; ++i)
+      for (int j = 0; j < k; ++j) {
+        w_.at(i, j) = ys_[j][i];
+        w_.at(i, k + j) = theta_ * ss_[j][i];
+      }
+    // M = [[-D, L^T], [L, theta S^T S]]^-1 with A = S^T Y, D = diag(A), L = strictly lower part of A
+    Dense big(2 * k, 2 * k);
+    for (int a = 0; a < k; ++a)
+      for (int b = 0; b < k; ++b) {
+        const double sayb = dot(ss_[a], ys_[b]);
+        if (a == b) big.at(a, a) = -sayb;
+        if (a > b) {
+          big.at(k + a, b) = sayb;
+          big.at(b, k + a) = sayb;
+        }
+        big.at(k + a, k + b) = theta_ * dot(ss_[a], ss_[b]);
+      }
+    Dense inv(2 * k, 2 * k);
+    for (int a = 0; a < 2 * k; ++a) inv.at(a, a) = 1.0;
+    if (!lu_solve(big, inv)) throw QnFailure{"singular curvature matrix"};
+    mm_ = std::move(inv);
+  }
+
+  Vec clamped_step(const Vec& x, const Vec& dir, double alpha) const {
+    Vec nx(x.size());
+    for (size_t i = 0; i < nx.size(); ++i) {
+      double v = x[i] + dir[i] * alpha;
+      if (v > hi_[i]) v = hi_[i];
+      if (v < lo_[i]) v = lo_[i];
+      nx[i] = v;
+    }
+    return nx;
+  }
+
+  // StrongWolfeLineSearch(maxZoomIter = 64, maxLineSearchIter = 64).minimizeWithBound(f, 1.0, largest feasible step)
+  double capped_wolfe_step(const Point& s, const Vec& dir) {
+    double bound = std::numeric_limits<double>::infinity();
+    for (size_t i = 0; i < dir.size(); ++i) {
+      if (dir[i] == 0.0) continue;
+      const double b = ((dir[i] < 0.0 ? lo_[i] : hi_[i]) - s.x[i]) / dir[i];
+      if (b < bound) bound = b;
+    }
+    if (!(1.0 <= bound)) throw SolveError{DQ4ML_ERR_INVALID, "requirement failed: init value should <= bound (LBFGSB line search)"};
+    struct Bracket {
+      double t, dd, fval;
+    };
+    const double c1 = 1e-4, c2 = 0.9;
+    auto phi = [&](double t) {
+      Vec nx = clamped_step(s.x, dir, t), g;
+      Bracket b;
+      b.t = t;
+      b.fval = f_(nx, g);
+      b.dd = dot(g, dir);
+      return b;
+    };
+    auto cubic = [](const Bracket& l, const Bracket& r) {
+      const double d1 = l.dd + r.dd - 3.0 * (l.fval - r.fval) / (l.t - r.t);
+      const double d2 = std::sqrt(d1 * d1 - l.dd * r.dd);
+      const double t = r.t - (r.t - l.t) * (r.dd + d2 - d1) / (r.dd - l.dd + 2.0 * d2);
+      const double lo = l.t + 0.1 * (r.t - l.t), hi = l.t + 0.9 * (r.t - l.t);
+      return t < lo ? lo : (t > hi ? hi : t);
+    };
+    double t = 1.0;
+    Bracket low = phi(0.0);
+    const double fval = low.fval, dd = low.dd;
+    if (dd > 0.0) throw QnFailure{"non-descent direction"};
+    auto zoom = [&](Bracket lo, Bracket hi) {
+      for (int i = 0; i < 64; ++i) {
+        const double tt = lo.t > hi.t ? cubic(hi, lo) : cubic(lo, hi);
+        const Bracket c = phi(tt);
+        if (c.fval > fval + c1 * c.t * dd || c.fval >= lo.fval) {
+          hi = c;
+        } else {
+          if (std::fabs(c.dd) <= c2 * std::fabs(dd)) return c.t;
+          if (c.dd * (hi.t - lo.t) >= 0.0) hi = lo;
+          lo = c;
+        }
+      }
+      throw QnFailure{"zoom failed"};
+    };
+    for (int i = 0; i < 64; ++i) {
+      const Bracket c = phi(t);
+      if (std::isinf(c.fval) || std::isnan(c.fval)) {
+        t /= 2.0;
+        continue;
+      }
+      if (c.fval > fval + c1 * t * dd || (c.fval >= low.fval && i > 0)) return zoom(low, c);
+      if (std::fabs(c.dd) <= c2 * std::fabs(dd)) return c.t;
+      if (c.dd >= 0.0) return zoom(c, low);
+      low = c;
+      if (t == bound) return bound;
+      t = std::min(t * 1.5, bound);
+    }
+    throw QnFailure{"line search failed"};
+  }
+
+  MemoObjective f_;
+  Vec lo_, hi_;
+  int max_iter_;
+  double tol_;
+  int m_;
+  double theta_ = 1.0;
+  Dense w_, mm_;
+  std::deque<Vec> ys_, ss_;  // oldest first
+};
+
 }  // namespace
+
+QnResult lbfgsb_minimize(const CostFn& f, Vec x0, const Vec& lower, const Vec& upper, int max_iter, double tol, int memory) {
+  BoundedQuasiNewton qn(f, lower, upper, max_iter, tol, memory);
+  return qn.run(std::move(x0));
+}
 
 QnResult quasi_newton_minimize(const CostFn& f, Vec x0, int max_iter, double tol, const L1Fn& l1, int memory) {
   QuasiNewton qn(f, max_iter, tol, l1, memory);
@@ -639,6 +1023,68 @@ LrModel lbfgs_path_fit(const ColumnStats& st, int d, const LrParams& p, const Ls
     s += model.coefficients[j] * f_mean[j];
   }
   model.intercept = p.fit_intercept ? y_mean - s : 0.0;
+  return model;
+}
+
+// LinearRegression.train with loss = huber: HuberAggregator per evaluation (label NOT standardised, features divided by
+// their standard deviation), L2 penalty with regParam as given, parameters [coefficients, intercept?, sigma] started at
+// all ones, LBFGSB with sigma >= Double.MinPositiveValue.
+LrModel huber_path_fit(const ColumnStats& st, int d, const LrParams& p, const HuberPassFn& pass) {
+  if (!(st.count > 0.0)) throw SolveError{DQ4ML_ERR_EMPTY, "Training dataset is empty."};
+  LrModel model;
+  model.num_rows = static_cast<int64_t>(st.count);
+  model.data_passes = 1;  // the summarizer pass
+  const double y_mean = st.mean[d];
+  const double raw_y_std = std::sqrt(st.variance[d]);
+  if (raw_y_std == 0.0) {
+    if (p.fit_intercept || y_mean == 0.0) {
+      model.coefficients.assign(d, 0.0);
+      model.intercept = y_mean;
+      model.objective_history = {0.0};
+      model.solver_used = "trivial";
+      return model;
+    }
+    if (p.reg_param != 0.0)
+      throw SolveError{DQ4ML_ERR_INVALID, "The standard deviation of the label is zero. Model cannot be regularized."};
+  }
+  Vec f_std(d);
+  for (int j = 0; j < d; ++j) f_std[j] = std::sqrt(st.variance[j]);
+  const double l2 = p.reg_param;  // (1 - elasticNetParam) regParam with elasticNetParam = 0
+  const int dim = d + (p.fit_intercept ? 2 : 1);
+
+  CostFn cost = [&](Vec& c, Vec& grad) {
+    double loss_sum = 0.0, w_sum = 0.0;
+    Vec gsum(dim, 0.0);
+    pass(c, f_std, loss_sum, w_sum, gsum);
+    double loss = loss_sum / w_sum;
+    grad.resize(dim);
+    for (int j = 0; j < dim; ++j) grad[j] = gsum[j] / w_sum;
+    if (l2 != 0.0) {
+      double s = 0.0;
+      for (int j = 0; j < d; ++j) {
+        if (p.standardization) {
+          s += c[j] * c[j];
+          grad[j] += l2 * c[j];
+        } else if (f_std[j] != 0.0) {
+          const double t = c[j] / (f_std[j] * f_std[j]);
+          s += c[j] * t;
+          grad[j] += l2 * t;
+        }
+      }
+      loss += 0.5 * s * l2;
+    }
+    return loss;
+  };
+  Vec lower(dim, -std::numeric_limits<double>::max()), upper(dim, std::numeric_limits<double>::max());
+  lower[dim - 1] = std::numeric_limits<double>::denorm_min();  // Double.MinPositiveValue
+  QnResult r = lbfgsb_minimize(cost, Vec(dim, 1.0), lower, upper, p.max_iter, p.tol, 10);
+  model.objective_history = r.adjusted_values;
+  model.solver_used = "lbfgsb";
+  model.data_passes += r.evaluations;
+  model.coefficients.assign(r.x.begin(), r.x.begin() + d);
+  for (int j = 0; j < d; ++j) model.coefficients[j] *= f_std[j] != 0.0 ? 1.0 / f_std[j] : 0.0;
+  model.intercept = p.fit_intercept ? r.x[d] : 0.0;
+  model.scale = r.x[dim - 1];
   return model;
 }
 

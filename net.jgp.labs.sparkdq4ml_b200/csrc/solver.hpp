@@ -38,6 +38,7 @@ struct LrModel {
   // WeightedLeastSquaresModel.diagInvAtWA: diagonal of (A^T W A)^-1 in original units (features, then the intercept);
   // filled on the Cholesky path only, like Spark.  Empty = "No Std. Error of coefficients available".
   Vec diag_inv_atwa;
+  double scale = 1.0;  // LinearRegressionModel.scale: the huber loss's sigma; 1.0 for squaredError
 };
 
 // Diagonal of the inverse of a packed upper SPD matrix (LAPACK dpptri, diagonal only).  Returns false if not SPD.
@@ -67,6 +68,9 @@ struct QnResult {
 // Breeze LBFGS(maxIter, m = 10, tol) when l1 is empty, else OWLQN(maxIter, 10, l1, tol).
 QnResult quasi_newton_minimize(const CostFn& f, Vec x0, int max_iter, double tol, const L1Fn& l1, int memory = 10);
 
+// Breeze LBFGSB(lowerBounds, upperBounds, maxIter, m = 10, tol): what LinearRegression runs for loss = huber.
+QnResult lbfgsb_minimize(const CostFn& f, Vec x0, const Vec& lower, const Vec& upper, int max_iter, double tol, int memory = 10);
+
 // LAPACK dppsv('U') equivalent on a packed upper, column-major SPD matrix; b is overwritten by the solution.
 // Returns 0, or j+1 when the leading minor of order j+1 is not positive definite.
 int packed_cholesky_solve(Vec& ap, Vec& b);
@@ -87,5 +91,12 @@ using LsqPassFn = std::function<void(const Vec& coef, const Vec& fstd, const Vec
 
 // LinearRegression.train, l-bfgs branch, after the summarizer pass.  Throws SolveError.
 LrModel lbfgs_path_fit(const ColumnStats& st, int d, const LrParams& p, const LsqPassFn& pass);
+
+// One evaluation of the huber objective on the data at params = [coefficients (d), intercept (if fitted), sigma]:
+// fills loss_sum, weight_sum and grad_sum (same layout as params; HuberAggregator's raw sums).
+using HuberPassFn = std::function<void(const Vec& params, const Vec& fstd, double& loss_sum, double& weight_sum, Vec& grad_sum)>;
+
+// LinearRegression.train with loss = huber, after the summarizer pass.  Throws SolveError.
+LrModel huber_path_fit(const ColumnStats& st, int d, const LrParams& p, const HuberPassFn& pass);
 
 }  // namespace dq4ml

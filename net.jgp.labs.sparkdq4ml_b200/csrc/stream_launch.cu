@@ -29,6 +29,8 @@ int stream_nacc(StreamOpKind op, int bucket) {
     case kOpSummCoreW: return 3 + 2 * bucket;
     case kOpLsqW: return 2 + bucket;
     case kOpWResid: return 3;
+    case kOpHuber: return 4 + bucket;
+    case kOpHuberW: return 4 + bucket;
   }
   return 0;
 }
@@ -81,7 +83,7 @@ cudaError_t launch_one(const Op& op, const PassArgs& a) {
   if (need > a.scratch.partials_bytes) return cudaErrorMemoryAllocation;
   kernel<<<static_cast<unsigned>(grid), kBlock, 0, a.stream>>>(op, a.cols, a.d, a.label, a.dq, a.n, a.dev_consts,
                                                                 a.row_out, a.scratch.partials, a.scratch.ticket,
-                                                                a.scratch.result);
+                                                                a.scratch.result, a.scratch.ep);
   return cudaGetLastError();
 }
 
@@ -107,6 +109,15 @@ L make_lsq(const LsqConsts& c) {
   for (int j = 0; j < DMAX; ++j) op.eff[j] = c.eff[j];
   op.offset = c.offset;
   op.inv_ystd = c.inv_ystd;
+  return op;
+}
+template <class H, int DMAX>
+H make_huber(const HuberConsts& c) {
+  H op;
+  for (int j = 0; j < DMAX; ++j) op.eff[j] = c.eff[j];
+  op.intercept = c.intercept;
+  op.sigma = c.sigma;
+  op.epsilon = c.epsilon;
   return op;
 }
 template <int DMAX>
@@ -139,6 +150,10 @@ cudaError_t launch_bucket_rows(StreamOpKind kind, const PassArgs& a, const void*
       return cudaErrorInvalidValue;
     case kOpWResid:
       if constexpr (DMAX == 2) return launch_mode2<WResidOp<DMAX>, DMAX, ROWS>(WResidOp<DMAX>{}, a);
+      return cudaErrorInvalidValue;
+    case kOpHuber: return launch_mode<HuberOp<DMAX>, DMAX, ROWS>(make_huber<HuberOp<DMAX>, DMAX>(*static_cast<const HuberConsts*>(host_consts)), a);
+    case kOpHuberW:
+      if constexpr (DMAX >= 2) return launch_mode2<HuberWOp<DMAX>, DMAX, ROWS>(make_huber<HuberWOp<DMAX>, DMAX>(*static_cast<const HuberConsts*>(host_consts)), a);
       return cudaErrorInvalidValue;
   }
   return cudaErrorInvalidValue;
@@ -176,7 +191,7 @@ cudaError_t launch_stream_pass(StreamOpKind op, const DeviceCols& cols, const do
   a.dq.t.min_guest = dq.params.min_guest;
   if (dq.guest == nullptr) {
     a.dq_mode = kDqNone;
-  } else if (op < kOpSummCoreW && cols.n > 0 && cols.dtype[0] == DQ4ML_I32 && cols.ptr[0] == dq.guest &&
+  } else if ((op < kOpSummCoreW || op == kOpHuber) && cols.n > 0 && cols.dtype[0] == DQ4ML_I32 && cols.ptr[0] == dq.guest &&
              label != nullptr && label == dq.price) {
     a.dq_mode = kDqLab;
   } else {

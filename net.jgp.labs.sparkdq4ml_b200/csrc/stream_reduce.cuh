@@ -10,6 +10,7 @@
 #pragma once
 
 #include "device_utils.cuh"
+#include "epilogue.cuh"
 
 namespace dq4ml {
 
@@ -101,7 +102,7 @@ __global__ void __launch_bounds__(kBlock, (DMAX * ROWS >= 64 ? 1 : (DMAX <= 2 ? 
     stream_reduce_kernel(const Op op, const ColTable cols, const int d, const double* __restrict__ label,
                          const DqArgs dq, const int64_t n, const double* __restrict__ dev_consts,
                          double* __restrict__ row_out, double* __restrict__ partials, unsigned int* __restrict__ ticket,
-                         double* __restrict__ result) {
+                         double* __restrict__ result, const XrEpilogue ep) {
   constexpr int NACC = Op::NACC;
   double acc[NACC];
 #pragma unroll
@@ -160,6 +161,7 @@ __global__ void __launch_bounds__(kBlock, (DMAX * ROWS >= 64 ? 1 : (DMAX <= 2 ? 
     if (threadIdx.x == 0) result[k] = v;
   }
   if (threadIdx.x == 0) *ticket = 0u;  // ready for the next launch on this stream
+  xr_publish(ep, result, NACC, dev_consts, [](int k) { return Op::kind(k); });
 }
 
 }  // namespace dq4ml

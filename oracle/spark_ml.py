@@ -69,9 +69,13 @@ def backtracking_line_search(ff, init, initfval, shrink_step, grow_step=2.1, c_a
             return prev_alpha
 
 
-def strong_wolfe_line_search(ff, init, max_zoom_iter=10, max_line_search_iter=10):
-    """breeze.optimize.StrongWolfeLineSearch.minimize (Nocedal & Wright p.58-60)."""
+def strong_wolfe_line_search(ff, init, max_zoom_iter=10, max_line_search_iter=10, bound=None):
+    """breeze.optimize.StrongWolfeLineSearch.minimize (Nocedal & Wright p.58-60); with `bound`, .minimizeWithBound
+    (the variant LBFGSB uses: the step never grows past the bound and is returned as soon as it is reached with
+    sufficient decrease)."""
     c1, c2 = 1e-4, 0.9
+    if bound is not None and not init <= bound:
+        raise ValueError("requirement failed: init value should <= bound")  # IllegalArgumentException in Breeze
 
     def phi(t):
         v, dd = ff(t)
@@ -125,7 +129,12 @@ def strong_wolfe_line_search(ff, init, max_zoom_iter=10, max_line_search_iter=10
             if c[1] >= 0:
                 return zoom(c, low)
             low = c
-            t *= 1.5
+            if bound is None:
+                t *= 1.5
+            elif t == bound:
+                return bound  # sufficient decrease at the bound, curvature condition not met
+            else:
+                t = min(t * 1.5, bound)
     raise FirstOrderException("Line search failed")
 
 
@@ -170,9 +179,16 @@ class LBFGS:
     def __init__(self, max_iter, m, tol):
         self.max_iter, self.m, self.tol = max_iter, m, tol
 
-    # -- hooks overridden by OWLQN
+    # -- hooks overridden by OWLQN / LBFGSB
     def adjust(self, x, grad, value):
         return value, grad
+
+    def initial_history(self, x):
+        return ([], [])
+
+    def update_history(self, state, x, grad):
+        mem_step, mem_gd = state.history
+        return (([x - state.x] + mem_step)[: self.m], ([grad - state.grad] + mem_gd)[: self.m])
 
     def take_step(self, state, direction, step):
         return state.x + direction * step
@@ -235,7 +251,7 @@ class LBFGS:
         x = init
         value, grad = f(x)
         adj_v, adj_g = self.adjust(x, grad, value)
-        state = State(x, value, grad, adj_v, adj_g, 0, adj_v, ([], []))
+        state = State(x, value, grad, adj_v, adj_g, 0, adj_v, self.initial_history(x))
         failed_once = False
         while True:
             yield state
@@ -248,8 +264,7 @@ class LBFGS:
                 x = self.take_step(state, direction, step)
                 value, grad = f(x)
                 adj_v, adj_g = self.adjust(x, grad, value)
-                mem_step, mem_gd = state.history
-                history = (([x - state.x] + mem_step)[: self.m], ([grad - state.grad] + mem_gd)[: self.m])
+                history = self.update_history(state, x, grad)
                 fvals = (state.fvals + [value])[-self.FVAL_MEMORY:]
                 failed_once = False
                 state = State(x, value, grad, adj_v, adj_g, state.iter + 1, state.initial_adj_val, history, fvals)
@@ -257,7 +272,8 @@ class LBFGS:
                 if not failed_once:
                     failed_once = True
                     state = State(state.x, state.value, state.grad, state.adjusted_value, state.adjusted_gradient,
-                                  state.iter, state.initial_adj_val, ([], []), state.fvals, state.search_failed)
+                                  state.iter, state.initial_adj_val, self.initial_history(state.x), state.fvals,
+                                  state.search_failed)
                 else:
                     state = State(state.x, state.value, state.grad, state.adjusted_value, state.adjusted_gradient,
                                   state.iter, state.initial_adj_val, state.history, state.fvals, True)
@@ -308,6 +324,163 @@ class OWLQN(LBFGS):
         shrink = 0.1 if it < 1 else 0.5
         init = 0.5 / float(np.linalg.norm(state.grad)) if it < 1 else 1.0
         return backtracking_line_search(ff, init, state.value, shrink)
+
+
+class LBFGSB(LBFGS):
+    """breeze.optimize.LBFGSB(lowerBounds, upperBounds, maxIter, m, tolerance, maxZoomIter = 64, maxLineSearchIter = 64):
+    Byrd, Lu, Nocedal & Zhu's L-BFGS-B as Breeze 0.13.2 states it -- generalized Cauchy point (algorithm CP), subspace
+    minimisation by the primal method, compact representation B = theta I - W M W^T with W = [Y, theta S], strong-Wolfe
+    line search capped at the largest feasible step.  LinearRegression uses it for loss = huber, where only the scale
+    sigma has a bound (sigma >= Double.MinPositiveValue).
+
+    One deliberate difference: the subspace step is shortened by Byrd et al.'s alpha* (largest alpha <= 1 that stays
+    inside the bounds).  Breeze 0.13.2's findAlpha, as this restatement recalls it, takes max(alpha, min(., 1)) starting
+    from alpha = 1 and therefore never shortens the step; an infeasible subspace minimum then makes the largest feasible
+    line-search step smaller than the initial step 1 and StrongWolfeLineSearch.minimizeWithBound fails its
+    `require(init <= bound)` -- the fit dies with an IllegalArgumentException.  Wherever Breeze's version succeeds
+    (alpha* = 1) the two are the same algorithm; alpha_cuts counts the steps where they are not."""
+
+    PROJ_GRADIENT_EPS = 1e-5
+    EPS = 2.2e-16
+
+    def __init__(self, lower, upper, max_iter, m, tol, max_zoom_iter=64, max_line_search_iter=64):
+        super().__init__(max_iter, m, tol)
+        self.lower = np.asarray(lower, dtype=np.float64)
+        self.upper = np.asarray(upper, dtype=np.float64)
+        self.max_zoom_iter, self.max_ls_iter = max_zoom_iter, max_line_search_iter
+        self.alpha_cuts = 0
+
+    # history = (theta, W, M, Y, S) with Y, S of shape (n, k), newest column last
+    def initial_history(self, x):
+        n = x.size
+        return (1.0, np.zeros((n, 1)), np.zeros((1, 1)), np.zeros((n, 0)), np.zeros((n, 0)))
+
+    def update_history(self, state, x, grad):
+        theta, w_mat, m_mat, y_hist, s_hist = state.history
+        new_s, new_y = x - state.x, grad - state.grad
+        if y_hist.shape[1] < self.m:
+            y_new = np.concatenate([y_hist, new_y[:, None]], axis=1)
+            s_new = np.concatenate([s_hist, new_s[:, None]], axis=1)
+        else:
+            y_new = np.concatenate([y_hist[:, 1:], new_y[:, None]], axis=1)
+            s_new = np.concatenate([s_hist[:, 1:], new_s[:, None]], axis=1)
+        curvature = abs(float(new_s @ new_y))
+        if self.EPS * float(new_y @ new_y) < curvature:
+            theta_new = float(new_y @ new_y) / float(new_y @ new_s)
+            w_new = np.concatenate([y_new, theta_new * s_new], axis=1)
+            a = s_new.T @ y_new
+            low = np.tril(a, -1)
+            dmat = -np.diag(np.diag(a))
+            mm = np.block([[dmat, low.T], [low, theta_new * (s_new.T @ s_new)]])
+            return (theta_new, w_new, np.linalg.inv(mm), y_new, s_new)
+        return (theta, w_mat, m_mat, y_hist, s_hist)
+
+    def _cauchy_point(self, history, x, g):
+        theta, w_mat, m_mat = history[0], history[1], history[2]
+        n = x.size
+        d = np.zeros(n)
+        t = np.full(n, np.finfo(np.float64).max)
+        for i in range(n):
+            gi = g[i]
+            if gi != 0.0:
+                ti = (x[i] - self.upper[i]) / gi if gi < 0 else (x[i] - self.lower[i]) / gi
+                d[i] = 0.0 if ti == 0.0 else -gi
+                t[i] = ti
+        x_cauchy = x.copy()
+        p = w_mat.T @ d
+        c = np.zeros(m_mat.shape[0])
+        f_deriv = float(g @ d)
+        f_second = -theta * f_deriv - float(p @ (m_mat @ p))
+        dt_min = -(f_deriv / f_second)
+        old_t = 0.0
+        order = sorted(range(n), key=lambda i: t[i])  # stable, like sortWith on equal keys? (ties are measure-zero here)
+        i = next((k for k, idx in enumerate(order) if t[idx] != 0.0), n)
+        if i < n:
+            b = order[i]
+            min_t = t[b]
+            delta_t = min_t - old_t
+            while delta_t <= dt_min and i < n:
+                x_cauchy[b] = self.upper[b] if d[b] > 0 else self.lower[b]
+                zb = x_cauchy[b] - x[b]
+                c = c + p * delta_t
+                wb = w_mat[b, :].copy()
+                f_deriv += delta_t * f_second + g[b] * g[b] + theta * g[b] * zb - g[b] * float(wb @ (m_mat @ c))
+                f_second += -theta * g[b] * g[b] - 2.0 * (g[b] * float(wb @ (m_mat @ p))) - g[b] * g[b] * float(wb @ (m_mat @ wb))
+                p = p + wb * g[b]
+                d[b] = 0.0
+                dt_min = -f_deriv / f_second
+                old_t = min_t
+                i += 1
+                if i < n:
+                    b = order[i]
+                    min_t = t[b]
+                    delta_t = min_t - old_t
+        dt_min = max(dt_min, 0.0)
+        old_t += dt_min
+        for k in range(i, n):
+            idx = order[k]
+            x_cauchy[idx] = x[idx] + old_t * d[idx]
+        c = c + p * dt_min
+        return x_cauchy, c
+
+    def _subspace_min(self, history, x_cauchy, x, c, g):
+        theta, w_mat, m_mat = history[0], history[1], history[2]
+        inv_theta = 1.0 / theta
+        free = [i for i in range(x.size) if x_cauchy[i] != self.upper[i] and x_cauchy[i] != self.lower[i]]
+        wz = w_mat[free, :].T  # (2k, free)
+        full_r = g + (x_cauchy - x) * theta - w_mat @ (m_mat @ c)
+        rc = full_r[free]
+        v = m_mat @ (wz @ rc)
+        n_mat = np.eye(wz.shape[0]) - m_mat @ ((wz @ wz.T) * inv_theta)
+        v = np.linalg.solve(n_mat, v)
+        wzv = (wz.T @ v) * (inv_theta * inv_theta)
+        du = -(rc * inv_theta + wzv)
+        # findAlpha, as Byrd et al. define it: the largest alpha <= 1 that keeps x_cauchy + alpha du inside the bounds
+        alpha_star = 1.0
+        with np.errstate(over="ignore"):  # overflow to inf against the +-Double.MaxValue bounds is harmless under min
+            for k, idx in enumerate(free):
+                if du[k] > 0:
+                    alpha_star = min(alpha_star, (self.upper[idx] - x_cauchy[idx]) / du[k])
+                elif du[k] < 0:
+                    alpha_star = min(alpha_star, (self.lower[idx] - x_cauchy[idx]) / du[k])
+        self.alpha_cuts += int(alpha_star < 1.0)
+        out = x_cauchy.copy()
+        for k, idx in enumerate(free):
+            out[idx] += alpha_star * du[k]
+        return out
+
+    def choose_descent_direction(self, state, grad=None):
+        x, g = state.x, state.grad
+        with np.errstate(over="ignore"):  # (x - Double.MaxValue) / g overflows to +-inf, as it does on the JVM
+            x_cauchy, c = self._cauchy_point(state.history, x, g)
+        if state.iter == 0:
+            return x_cauchy - x
+        return self._subspace_min(state.history, x_cauchy, x, c, g) - x
+
+    def take_step(self, state, direction, step):
+        return np.minimum(np.maximum(state.x + direction * step, self.lower), self.upper)
+
+    def determine_step_size(self, state, f, direction):
+        def ff(alpha):
+            v, g = f(self.take_step(state, direction, alpha))
+            return v, float(g @ direction)
+
+        min_bound = float("inf")
+        with np.errstate(over="ignore"):
+            for i in range(direction.size):
+                di = direction[i]
+                if di != 0.0:
+                    bnd = self.lower[i] if di < 0.0 else self.upper[i]
+                    step_bound = (bnd - state.x[i]) / di
+                    assert step_bound >= 0.0
+                    min_bound = min(min_bound, step_bound)
+        return strong_wolfe_line_search(ff, 1.0, self.max_zoom_iter, self.max_ls_iter, bound=min_bound)
+
+    def _converged(self, s):
+        proj = np.minimum(np.maximum(s.x - s.grad, self.lower), self.upper) - s.x
+        if abs(float(np.max(np.abs(proj)))) < self.PROJ_GRADIENT_EPS:
+            return "ProjectedStepConverged"
+        return super()._converged(s)
 
 
 def run_optimizer(opt, cost_fun, x0):
@@ -417,6 +590,8 @@ class LRParams:
     fit_intercept: bool = True
     standardization: bool = True
     solver: str = "auto"  # auto | normal | l-bfgs
+    loss: str = "squaredError"  # squaredError | huber
+    epsilon: float = 1.35
 
 
 @dataclass
@@ -427,6 +602,7 @@ class LRModel:
     total_iterations: int
     solver_used: str
     data_passes: int = 0
+    scale: float = 1.0  # LinearRegressionModel.scale: the huber loss's sigma (1.0 for squaredError)
 
 
 def wls_fit_from_moments(mom, d, p: LRParams, solver_type="auto"):
@@ -654,9 +830,101 @@ def lbfgs_path_fit(features, label, p: LRParams, dq=None, threads=1, weight=None
     return LRModel(raw, float(intercept), list(hist), len(hist), used, n_pass + n_eval)
 
 
+def huber_loss_grad(x, y, w, params, fstd, fit_intercept, epsilon):
+    """ml.optim.aggregator.HuberAggregator.add over every row with w != 0: returns (lossSum, weightSum, gradientSum)
+    with gradientSum laid out like the parameters [coefficients (d), intercept (if fitted), sigma].  The label is NOT
+    standardised; features enter as value / featuresStd (columns with std 0 are skipped)."""
+    d = x.shape[1]
+    params = np.asarray(params, dtype=np.float64)
+    sigma = params[-1]
+    intercept = params[d] if fit_intercept else 0.0
+    on = w != 0.0
+    x, y, w = x[on], y[on], w[on]
+    ok = fstd != 0.0
+    xs = np.where(ok, x / np.where(ok, fstd, 1.0), 0.0)
+    margin = xs @ params[:d] + intercept
+    lin = y - margin
+    inner = np.abs(lin) <= sigma * epsilon
+    with np.errstate(over="ignore", invalid="ignore"):  # a line-search trial may put sigma next to its lower bound
+        lds = lin / sigma
+        lds2 = lin * lin / sigma
+    loss = np.where(inner, 0.5 * w * (sigma + lds2),
+                    0.5 * w * (sigma + 2.0 * epsilon * np.abs(lin) - sigma * epsilon * epsilon))
+    sign = np.where(lin >= 0, -1.0, 1.0)
+    factor = np.where(inner, -1.0 * w * lds, w * sign * epsilon)  # multiplies value / std (and 1 for the intercept)
+    grad = np.zeros(params.size)
+    grad[:d] = (factor[:, None] * xs).sum(axis=0)
+    if fit_intercept:
+        grad[d] = factor.sum()
+    grad[-1] = np.where(inner, 0.5 * w * (1.0 - lds * lds), 0.5 * w * (1.0 - epsilon * epsilon)).sum()
+    return float(loss.sum()), float(w.sum()), grad
+
+
+def huber_path_fit(features, label, p: LRParams, dq=None, threads=1, weight=None):
+    """LinearRegression.train with loss = huber (Spark 2.3+): summarizer for the feature scales, HuberAggregator per
+    evaluation, L2 regularisation only (regParam NOT divided by yStd), Breeze LBFGSB with sigma > 0, start at all ones."""
+    d = len(features)
+    if p.elastic_net_param != 0.0:
+        raise ValueError("requirement failed: LinearRegression with huber loss only supports L2 regularization")
+    if p.solver == "normal":
+        raise ValueError("requirement failed: LinearRegression with huber loss doesn't support normal solver")
+    if not p.epsilon > 1.0:
+        raise ValueError("epsilon must be > 1.0")
+    if weight is None:
+        summ = passes.summarizer(features, label, dq=dq, threads=threads)
+    else:
+        summ = summarizer_weighted(features, label, weight, dq=dq)
+    y_mean = float(summ["mean"][d])
+    raw_y_std = math.sqrt(float(summ["variance"][d]))
+    if raw_y_std == 0.0:
+        if p.fit_intercept or y_mean == 0.0:
+            return LRModel(np.zeros(d), y_mean, [0.0], 1, "trivial", 1)
+        if p.reg_param != 0.0:
+            raise ValueError("The standard deviation of the label is zero. Model cannot be regularized.")
+    f_std = np.sqrt(summ["variance"][:d])
+    eff_l2 = p.reg_param  # (1 - elasticNetParam) * regParam with elasticNetParam == 0
+    y = np.asarray(label, dtype=np.float64)
+    w_all = np.ones(y.size) if weight is None else np.asarray(weight, dtype=np.float64)
+    x, yk, wk = _weighted_table(features, label, w_all, dq)
+    dim = d + 2 if p.fit_intercept else d + 1
+
+    def cost(c):
+        loss_sum, w_sum, grad_sum = huber_loss_grad(x, yk, wk, c, f_std, p.fit_intercept, p.epsilon)
+        loss = loss_sum / w_sum
+        grad = grad_sum / w_sum
+        if eff_l2 != 0.0:
+            ssum = 0.0
+            for j in range(d):
+                if p.standardization:
+                    ssum += c[j] * c[j]
+                    grad[j] += eff_l2 * c[j]
+                elif f_std[j] != 0.0:
+                    temp = c[j] / (f_std[j] * f_std[j])
+                    ssum += c[j] * temp
+                    grad[j] += eff_l2 * temp
+            loss += 0.5 * ssum * eff_l2
+        return loss, grad
+
+    lower = np.full(dim, -np.finfo(np.float64).max)
+    lower[dim - 1] = 5e-324  # Double.MinPositiveValue
+    upper = np.full(dim, np.finfo(np.float64).max)
+    opt = LBFGSB(lower, upper, p.max_iter, 10, p.tol)
+    state, hist, n_eval = run_optimizer(opt, cost, np.ones(dim))
+    par = state.x.copy()
+    raw = par[:d].copy()
+    for j in range(d):
+        raw[j] *= (1.0 / f_std[j]) if f_std[j] != 0.0 else 0.0
+    intercept = float(par[d]) if p.fit_intercept else 0.0
+    model = LRModel(raw, intercept, list(hist), len(hist), "lbfgsb", 1 + n_eval, scale=float(par[-1]))
+    model.alpha_cuts = opt.alpha_cuts  # steps on which Breeze 0.13.2 (as recalled) would have thrown instead
+    return model
+
+
 def linear_regression_fit(features, label, p: LRParams, dq=None, threads=1, weight=None):
     """ml.regression.LinearRegression.train: solver selection (auto & d <= 4096 -> WLS, else l-bfgs)."""
     d = len(features)
+    if p.loss == "huber":
+        return huber_path_fit(features, label, p, dq=dq, threads=threads, weight=weight)
     if (p.solver == "auto" and d <= 4096) or p.solver == "normal":
         if weight is None:
             mom = passes.wls_moments(features, label, dq=dq, threads=threads)

@@ -60,10 +60,11 @@ def test_noalloc_filter_matches_regular_filter_on_two_calls_in_a_row(pkg, ctx):
 def test_noalloc_filter_edge_sizes_and_limit(pkg, ctx):
     L = pkg.capi.lib()
     torch.cuda.set_device(0)
-    # around the 4096-row tile boundary, and one input whose look-back has to walk over more than 256 tiles
-    for n in (0, 1, 2047, 2048, 2049, 4095, 4096, 4097, 4096 * 257 + 1):
+    # around the tile boundaries of both kernels (2048 and 4096 rows), and inputs of several hundred tiles
+    for n in (0, 1, 2047, 2048, 2049, 4095, 4096, 4097, 4096 * 257 + 1, 2048 * 1031 + 5):
         guest = torch.arange(n, dtype=torch.int32, device="cuda") % 36
         price = (torch.arange(n, dtype=torch.float64, device="cuda") * 7.5) % 160.0
+        torch.cuda.synchronize()  # the ctx stream is non-blocking: it does not wait for torch's stream to fill the inputs
         ref_g, ref_p, ref_n1 = _call_regular(pkg, ctx, guest, price)
         rc, go, po, m, n1 = _call_noalloc(L, guest, price)
         assert rc == 0 and (m, n1) == (ref_g.shape[0], ref_n1)
@@ -80,7 +81,7 @@ def test_noalloc_filter_edge_sizes_and_limit(pkg, ctx):
 
 @pytest.mark.parametrize("n", [MAX_ROWS, MAX_ROWS - 4095])
 def test_noalloc_filter_at_the_row_limit(pkg, ctx, n):
-    """The largest accepted input uses the last look-back word of the built-in array (n = 2^26 is exactly 16384 tiles);
+    """The largest accepted input uses the last look-back word of the built-in array (n = 2^26 is exactly 32768 tiles of 2048 rows);
     2^26 - 4095 ends on a tile holding a single row."""
     L = pkg.capi.lib()
     torch.cuda.set_device(0)
