@@ -277,7 +277,9 @@ int dq4ml_linreg_fit(dq4ml_ctx* ctx, const dq4ml_columns* features, const double
  * App:111-126 leaves it at Spark's default; SURVEY.md 8f lists it as the next parameter).  weight: f64[n], host or
  * device, every value >= 0 (Spark: require(w >= 0.0)); NULL = dq4ml_linreg_fit.  Normal-equation branch: the Gram
  * kernel scales each row by sqrt(w) (any width).  l-bfgs branch: weighted summarizer (zero-weight rows are not counted,
- * variance denominator wSum - sum(w^2)/wSum) and weighted LeastSquaresAggregator, at most 31 feature columns. */
+ * variance denominator wSum - sum(w^2)/wSum) and weighted LeastSquaresAggregator; up to 31 feature columns the weight
+ * rides as one more column of the streaming pass, wider tables take the grouped summarizer and the two-pass
+ * loss/gradient (per-row weighted difference, then column groups). */
 int dq4ml_linreg_fit_weighted(dq4ml_ctx* ctx, const dq4ml_columns* features, const double* label, const double* weight,
                               int64_t n, const dq4ml_lr_params* params, const dq4ml_dq_fused* dq, dq4ml_lr_model** out);
 

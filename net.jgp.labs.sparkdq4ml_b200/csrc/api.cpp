@@ -518,28 +518,42 @@ int summarizer_pass(dq4ml_ctx* ctx, StreamOpKind op, const DeviceCols& cols, con
 }
 
 // Weighted summarizer for the l-bfgs branch: count (rows with w != 0), weighted mean and the unbiased weighted variance
-// MultivariateOnlineSummarizer.variance returns, sum(w (v - mean)^2) / (W - sum(w^2) / W).
+// MultivariateOnlineSummarizer.variance returns, sum(w (v - mean)^2) / (W - sum(w^2) / W).  The weight rides as column 0
+// of the streamed table, so wide tables go through in groups of kMaxCols - 1 feature columns (the label with the first).
 int summarize_core_weighted(dq4ml_ctx* ctx, const PassInputs& in, int64_t n, ColumnStats* st) {
-  int rc = weighted_width_check(in);
-  if (rc != DQ4ML_OK) return rc;
   const int d = in.width();
   st->mean.assign(d + 1, 0.0);
   st->variance.assign(d + 1, 0.0);
-  const int b = stream_bucket(d + 1);
-  int world = 1, len = 0;
-  rc = summarizer_pass(ctx, kOpSummCoreW, in.wcols, in.label, in.dq, n, b, b + 1, true, &world, &len);
-  if (rc != DQ4ML_OK) return rc;
-  const int nacc = stream_nacc(kOpSummCoreW, b);
   double count = 0.0, w_sum = 0.0, ww_sum = 0.0;
   std::vector<Moments> mom(d + 1);
-  for (int r = 0; r < world; ++r) {
-    const double* v = ctx->h_result + static_cast<size_t>(r) * len;
-    const double* c = v + nacc;  // centres: slot j of the table (slot 0 is the weight itself), the label at slot b
-    count += v[0];
-    w_sum += v[1];
-    ww_sum += v[2];
-    for (int j = 0; j < d; ++j) mom[j].merge(v[1], c[1 + j], v[1 + 2 * (1 + j)], v[2 + 2 * (1 + j)]);
-    mom[d].merge(v[1], c[b], v[1 + 2 * b], v[2 + 2 * b]);
+  constexpr int kGroup = kMaxCols - 1;
+  for (int c0 = 0; c0 == 0 || c0 < d; c0 += kGroup) {
+    DeviceCols g;
+    const int gd = std::min(kGroup, d - c0);
+    g.n = gd + 1;
+    g.ptr[0] = in.weight;
+    g.dtype[0] = DQ4ML_F64;
+    for (int j = 0; j < gd; ++j) {
+      g.ptr[1 + j] = in.ptr[c0 + j];
+      g.dtype[1 + j] = in.dtype[c0 + j];
+    }
+    const bool with_label = c0 == 0;
+    const int b = stream_bucket(g.n);
+    int world = 1, len = 0;
+    const int rc = summarizer_pass(ctx, kOpSummCoreW, g, with_label ? in.label : nullptr, in.dq, n, b, b + 1, true, &world, &len);
+    if (rc != DQ4ML_OK) return rc;
+    const int nacc = stream_nacc(kOpSummCoreW, b);
+    for (int r = 0; r < world; ++r) {
+      const double* v = ctx->h_result + static_cast<size_t>(r) * len;
+      const double* c = v + nacc;  // centres: slot j of the table (slot 0 is the weight itself), the label at slot b
+      if (with_label) {
+        count += v[0];
+        w_sum += v[1];
+        ww_sum += v[2];
+        mom[d].merge(v[1], c[b], v[1 + 2 * b], v[2 + 2 * b]);
+      }
+      for (int j = 0; j < gd; ++j) mom[c0 + j].merge(v[1], c[1 + j], v[1 + 2 * (1 + j)], v[2 + 2 * (1 + j)]);
+    }
   }
   if (!(w_sum == w_sum) || w_sum < 0.0) {
     set_error("instance weight must be >= 0 and not NaN");
@@ -613,9 +627,8 @@ int lsq_pass(dq4ml_ctx* ctx, const PassInputs& in, int64_t n, const double* coef
              const double* fmean, double ystd, double ymean, bool fit_intercept, double* loss_sum, double* weight_sum,
              double* grad_sum, double* diff_scratch = nullptr) {
   const int d = in.width();
-  if (in.weight != nullptr) {  // weight in column 0, features in 1..d
-    int rc = weighted_width_check(in);
-    if (rc != DQ4ML_OK) return rc;
+  if (in.weight != nullptr && in.wcols.n > 0) {  // weight in column 0, features in 1..d (d <= kMaxCols - 1)
+    int rc = DQ4ML_OK;
     const int b = stream_bucket(d + 1);
     LsqConsts c{};
     double s = 0.0;
@@ -635,9 +648,10 @@ int lsq_pass(dq4ml_ctx* ctx, const PassInputs& in, int64_t n, const double* coef
     for (int j = 0; j < d; ++j) grad_sum[j] = fstd[j] != 0.0 ? r[3 + j] / fstd[j] : 0.0;
     return DQ4ML_OK;
   }
-  if (d > kMaxCols) {
-    // Wide table: pass 1 writes the scaled difference r = y/yStd - (x.eff + offset) per row (and its sums), pass 2 takes
-    // gradSum_j = -sum r x_j over column groups.  The table is read twice; Spark reads it once, but keeps it in host RAM.
+  if (d > kMaxCols || in.weight != nullptr) {
+    // Wide table (or a weighted one too wide for the weight to ride as column 0): pass 1 writes the scaled difference
+    // r = y/yStd - (x.eff + offset) per row -- times the instance weight when there is one -- and its sums, pass 2 takes
+    // gradSum_j = -sum (w) r x_j over column groups.  The table is read twice; Spark reads it once, but keeps it in host RAM.
     if (diff_scratch == nullptr) {
       set_error("internal: no scratch column for the wide loss/gradient pass");
       return DQ4ML_ERR_INVALID;
@@ -650,7 +664,8 @@ int lsq_pass(dq4ml_ctx* ctx, const PassInputs& in, int64_t n, const double* coef
     }
     const double offset = fit_intercept ? ymean / ystd - s : 0.0;
     WideSums ws;
-    int rc = wide_rows_pass(ctx, in.ptr, in.dtype, eff.data(), offset, 1.0 / ystd, in.label, in.dq, n, 1, diff_scratch, false, &ws);
+    int rc = wide_rows_pass(ctx, in.ptr, in.dtype, eff.data(), offset, 1.0 / ystd, in.label, in.dq, n, 1, diff_scratch, false, &ws,
+                            in.weight);
     if (rc != DQ4ML_OK) return rc;
     std::vector<double> all(2 + d, 0.0);
     all[0] = 0.5 * ws.ss_res;
@@ -1366,7 +1381,9 @@ int dq4ml_linreg_fit_weighted(dq4ml_ctx* ctx, const dq4ml_columns* features, con
   const bool huber = p.loss == DQ4ML_LOSS_HUBER;  // always the summarizer + aggregator branch
   const bool wls = !huber && (p.solver == DQ4ML_SOLVER_NORMAL || (p.solver == DQ4ML_SOLVER_AUTO && d <= 4096));
   PassInputs in;
-  const bool wide_lbfgs = !wls && d > kMaxCols;  // needs one scratch column for the per-row scaled difference
+  // tables too wide for one streaming launch (with the weight as an extra column, if any) need one scratch column for
+  // the per-row scaled difference
+  const bool wide_lbfgs = !wls && !huber && d + (weight != nullptr ? 1 : 0) > kMaxCols;
   int rc = gather_inputs(ctx, features, label, n, dq, &in, wide_lbfgs ? static_cast<size_t>(n) * 8 : 0, 1 << 20, weight);
   if (rc != DQ4ML_OK) return rc;
   double* diff = wide_lbfgs ? static_cast<double*>(arena_take(ctx, static_cast<size_t>(n) * 8)) : nullptr;

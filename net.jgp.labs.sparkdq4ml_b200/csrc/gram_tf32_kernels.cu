@@ -50,9 +50,12 @@
 // count, not the conversion pipe); three operand buffers with three staging stages (same time); draining the CTAs at
 // different chunks instead of all at once (same time: the drain is not an L2 burst problem).  Next: two chunks per row-warp iteration, a TMA tensor-map load path
 // for uniformly strided tables (no per-thread load issue), 32-row chunks once the raw staging is gone.
+#include <cuda.h>  // CUtensorMap and its enums only: the encoder is looked up at run time, libcuda is not linked
+
 #include <algorithm>
 #include <cstdio>
 #include <cstdlib>
+#include <cstring>
 #include <vector>
 
 #include "context.hpp"
@@ -69,7 +72,7 @@ constexpr int TROWST = 16;                  // stages of the row warp's own ring
 constexpr int TCONV = 512;                  // loader / converter threads: TCONV / TF per feature slot (256: 53 ms against 48.5)
 constexpr int TFPW = 32 * TF / TCONV;       // features per converter warp
 constexpr int TRPT = TKC * TF / TCONV;      // rows of a chunk per converter thread
-constexpr int TTHREADS = TCONV + 64;        // + the MMA warp + the row warp
+constexpr int TTHREADS = TCONV + 64;        // + the MMA warp + the row warp (the TMA variant adds a producer warp)
 constexpr int TOPS = 2;                     // operand stages (hi/lo tf32)
 constexpr int TSCALE = 8;                   // row-factor buffers: how far the row warp may run ahead of the converters
 constexpr int TSTRIDE = TKC * 8 + 16;       // bytes per feature in a staging stage: +16 keeps 128-bit reads conflict-free
@@ -82,8 +85,15 @@ constexpr int kStagingOff = 0;
 constexpr int kOpsOff = kStagingOff + TSTAGES * TF * TSTRIDE;
 constexpr int kRowsOff = kOpsOff + TOPS * 2 * TOPB;
 constexpr int kScaleOff = kRowsOff + TROWST * TROWB;
-constexpr int kBarOff = kScaleOff + TSCALE * TSCB;  // 10 mbarriers + the TMEM base address
-constexpr int kTf32Smem = kBarOff + 8 * (2 * TOPS + 2 * TSCALE + 2);
+constexpr int kBarOff = kScaleOff + TSCALE * TSCB;  // mbarriers + the TMEM base address
+constexpr int kNumBars = 2 * TOPS + 2 * TSCALE + 1 + 2 * TSTAGES;  // free/ready, scale/sfree, drain, TMA full/empty
+constexpr int kTf32Smem = kBarOff + 8 * (kNumBars + 1) + 1024;      // + slack to align the staging ring to 1024 bytes
+// TMA staging (uniformly strided fp64 columns): one 2-D box of TKC rows x TF columns per stage, 128-byte swizzle.  It
+// reuses the staging region: TSTAGES boxes of 32 KB, then the pieces of the (at most TFPW) columns that are not part of
+// the strided table -- the lab's int32 guest column in front of the fp64 features -- in the cp.async layout.
+constexpr int kTmaBoxBytes = TF * TKC * 8;                 // 32 768
+constexpr int kTmaExtraOff = TSTAGES * kTmaBoxBytes;       // [TSTAGES][TFPW * TSTRIDE]
+static_assert(kTmaExtraOff + TSTAGES * TFPW * TSTRIDE <= TSTAGES * TF * TSTRIDE, "TMA staging must fit the staging region");
 // TMEM accumulator columns: [0, 256) = features 0..127 x features 0..255, [256, 384) = features 128..255 x features 128..255
 constexpr int kColC = 256;
 constexpr int SCOLS = 384;                  // fp64 tile columns per CTA (12 groups of 32), stored column-major
@@ -109,6 +119,7 @@ struct Tf32Args {
   int swap_offsets;  // debug: exchange LBO and SBO in the descriptors
   int experiment;    // ablation: bit 0 = converters skip the conversion, bit 1 = no MMAs are issued, bit 2 = no column loads, bit 3 = timers (profile build)
   double* partials;  // [grid][kCtaDoubles], zeroed by the launcher
+  int tma_first;     // TMA variant: feature slots [tma_first, d) are columns 0.. of the tensor map; slots below it use cp.async
 };
 
 __device__ __forceinline__ unsigned s_u32(const void* p) { return static_cast<unsigned>(__cvta_generic_to_shared(p)); }
@@ -135,6 +146,15 @@ __device__ __forceinline__ void mbar_wait(unsigned bar, unsigned parity) {
         : "memory");
     if (spin > (1u << 24)) __trap();  // a lost completion must not hang the GPU
   }
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(unsigned bar, unsigned bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+// One TMA tile load: box (TKC rows, TF columns) of the column table at (row, col 0) -> shared memory, completion on `bar`.
+// The tensor map covers this GPU's own buffers only.
+__device__ __forceinline__ void tma_load_2d(unsigned dst, const CUtensorMap* tmap, int c0, int c1, unsigned bar) {
+  asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+               ::"r"(dst), "l"(reinterpret_cast<unsigned long long>(tmap)), "r"(c0), "r"(c1), "r"(bar) : "memory");
 }
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
@@ -235,13 +255,18 @@ __device__ __forceinline__ bool drain_needed(int cg, int quad) {
   return cg - 8 >= quad;
 }
 
-__global__ void __launch_bounds__(TTHREADS, 1) gram_tf32_kernel(const Tf32Args g) {
+template <bool TMA>
+__global__ void __launch_bounds__(TTHREADS + (TMA ? 32 : 0), 1)
+    gram_tf32_kernel(const Tf32Args g, const __grid_constant__ CUtensorMap tmap) {
 #ifdef DQ4ML_TF32_PROFILE
   const bool prof = (g.experiment & 8) != 0 && blockIdx.x == 0 && (threadIdx.x & 31) == 0;
   long long tacc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
   long long tlast = clock64();
 #endif
-  extern __shared__ __align__(128) unsigned char smem[];
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  // the 128-byte swizzle of the TMA boxes is a function of the shared-memory address: the ring starts on a 1024-byte line
+  unsigned char* smem = smem_raw + ((1024u - (s_u32(smem_raw) & 1023u)) & 1023u);
+  constexpr int kThreads = TTHREADS + (TMA ? 32 : 0);
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const unsigned sbase = s_u32(smem);
   const unsigned bar_free0 = sbase + kBarOff;      // [TOPS] operand buffer o may be overwritten: arrived by tcgen05.commit
@@ -249,11 +274,13 @@ __global__ void __launch_bounds__(TTHREADS, 1) gram_tf32_kernel(const Tf32Args g
   const unsigned bar_scale0 = bar_ready0 + 8 * TOPS;      // [TSCALE] row factors of a chunk are written: the row warp
   const unsigned bar_sfree0 = bar_scale0 + 8 * TSCALE;    // [TSCALE] row factors of a chunk have been used: one arrival per converter warp
   const unsigned bar_drain = bar_sfree0 + 8 * TSCALE;     // every MMA issued so far has completed
-  unsigned* tmem_slot = reinterpret_cast<unsigned*>(smem + kBarOff + 8 * (2 * TOPS + 2 * TSCALE + 1));
+  const unsigned bar_full0 = bar_drain + 8;               // [TSTAGES] TMA box of stage s has landed (TMA variant)
+  const unsigned bar_empty0 = bar_full0 + 8 * TSTAGES;    // [TSTAGES] every converter warp has read stage s
+  unsigned* tmem_slot = reinterpret_cast<unsigned*>(smem + kBarOff + 8 * kNumBars);
   const int nb = g.d > 128 ? 2 : 1;
 
   // operand buffers start as zeros: feature slots >= d are never written again
-  for (int i = tid; i < TOPS * 2 * TOPB / 16; i += TTHREADS) reinterpret_cast<int4*>(smem + kOpsOff)[i] = make_int4(0, 0, 0, 0);
+  for (int i = tid; i < TOPS * 2 * TOPB / 16; i += kThreads) reinterpret_cast<int4*>(smem + kOpsOff)[i] = make_int4(0, 0, 0, 0);
   if (tid == 0) {
     for (int o = 0; o < TOPS; ++o) {
       mbar_init(bar_free0 + 8 * o, 1);
@@ -264,6 +291,10 @@ __global__ void __launch_bounds__(TTHREADS, 1) gram_tf32_kernel(const Tf32Args g
       mbar_init(bar_sfree0 + 8 * b, TCONV / 32);
     }
     mbar_init(bar_drain, 1);
+    for (int st = 0; st < TSTAGES; ++st) {
+      mbar_init(bar_full0 + 8 * st, 1);
+      mbar_init(bar_empty0 + 8 * st, TCONV / 32);
+    }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 0) {  // all 512 TMEM columns: this kernel is alone on its SM (shared memory sees to that)
@@ -401,6 +432,20 @@ __global__ void __launch_bounds__(TTHREADS, 1) gram_tf32_kernel(const Tf32Args g
 #ifdef DQ4ML_TF32_PROFILE
     if (prof) printf("row warp: loop %lld loads %lld compute+wait_sfree %lld write+arrive %lld\n", tacc[0], tacc[1], tacc[2], tacc[3]);
 #endif
+  } else if (TMA && warp == TCONV / 32 + 2) {
+    // ================================================= TMA producer warp ===============================================
+    // One thread keeps TSTAGES boxes of the strided fp64 table in flight: 16 rows x 256 columns = 32 KB per request,
+    // no per-thread load issue in the converter warps.  Rows past the end of the table are zero-filled by the TMA unit.
+    if (lane == 0) {
+      for (unsigned it = 0; it < my_iters; ++it) {
+        const int st = static_cast<int>(it % TSTAGES);
+        if (it >= TSTAGES) mbar_wait(bar_empty0 + 8 * st, static_cast<unsigned>(((it / TSTAGES) - 1) & 1));
+        const long long row = (blockIdx.x + it * static_cast<long long>(gridDim.x)) * TKC;
+        mbar_arrive_expect_tx(bar_full0 + 8 * st, kTmaBoxBytes);
+        if (!(g.experiment & 4)) tma_load_2d(sbase + kStagingOff + st * kTmaBoxBytes, &tmap, static_cast<int>(row), 0, bar_full0 + 8 * st);
+        else asm volatile("mbarrier.complete_tx.shared::cta.b64 [%0], %1;" ::"r"(bar_full0 + 8 * st), "r"(static_cast<unsigned>(kTmaBoxBytes)) : "memory");
+      }
+    }
   } else {
     // ================================================= loader / converter warps ========================================
     // converter: two threads per feature, 8 rows of every chunk each (lanes 0..15 / 16..31 of a warp share 16 features)
@@ -421,10 +466,13 @@ __global__ void __launch_bounds__(TTHREADS, 1) gram_tf32_kernel(const Tf32Args g
       const char* base = on ? static_cast<const char*>(g.col_ptr[slot]) : nullptr;
       const bool is_int = on && g.col_i32[slot] != 0;
       src[i] = base != nullptr ? base + ch * 16 : nullptr;
-      if (base != nullptr && (!is_int || ch < 4)) live |= 1u << i;
+      if (base != nullptr && (!is_int || ch < 4) && (!TMA || slot < g.tma_first)) live |= 1u << i;  // TMA: the table's columns come as boxes
       if (is_int) ints |= 1u << i;
     }
     const unsigned piece_dst = static_cast<unsigned>(slot0 * TSTRIDE + ch * 16);
+    // where the cp.async pieces of stage st start: the whole staging stage, or (TMA) the small region behind the boxes
+    auto piece_stage = [&](int st) { return TMA ? kTmaExtraOff + st * (TFPW * TSTRIDE) : kStagingOff + st * (TF * TSTRIDE); };
+    const bool by_tma = TMA && feat >= g.tma_first;  // this thread's feature arrives in the TMA box, row feat - tma_first
 
     auto issue_stage = [&](unsigned it) {
       const long long chunk = blockIdx.x + it * static_cast<long long>(gridDim.x);
@@ -432,8 +480,8 @@ __global__ void __launch_bounds__(TTHREADS, 1) gram_tf32_kernel(const Tf32Args g
       const int st = static_cast<int>(it % TSTAGES);
       if (chunk >= full_chunks) {  // the ragged last chunk: guarded plain loads, same raw formats
         const int valid = static_cast<int>(g.n - row);
-        if (half == 0 && active) {  // lanes 0..15 fill the rows of the warp's own 16 features
-          unsigned char* dst = smem + kStagingOff + st * (TF * TSTRIDE) + feat * TSTRIDE;
+        if (half == 0 && active && !by_tma) {  // lanes 0..15 fill the rows of the warp's own 16 features
+          unsigned char* dst = smem + piece_stage(st) + feat * TSTRIDE;
           for (int k = 0; k < TKC; ++k) {
             if (own_int) reinterpret_cast<int*>(dst)[k] = k < valid ? static_cast<const int*>(g.col_ptr[feat])[row + k] : 0;
             else reinterpret_cast<double*>(dst)[k] = k < valid ? static_cast<const double*>(g.col_ptr[feat])[row + k] : 0.0;
@@ -441,7 +489,7 @@ __global__ void __launch_bounds__(TTHREADS, 1) gram_tf32_kernel(const Tf32Args g
         }
         return;
       }
-      const unsigned stg = sbase + kStagingOff + st * (TF * TSTRIDE) + piece_dst;
+      const unsigned stg = sbase + piece_stage(st) + piece_dst;
 #pragma unroll
       for (int i = 0; i < TFPW / 4; ++i) {
         if (((live >> i) & 1u) && !(g.experiment & 4)) cpa16(stg + 4 * i * TSTRIDE, src[i] + (((ints >> i) & 1u) ? row * 4 : row * 8));
@@ -478,7 +526,9 @@ __global__ void __launch_bounds__(TTHREADS, 1) gram_tf32_kernel(const Tf32Args g
     double zz = 0.0, a1 = 0.0, ab = 0.0;
     int since_drain = 0;
     unsigned drains = 0;
-    const unsigned char* sp0 = smem + kStagingOff + feat * TSTRIDE + half * (own_int ? TRPT * 4 : TRPT * 8);
+    const unsigned char* sp0 = smem + feat * TSTRIDE + half * (own_int ? TRPT * 4 : TRPT * 8);  // + piece_stage(st)
+    // TMA box, 128-byte swizzle: row r = one feature's 16 values, its 16-byte piece c sits at r * 128 + ((c ^ (r & 7)) << 4)
+    const int tma_row = feat - g.tma_first;
     unsigned char* op0 = smem + kOpsOff + (feat >> 3) * TSBO + (feat & 7) * 16 + half * (TRPT / 4) * TLBO;
 
     for (unsigned it = 0; it < my_iters; ++it) {
@@ -492,13 +542,15 @@ __global__ void __launch_bounds__(TTHREADS, 1) gram_tf32_kernel(const Tf32Args g
       const int st = static_cast<int>(it % TSTAGES);
       const int o = static_cast<int>(it % TOPS);
       const int b = static_cast<int>(it % TSCALE);
+      if (TMA) mbar_wait(bar_full0 + 8 * st, static_cast<unsigned>((it / TSTAGES) & 1));        // the box of this chunk has landed
       mbar_wait(bar_scale0 + 8 * b, static_cast<unsigned>((it / TSCALE) & 1));                 // the row warp has written this chunk's factors
       if (it >= TOPS) mbar_wait(bar_free0 + 8 * o, static_cast<unsigned>(((it / TOPS) - 1) & 1));  // the MMAs of chunk it-2 have read this buffer
       TICK(2);
 
       if (active && !(g.experiment & 1)) {
         const float* scale = reinterpret_cast<const float*>(smem + kScaleOff + b * TSCB);
-        const unsigned char* sp = sp0 + st * (TF * TSTRIDE);
+        const unsigned char* sp = sp0 + piece_stage(st);
+        const unsigned char* box = smem + kStagingOff + st * kTmaBoxBytes + tma_row * 128;
         unsigned char* ohi = op0 + o * (2 * TOPB);
         unsigned char* olo = ohi + TOPB;
         const bool plain = reinterpret_cast<const int*>(scale + 2 * TKC)[0] != 0;
@@ -513,7 +565,15 @@ __global__ void __launch_bounds__(TTHREADS, 1) gram_tf32_kernel(const Tf32Args g
             z[2] = __double2float_rn(static_cast<double>(v.z) - centre);
             z[3] = __double2float_rn(static_cast<double>(v.w) - centre);
           } else {
-            const double2 u = *reinterpret_cast<const double2*>(sp + q * 32), v = *reinterpret_cast<const double2*>(sp + q * 32 + 16);
+            double2 u, v;
+            if (by_tma) {
+              const int c = half * (TRPT / 2) + 2 * q, x = tma_row & 7;
+              u = *reinterpret_cast<const double2*>(box + ((c ^ x) << 4));
+              v = *reinterpret_cast<const double2*>(box + (((c + 1) ^ x) << 4));
+            } else {
+              u = *reinterpret_cast<const double2*>(sp + q * 32);
+              v = *reinterpret_cast<const double2*>(sp + q * 32 + 16);
+            }
             z[0] = __double2float_rn(u.x - centre);
             z[1] = __double2float_rn(u.y - centre);
             z[2] = __double2float_rn(v.x - centre);
@@ -560,6 +620,7 @@ __global__ void __launch_bounds__(TTHREADS, 1) gram_tf32_kernel(const Tf32Args g
       if (lane == 0) {  // one arrival per warp
         mbar_arrive(bar_ready0 + 8 * o);
         mbar_arrive(bar_sfree0 + 8 * b);
+        if (TMA) mbar_arrive(bar_empty0 + 8 * st);  // this warp has read its rows of the box
       }
       TICK(3);
 
@@ -660,6 +721,55 @@ __global__ void tf32_pack_kernel(const double* __restrict__ partials, int grid, 
 
 bool gram_tf32_supported(int d) { return d >= 1 && d <= TF; }
 
+namespace {
+
+// The TMA path needs the table's fp64 columns to be one uniformly strided 2-D array in THIS GPU's memory: columns
+// [first, d) all fp64, 16-byte aligned, a constant multiple-of-16 byte distance apart, after at most TFPW other columns
+// (the lab's int32 guest).  What dq4ml_synth_generate and any column-major allocation produce.  Returns false when the
+// table does not have that shape (or the driver lacks the encoder): the per-thread cp.async path serves it then.
+bool build_column_tensor_map(const std::vector<const void*>& col_ptrs, const std::vector<int>& dtypes, int64_t n,
+                             CUtensorMap* tmap, int* first_out) {
+  const int d = static_cast<int>(col_ptrs.size());
+  int first = 0;
+  while (first < d && dtypes[first] != DQ4ML_F64) ++first;
+  if (first > TFPW || d - first < 2 || n < TKC) return false;
+  for (int j = first; j < d; ++j)
+    if (dtypes[j] != DQ4ML_F64) return false;
+  const char* base = static_cast<const char*>(col_ptrs[first]);
+  const long long stride = static_cast<const char*>(col_ptrs[first + 1]) - base;
+  if (stride <= 0 || (stride & 15) != 0 || (reinterpret_cast<uintptr_t>(base) & 15u) != 0 || stride < n * 8) return false;
+  for (int j = first + 1; j < d; ++j)
+    if (static_cast<const char*>(col_ptrs[j]) - base != stride * (j - first)) return false;
+  cudaPointerAttributes at;
+  int dev = -1;
+  if (cudaGetDevice(&dev) != cudaSuccess || cudaPointerGetAttributes(&at, base) != cudaSuccess ||
+      at.type != cudaMemoryTypeDevice || at.device != dev)
+    return false;  // only this GPU's own memory is ever described by the map
+  typedef CUresult (*EncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                               const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                               CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+  static EncodeFn encode = [] {
+    void* fn = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &q) != cudaSuccess || q != cudaDriverEntryPointSuccess)
+      fn = nullptr;
+    return reinterpret_cast<EncodeFn>(fn);
+  }();
+  if (encode == nullptr) return false;
+  const cuuint64_t dims[2] = {static_cast<cuuint64_t>(n), static_cast<cuuint64_t>(d - first)};  // rows (contiguous), columns
+  const cuuint64_t strides[1] = {static_cast<cuuint64_t>(stride)};
+  const cuuint32_t box[2] = {TKC, TF};
+  const cuuint32_t elem[2] = {1, 1};
+  const CUresult rc = encode(tmap, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 2, const_cast<char*>(base), dims, strides, box, elem,
+                             CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                             CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (rc != CUDA_SUCCESS) return false;
+  *first_out = first;
+  return true;
+}
+
+}  // namespace
+
 int gram_tf32_wls_moments(dq4ml_ctx* ctx, const std::vector<const void*>& col_ptrs, const std::vector<int>& dtypes,
                           const double* label, const double* weight, const DeviceDq& dq, int64_t n, double* out) {
   const int d = static_cast<int>(col_ptrs.size());
@@ -733,15 +843,24 @@ int gram_tf32_wls_moments(dq4ml_ctx* ctx, const std::vector<const void*>& col_pt
   g.partials = d_part;
   static bool attr_set[64] = {false};
   if (ctx->device < 64 && !attr_set[ctx->device]) {
-    if ((e = cudaFuncSetAttribute(gram_tf32_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kTf32Smem)) != cudaSuccess)
+    if ((e = cudaFuncSetAttribute(gram_tf32_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kTf32Smem)) != cudaSuccess)
+      return fail(e, "tf32 gram smem attribute");
+    if ((e = cudaFuncSetAttribute(gram_tf32_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kTf32Smem)) != cudaSuccess)
       return fail(e, "tf32 gram smem attribute");
     attr_set[ctx->device] = true;
   }
+  // uniformly strided fp64 columns are staged by TMA tensor-map loads; DQ4ML_TF32_TMA=0 keeps the per-thread cp.async path
+  CUtensorMap tmap;
+  std::memset(&tmap, 0, sizeof(tmap));
+  g.tma_first = 0;
+  static const bool tma_off = getenv("DQ4ML_TF32_TMA") != nullptr && atoi(getenv("DQ4ML_TF32_TMA")) == 0;
+  const bool use_tma = !tma_off && build_column_tensor_map(col_ptrs, dtypes, n, &tmap, &g.tma_first);
   if (ctx->pass_timing) cudaEventRecord(ctx->pass_ev0, ctx->stream);
   tf32_centres_kernel<<<d + 1, 32, 0, ctx->stream>>>(d_ptrs, d_i32, label, d, n, d_centres);
   if ((e = cudaGetLastError()) != cudaSuccess) return fail(e, "tf32 centres kernel");
   if ((e = cudaMemsetAsync(d_part, 0, part_bytes, ctx->stream)) != cudaSuccess) return fail(e, "tf32 tile clear");
-  gram_tf32_kernel<<<grid, TTHREADS, kTf32Smem, ctx->stream>>>(g);
+  if (use_tma) gram_tf32_kernel<true><<<grid, TTHREADS + 32, kTf32Smem, ctx->stream>>>(g, tmap);
+  else gram_tf32_kernel<false><<<grid, TTHREADS, kTf32Smem, ctx->stream>>>(g, tmap);
   if ((e = cudaGetLastError()) != cudaSuccess) return fail(e, "tf32 gram kernel");
   tf32_border_reduce_kernel<<<(5 + 2 * d + 127) / 128, 128, 0, ctx->stream>>>(d_part, grid, d, d_centres, d_tot, d_out);
   if ((e = cudaGetLastError()) != cudaSuccess) return fail(e, "tf32 border reduce kernel");

@@ -14,10 +14,12 @@ struct WideSums {
 
 // For every row kept by the DQ predicate: pred = x . coef + c0, res = y * y_scale - pred.
 // row_out (device, nullable) receives pred (mode 0) or res (mode 1); rows the rules drop get 0.
+// With `weight` (instance weights, nullable): rows of weight 0 are skipped, sums.n is the weight sum, sums.ss_res is
+// sum w res^2 and row_out carries w * res (mode 1) -- what the weighted loss/gradient pass of a wide table needs.
 // sums are summed over ranks when the ctx is bound.  All data pointers are DEVICE pointers.
 int wide_rows_pass(dq4ml_ctx* ctx, const std::vector<const void*>& col_ptrs, const std::vector<int>& dtypes,
                    const double* coef_host, double c0, double y_scale, const double* label, const DeviceDq& dq, int64_t n,
-                   int mode, double* row_out, bool reduce_over_ranks, WideSums* sums);
+                   int mode, double* row_out, bool reduce_over_ranks, WideSums* sums, const double* weight = nullptr);
 
 // Grow-only device scratch shared by the wide passes (column table, coefficients, Gram partials).
 int ensure_wide_scratch(dq4ml_ctx* ctx, size_t bytes);

@@ -18,6 +18,7 @@ struct WideArgs {
   int d;
   double c0, y_scale;
   const double* label;
+  const double* weight;  // instance weights (nullable): the row output and the two leading sums become weighted
   const int* dq_guest;
   const double* dq_price;
   DqThresholds t;
@@ -83,12 +84,30 @@ __global__ void __launch_bounds__(kBlock) wide_rows_kernel(const WideArgs a) {
       k0 = dq_keep(__ldg(a.dq_guest + row), __ldg(a.dq_price + row), a.t);
       if (pair) k1 = dq_keep(__ldg(a.dq_guest + row + 1), __ldg(a.dq_price + row + 1), a.t);
     }
+    // instance weights (weighted LeastSquaresAggregator for wide tables): a row of weight 0 is skipped like a dropped
+    // row; a negative or NaN weight poisons the weight sum (Spark: require(weight >= 0.0))
+    double w0 = 1.0, w1 = 1.0;
+    if (a.weight != nullptr) {
+      w0 = __ldg(a.weight + row);
+      w1 = pair ? __ldg(a.weight + row + 1) : 0.0;
+      if (!(w0 >= 0.0)) w0 = k0 ? __longlong_as_double(0x7ff8000000000000LL) : 0.0;
+      if (!(w1 >= 0.0)) w1 = k1 ? __longlong_as_double(0x7ff8000000000000LL) : 0.0;
+      k0 = k0 && w0 != 0.0;
+      k1 = k1 && w1 != 0.0;
+    }
     // dropped rows may carry NaN/Inf garbage: they contribute exact zeros
     const double pred0 = k0 ? d0 + a.c0 : 0.0, pred1 = k1 ? d1 + a.c0 : 0.0;
     const double ys0 = k0 ? y0 * a.y_scale : 0.0, ys1 = k1 ? y1 * a.y_scale : 0.0;
-    const double r0 = ys0 - pred0, r1 = ys1 - pred1;
-    acc[0] += (k0 ? 1.0 : 0.0) + (k1 ? 1.0 : 0.0);
-    acc[1] = fma(r0, r0, fma(r1, r1, acc[1]));
+    double r0 = ys0 - pred0, r1 = ys1 - pred1;
+    if (a.weight != nullptr) {
+      acc[0] += (k0 ? w0 : 0.0) + (k1 ? w1 : 0.0);                 // weightSum
+      acc[1] = fma(w0 * r0, r0, fma(w1 * r1, r1, acc[1]));         // sum w r^2
+      r0 *= w0;                                                     // the row output carries w r for the gradient pass
+      r1 *= w1;
+    } else {
+      acc[0] += (k0 ? 1.0 : 0.0) + (k1 ? 1.0 : 0.0);
+      acc[1] = fma(r0, r0, fma(r1, r1, acc[1]));
+    }
     acc[2] += ys0 + ys1;
     acc[3] = fma(ys0, ys0, fma(ys1, ys1, acc[3]));
     acc[4] += fabs(r0) + fabs(r1);
@@ -146,7 +165,7 @@ int ensure_wide_scratch(dq4ml_ctx* ctx, size_t need) {
 
 int wide_rows_pass(dq4ml_ctx* ctx, const std::vector<const void*>& col_ptrs, const std::vector<int>& dtypes,
                    const double* coef_host, double c0, double y_scale, const double* label, const DeviceDq& dq, int64_t n,
-                   int mode, double* row_out, bool reduce_over_ranks, WideSums* sums) {
+                   int mode, double* row_out, bool reduce_over_ranks, WideSums* sums, const double* weight) {
   const int d = static_cast<int>(col_ptrs.size());
   const size_t ptr_b = (static_cast<size_t>(d) * 8 + 255) & ~static_cast<size_t>(255);
   const size_t coef_b = ptr_b;
@@ -171,6 +190,7 @@ int wide_rows_pass(dq4ml_ctx* ctx, const std::vector<const void*>& col_ptrs, con
   a.c0 = c0;
   a.y_scale = y_scale;
   a.label = label;
+  a.weight = weight;
   a.dq_guest = dq.guest;
   a.dq_price = dq.price;
   a.t.min_price = dq.params.min_price;

@@ -83,7 +83,7 @@ def test_weighted_fit_equals_replicated_rows(pkg, ctx):
     assert abs(mw.intercept() - mr.intercept()) < 1e-7 * max(1.0, abs(mr.intercept()))
 
 
-@pytest.mark.parametrize("d,n", [(1, 2_000), (3, 50_001), (15, 8_000), (31, 6_001)])
+@pytest.mark.parametrize("d,n", [(1, 2_000), (3, 50_001), (15, 8_000), (31, 6_001), (32, 6_001), (40, 9_000), (70, 5_003)])
 @pytest.mark.parametrize("reg", [(0.0, 0.0), (0.2, 0.0), (0.3, 0.8)])
 @pytest.mark.parametrize("fused", [False, True])
 def test_weighted_lbfgs_fit_vs_oracle(pkg, ctx, d, n, reg, fused):
@@ -102,12 +102,14 @@ def test_weighted_lbfgs_fit_vs_oracle(pkg, ctx, d, n, reg, fused):
     assert abs(hist[0] - ref.objective_history[0]) < 1e-9 * max(1.0, abs(ref.objective_history[0]))
 
 
-def test_weighted_lbfgs_wider_than_31_is_refused(pkg, ctx):
-    guest, price, feats, w = table(500, 32)
-    lr = pkg.LinearRegression().setSolver("l-bfgs").setWeightCol("w")
+def test_weighted_lbfgs_wide_table_nan_weight_is_an_error(pkg, ctx):
+    """Tables of 32 and more feature columns take the grouped weighted summarizer and the two-pass weighted
+    loss/gradient (the weight no longer fits as column 0 of one streaming launch): same require(w >= 0) behaviour."""
+    guest, price, feats, w = table(2_000, 40)
+    w[77] = -0.5
     with pytest.raises(pkg.capi.Dq4mlError) as ei:
-        lr.fit(frame(pkg, ctx, feats, price, w, False))
-    assert ei.value.status == pkg.capi.ERR_UNSUPPORTED
+        pkg.LinearRegression().setSolver("l-bfgs").setWeightCol("w").fit(frame(pkg, ctx, feats, price, w, False))
+    assert ei.value.status == pkg.capi.ERR_INVALID
 
 
 @pytest.mark.parametrize("solver", ["normal", "l-bfgs"])
