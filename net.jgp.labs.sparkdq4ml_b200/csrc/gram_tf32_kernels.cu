@@ -760,9 +760,14 @@ bool build_column_tensor_map(const std::vector<const void*>& col_ptrs, const std
   const cuuint64_t strides[1] = {static_cast<cuuint64_t>(stride)};
   const cuuint32_t box[2] = {TKC, TF};
   const cuuint32_t elem[2] = {1, 1};
+  // L2 promotion: a box row is 128 bytes of one column; consecutive 128-byte pieces of a column belong to different CTAs
+  static const CUtensorMapL2promotion promo = [] {
+    const char* env = getenv("DQ4ML_TF32_TMA_L2");
+    const int v = env != nullptr ? atoi(env) : 128;
+    return v == 256 ? CU_TENSOR_MAP_L2_PROMOTION_L2_256B : (v == 0 ? CU_TENSOR_MAP_L2_PROMOTION_NONE : CU_TENSOR_MAP_L2_PROMOTION_L2_128B);
+  }();
   const CUresult rc = encode(tmap, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 2, const_cast<char*>(base), dims, strides, box, elem,
-                             CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                             CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+                             CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, promo, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (rc != CUDA_SUCCESS) return false;
   *first_out = first;
   return true;
@@ -849,12 +854,16 @@ int gram_tf32_wls_moments(dq4ml_ctx* ctx, const std::vector<const void*>& col_pt
       return fail(e, "tf32 gram smem attribute");
     attr_set[ctx->device] = true;
   }
-  // uniformly strided fp64 columns are staged by TMA tensor-map loads; DQ4ML_TF32_TMA=0 keeps the per-thread cp.async path
+  // Staging: per-thread cp.async copies by default; DQ4ML_TF32_TMA=1 stages uniformly strided fp64 columns with TMA
+  // tensor-map loads instead.  Both give bit-identical moments (tests/test_gpu_tf32.py); measured at 62.5 M x 256 the TMA
+  // path is 3-5 % slower (50.4-51.0 ms against 48.5-49.3 ms, profiles/r2_config4_tf32_staging.jsonl): it removes the
+  // ~390 cycles of load issue per chunk from the converter warps, but all 16 of them now have to release a stage before
+  // its next box can be requested, and the pass is bound by their conversion arithmetic either way.
   CUtensorMap tmap;
   std::memset(&tmap, 0, sizeof(tmap));
   g.tma_first = 0;
-  static const bool tma_off = getenv("DQ4ML_TF32_TMA") != nullptr && atoi(getenv("DQ4ML_TF32_TMA")) == 0;
-  const bool use_tma = !tma_off && build_column_tensor_map(col_ptrs, dtypes, n, &tmap, &g.tma_first);
+  const char* tma_env = getenv("DQ4ML_TF32_TMA");  // read per call: the tests switch it
+  const bool use_tma = tma_env != nullptr && atoi(tma_env) != 0 && build_column_tensor_map(col_ptrs, dtypes, n, &tmap, &g.tma_first);
   if (ctx->pass_timing) cudaEventRecord(ctx->pass_ev0, ctx->stream);
   tf32_centres_kernel<<<d + 1, 32, 0, ctx->stream>>>(d_ptrs, d_i32, label, d, n, d_centres);
   if ((e = cudaGetLastError()) != cudaSuccess) return fail(e, "tf32 centres kernel");

@@ -187,3 +187,22 @@ def test_unknown_tier_is_refused(pkg, ctx):
     with pytest.raises(ValueError):
         ctx.set_gram_tier("bf16")
     assert pkg.capi.lib().dq4ml_ctx_set_gram_tier(ctx.handle, 7) == pkg.capi.ERR_INVALID
+
+
+@pytest.mark.parametrize("d,n", [(256, 200_003), (40, 50_000), (3, 4_099)])
+def test_tf32_tma_staging_equals_cp_async_staging(pkg, tf32, monkeypatch, d, n):
+    """The tcgen05 kernel can stage a uniformly strided fp64 table (dq4ml_synth_generate's layout) with TMA tensor-map
+    loads -- one 16-row x 256-column box per request, DQ4ML_TF32_TMA=1 -- instead of per-thread cp.async copies.  Only
+    the staging differs, so the two paths must give bit-identical moments; a table whose columns are NOT one strided
+    array must quietly take the cp.async path under the same setting."""
+    from sparkdq4ml_b200 import ml
+    g, p, x = tf32.synth_generate(n, d=d, p_low=0.05, p_high=0.05)
+    strided = [g] + [x[k] for k in range(d - 1)]
+    monkeypatch.setenv("DQ4ML_TF32_TMA", "0")
+    ref = ml.wls_moments(tf32, strided, p, dq=(g, p))
+    monkeypatch.setenv("DQ4ML_TF32_TMA", "1")
+    got = ml.wls_moments(tf32, strided, p, dq=(g, p))
+    assert got.tobytes() == ref.tobytes()
+    scattered = [g] + [torch.empty(n + 16 * (1 + k % 3), dtype=torch.float64, device="cuda")[:n].copy_(x[k]) for k in range(d - 1)]
+    torch.cuda.synchronize()
+    assert ml.wls_moments(tf32, scattered, p, dq=(g, p)).tobytes() == ref.tobytes()
