@@ -269,7 +269,8 @@ int dq4ml_lsq_loss_grad(dq4ml_ctx* ctx, const dq4ml_columns* features, const dou
  * loss = DQ4ML_LOSS_HUBER (the lab leaves Spark's default, squaredError, at App:120-123; SURVEY.md 8f lists huber as a
  * next parameter): summarizer pass for the feature scales, one HuberAggregator pass per evaluation, Breeze LBFGSB on the
  * host over [coefficients, intercept, sigma] with sigma > 0; needs elasticNetParam == 0, epsilon > 1, solver != normal
- * (as Spark requires) and at most 32 feature columns (31 with a weight column). */
+ * (as Spark requires).  Up to 32 streamed columns (features, plus the weight if any) one launch per evaluation; wider
+ * tables a column-walking row pass plus gradient passes over column groups. */
 int dq4ml_linreg_fit(dq4ml_ctx* ctx, const dq4ml_columns* features, const double* label, int64_t n,
                      const dq4ml_lr_params* params, const dq4ml_dq_fused* dq, dq4ml_lr_model** out);
 

@@ -465,14 +465,6 @@ int wls_moments_any(dq4ml_ctx* ctx, const PassInputs& in, int64_t n, double* out
   return rc;
 }
 
-int weighted_width_check(const PassInputs& in) {
-  if (in.weight != nullptr && in.wcols.n == 0) {
-    set_error("weightCol with the l-bfgs branch handles at most %d feature columns (got %d)", kMaxCols - 1, in.width());
-    return DQ4ML_ERR_UNSUPPORTED;
-  }
-  return DQ4ML_OK;
-}
-
 // ---- merging summarizers across ranks ---------------------------------------------------------------------------------
 // Every rank accumulates shifted power sums S1 = sum w (v - c), S2 = sum w (v - c)^2 around ITS OWN provisional centre c
 // (the head of its shard of the column), and publishes c next to them.  The host turns each rank's triple into
@@ -724,16 +716,55 @@ int lsq_pass(dq4ml_ctx* ctx, const PassInputs& in, int64_t n, const double* coef
 // One HuberAggregator evaluation at params = [coefficients (d), intercept (if fitted), sigma]: raw sums in the same
 // layout.  The weight, when there is one, rides as column 0 of the streamed table (so d <= kMaxCols - 1 then).
 int huber_pass(dq4ml_ctx* ctx, const PassInputs& in, int64_t n, const double* params, const double* fstd, bool fit_intercept,
-               double epsilon, double* loss_sum, double* weight_sum, double* grad_sum) {
+               double epsilon, double* loss_sum, double* weight_sum, double* grad_sum, double* diff_scratch) {
   const int d = in.width();
   const bool weighted = in.weight != nullptr;
-  if (weighted) {
-    const int rc = weighted_width_check(in);
-    if (rc != DQ4ML_OK) return rc;
-  }
   if (d + (weighted ? 1 : 0) > kMaxCols) {
-    set_error("huber loss handles at most %d feature columns (%d with a weight column); got %d", kMaxCols, kMaxCols - 1, d);
-    return DQ4ML_ERR_UNSUPPORTED;
+    // Wide table: pass 1 walks the columns per row, writes the factor that multiplies x_j / std_j in the gradient and
+    // sums the loss, the weight and the intercept / sigma derivatives; pass 2 takes sum factor x_j over column groups.
+    if (diff_scratch == nullptr) {
+      set_error("internal: no scratch column for the wide huber pass");
+      return DQ4ML_ERR_INVALID;
+    }
+    std::vector<double> eff(d);
+    for (int j = 0; j < d; ++j) eff[j] = fstd[j] != 0.0 ? params[j] / fstd[j] : 0.0;
+    const double sigma = params[d + (fit_intercept ? 1 : 0)];
+    WideSums ws;
+    int rc = wide_rows_pass(ctx, in.ptr, in.dtype, eff.data(), fit_intercept ? params[d] : 0.0, 1.0, in.label, in.dq, n, 2,
+                            diff_scratch, false, &ws, in.weight, sigma, epsilon);
+    if (rc != DQ4ML_OK) return rc;
+    std::vector<double> all(4 + d, 0.0);
+    all[0] = ws.ss_res;   // loss sum
+    all[1] = ws.n;        // weight sum
+    all[2] = ws.sum_res;  // d / d intercept
+    all[3] = ws.sum_y;    // d / d sigma
+    constexpr int kGradGroup = 16;
+    for (int c0 = 0; c0 < d; c0 += kGradGroup) {
+      DeviceCols g;
+      g.n = std::min(kGradGroup, d - c0);
+      for (int j = 0; j < g.n; ++j) {
+        g.ptr[j] = in.ptr[c0 + j];
+        g.dtype[j] = in.dtype[c0 + j];
+      }
+      PassOpts local;
+      local.reduce = false;
+      cudaError_t e = run_stream_pass(ctx, kOpGrad, g, diff_scratch, DeviceDq{}, n, nullptr, nullptr, local);
+      if (e != cudaSuccess) return cuda_fail(e, "huber gradient pass");
+      rc = finish_result(ctx, stream_nacc(kOpGrad, stream_bucket(g.n)), local);
+      if (rc != DQ4ML_OK) return rc;
+      for (int j = 0; j < g.n; ++j) all[4 + c0 + j] = ctx->h_result[j];
+    }
+    if (multi_rank(ctx)) {
+      rc = host_allreduce(ctx, all.data(), static_cast<int64_t>(all.size()));
+      if (rc != DQ4ML_OK) return rc;
+    }
+    *loss_sum = all[0];
+    *weight_sum = all[1];
+    for (int j = 0; j < d; ++j) grad_sum[j] = fstd[j] != 0.0 ? all[4 + j] / fstd[j] : 0.0;
+    int k = d;
+    if (fit_intercept) grad_sum[k++] = all[2];
+    grad_sum[k] = all[3];
+    return DQ4ML_OK;
   }
   const int off = weighted ? 1 : 0;
   const int b = stream_bucket(d + off > 0 ? d + off : 1);
@@ -1383,7 +1414,7 @@ int dq4ml_linreg_fit_weighted(dq4ml_ctx* ctx, const dq4ml_columns* features, con
   PassInputs in;
   // tables too wide for one streaming launch (with the weight as an extra column, if any) need one scratch column for
   // the per-row scaled difference
-  const bool wide_lbfgs = !wls && !huber && d + (weight != nullptr ? 1 : 0) > kMaxCols;
+  const bool wide_lbfgs = !wls && d + (weight != nullptr ? 1 : 0) > kMaxCols;
   int rc = gather_inputs(ctx, features, label, n, dq, &in, wide_lbfgs ? static_cast<size_t>(n) * 8 : 0, 1 << 20, weight);
   if (rc != DQ4ML_OK) return rc;
   double* diff = wide_lbfgs ? static_cast<double*>(arena_take(ctx, static_cast<size_t>(n) * 8)) : nullptr;
@@ -1395,17 +1426,13 @@ int dq4ml_linreg_fit_weighted(dq4ml_ctx* ctx, const dq4ml_columns* features, con
       if (rc != DQ4ML_OK) return rc;
       model->m = wls_fit_from_moments(mom.data(), d, p);
     } else if (huber) {
-      if (d + (in.weight != nullptr ? 1 : 0) > kMaxCols) {
-        set_error("huber loss handles at most %d feature columns (%d with a weight column); got %d", kMaxCols, kMaxCols - 1, d);
-        return DQ4ML_ERR_UNSUPPORTED;
-      }
       ColumnStats st;
       rc = in.weight != nullptr ? summarize_core_weighted(ctx, in, n, &st) : summarize_core(ctx, in, n, &st);
       if (rc != DQ4ML_OK) return rc;
       HuberPassFn pass = [&](const Vec& par, const Vec& fstd, double& loss_sum, double& weight_sum, Vec& grad_sum) {
         grad_sum.assign(par.size(), 0.0);
         const int r = huber_pass(ctx, in, n, par.data(), fstd.data(), p.fit_intercept, p.epsilon, &loss_sum, &weight_sum,
-                                 grad_sum.data());
+                                 grad_sum.data(), diff);
         if (r != DQ4ML_OK) throw SolveError{r, get_error()};
       };
       model->m = huber_path_fit(st, d, p, pass);

@@ -91,11 +91,13 @@ __device__ __forceinline__ void pair_rows(double (&acc)[PairShape<OP, PH>::NT], 
       for (int r = 0; r < PR; ++r) x[j][r] = 0.0;
     }
   }
-  if (VEC) {
-    load_f64<PR, true>(label, row, y);
-  } else {
+  if (label != nullptr) {  // the later column groups of a wide table's summarizer come without the label
+    if (VEC) {
+      load_f64<PR, true>(label, row, y);
+    } else {
 #pragma unroll
-    for (int r = 0; r < PR; ++r) y[r] = row + r < n ? label[row + r] : 0.0;
+      for (int r = 0; r < PR; ++r) y[r] = row + r < n ? label[row + r] : 0.0;
+    }
   }
   bool keep[PR];
   if (DQMODE == kDqSeparate) {

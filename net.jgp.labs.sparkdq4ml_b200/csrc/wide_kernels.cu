@@ -17,6 +17,7 @@ struct WideArgs {
   const double* coef;
   int d;
   double c0, y_scale;
+  double sigma, epsilon;  // mode 2 (huber)
   const double* label;
   const double* weight;  // instance weights (nullable): the row output and the two leading sums become weighted
   const int* dq_guest;
@@ -99,6 +100,30 @@ __global__ void __launch_bounds__(kBlock) wide_rows_kernel(const WideArgs a) {
     const double pred0 = k0 ? d0 + a.c0 : 0.0, pred1 = k1 ? d1 + a.c0 : 0.0;
     const double ys0 = k0 ? y0 * a.y_scale : 0.0, ys1 = k1 ? y1 * a.y_scale : 0.0;
     double r0 = ys0 - pred0, r1 = ys1 - pred1;
+    if (a.mode == 2) {
+      // HuberAggregator for wide tables: r is the plain residual (label - margin); the row output carries the factor
+      // that multiplies x_j / std_j in the gradient, sums: [0] weight sum, [1] loss, [5] sum of factors (d/d intercept),
+      // [2] d/d sigma
+      auto huber = [&](bool k, double w, double r, double& loss, double& factor, double& dsig) {
+        const double rs = r / a.sigma;
+        const bool inner = fabs(r) <= a.sigma * a.epsilon;
+        loss = k ? w * (inner ? 0.5 * (a.sigma + r * rs) : 0.5 * (a.sigma + 2.0 * a.epsilon * fabs(r) - a.sigma * a.epsilon * a.epsilon)) : 0.0;
+        factor = k ? w * (inner ? -rs : (r >= 0.0 ? -a.epsilon : a.epsilon)) : 0.0;
+        dsig = k ? w * (inner ? 0.5 * (1.0 - rs * rs) : 0.5 * (1.0 - a.epsilon * a.epsilon)) : 0.0;
+      };
+      double l0, f0, g0, l1, f1, g1;
+      huber(k0, w0, r0, l0, f0, g0);
+      huber(k1, w1, r1, l1, f1, g1);
+      acc[0] += (k0 ? w0 : 0.0) + (k1 ? w1 : 0.0);
+      acc[1] += l0 + l1;
+      acc[2] += g0 + g1;
+      acc[5] += f0 + f1;
+      if (a.row_out != nullptr) {
+        if (pair) stg_stream_d2(a.row_out + row, make_double2(f0, f1));
+        else a.row_out[row] = f0;
+      }
+      continue;
+    }
     if (a.weight != nullptr) {
       acc[0] += (k0 ? w0 : 0.0) + (k1 ? w1 : 0.0);                 // weightSum
       acc[1] = fma(w0 * r0, r0, fma(w1 * r1, r1, acc[1]));         // sum w r^2
@@ -165,7 +190,8 @@ int ensure_wide_scratch(dq4ml_ctx* ctx, size_t need) {
 
 int wide_rows_pass(dq4ml_ctx* ctx, const std::vector<const void*>& col_ptrs, const std::vector<int>& dtypes,
                    const double* coef_host, double c0, double y_scale, const double* label, const DeviceDq& dq, int64_t n,
-                   int mode, double* row_out, bool reduce_over_ranks, WideSums* sums, const double* weight) {
+                   int mode, double* row_out, bool reduce_over_ranks, WideSums* sums, const double* weight, double sigma,
+                   double epsilon) {
   const int d = static_cast<int>(col_ptrs.size());
   const size_t ptr_b = (static_cast<size_t>(d) * 8 + 255) & ~static_cast<size_t>(255);
   const size_t coef_b = ptr_b;
@@ -189,6 +215,8 @@ int wide_rows_pass(dq4ml_ctx* ctx, const std::vector<const void*>& col_ptrs, con
   a.d = d;
   a.c0 = c0;
   a.y_scale = y_scale;
+  a.sigma = sigma;
+  a.epsilon = epsilon;
   a.label = label;
   a.weight = weight;
   a.dq_guest = dq.guest;

@@ -385,6 +385,26 @@ def test_wide_lbfgs_fit_d40(pkg, ctx, parity_log):
     check_fit(parity_log, "wide_lbfgs_d40", model, ref.coefficients, ref.intercept, ref.objective_history, TOL_WIDE)
 
 
+def test_wide_lbfgs_fit_d70_second_group_takes_the_lane_pair_kernel(pkg, ctx, parity_log):
+    """70 columns under solver l-bfgs: the summarizer runs in groups of 32, 32 and 6 columns, and the second group -- more
+    than 16 columns, no label -- goes through the lane-pair kernel without a label column."""
+    n, d = 30_001, 70
+    guest, price, feats = wide_table(n, d)
+    params = dict(max_iter=25, reg_param=0.1, elastic_net_param=0.3, solver="l-bfgs")
+    ref = spark_ml.linear_regression_fit(feats, price, spark_ml.LRParams(**params), dq=(guest, price), threads=8)
+    dfeats, dprice = to_dev(*feats), to_dev(price)[0]
+    cols = {"guest": dfeats[0], "label": dprice}
+    names = ["guest"]
+    for k in range(1, d):
+        cols[f"x{k}"] = dfeats[k]
+        names.append(f"x{k}")
+    df = pkg.VectorAssembler().setInputCols(names).transform(pkg.Frame(ctx, cols).with_fused_dq("guest", "label"))
+    model = estimator(pkg, params).fit(df)
+    assert model.solver_used == ref.solver_used == "owlqn"
+    assert model.summary().totalIterations() == ref.total_iterations
+    check_fit(parity_log, "wide_lbfgs_d70", model, ref.coefficients, ref.intercept, ref.objective_history, TOL_WIDE)
+
+
 @pytest.mark.parametrize("d", [3, 40])
 def test_training_summary_surface_vs_numpy(pkg, ctx, d):
     """The rest of LinearRegressionTrainingSummary (explainedVariance, r2adj, degreesOfFreedom, devianceResiduals,

@@ -13,6 +13,7 @@ from oracle import passes, spark_ml
 pytestmark = pytest.mark.gpu
 
 TOL = 1e-8
+TOL_WIDE = 1e-6
 
 
 def table(n, d, seed=0):
@@ -49,14 +50,14 @@ CASES = [
     (4, 50_000, dict(fit_intercept=False, epsilon=2.0)),
     (16, 120_000, dict(reg_param=0.05, solver="l-bfgs")),
     (32, 40_000, dict(reg_param=0.01)),
+    (40, 30_000, dict(reg_param=0.02)),   # wider than one streaming launch: column-walking row pass + gradient groups
+    (70, 20_003, dict(reg_param=0.05, fit_intercept=False)),
 ]
 
 
 @pytest.mark.parametrize("d,n,params", CASES)
 @pytest.mark.parametrize("weighted", [False, True])
 def test_huber_fit_vs_oracle(pkg, ctx, parity_log, d, n, params, weighted):
-    if weighted and d == 32:
-        pytest.skip("a weight column takes one of the 32 streamed columns")
     feats, price = table(n, d)
     w = None
     if weighted:
@@ -72,7 +73,9 @@ def test_huber_fit_vs_oracle(pkg, ctx, parity_log, d, n, params, weighted):
             abs(model.intercept() - ref.intercept) / max(abs(ref.intercept), 1e-300) if ref.intercept != 0 else abs(model.intercept()),
             rel_err(model.scale(), ref.scale)]
     parity_log(f"huber_d{d}_n{n}_w{int(weighted)}_{params}", "objectiveHistory / coef scale-rel / intercept / scale", errs)
-    assert max(errs) < TOL, errs
+    # up to 32 streamed columns the sums differ from the oracle's in the last bits only (measured <= 9e-11); the two-pass
+    # path of wider tables sums in another order and ~40 L-BFGS-B iterations amplify that (measured 4e-8 at d = 40)
+    assert errs[0] < TOL and max(errs) < (TOL if d <= 32 else TOL_WIDE), errs
 
 
 def test_huber_with_fused_dq_equals_filtered_table(pkg, ctx):
@@ -111,6 +114,3 @@ def test_huber_parameter_checks(pkg, ctx):
     df = pkg.VectorAssembler().setInputCols(["f0"]).transform(pkg.Frame(ctx, cols))
     with pytest.raises(pkg.capi.Dq4mlError):  # huber supports L2 only
         pkg.LinearRegression().setLoss("huber").setRegParam(0.1).setElasticNetParam(0.5).fit(df)
-    wide, price = table(500, 33)
-    with pytest.raises(pkg.capi.Dq4mlError):
-        fit_gpu(pkg, ctx, wide, price, dict())
