@@ -13,9 +13,10 @@ pytestmark = pytest.mark.gpu
 
 COV_TOL = 5e-6   # |G - G_ref| / (n sigma_i sigma_j)
 FIT_TOL = 1e-5   # the tier's stated tolerance: intercept relative; coefficients relative to the largest coefficient
-# (measured on these cases: <= 1.0e-6 scale-relative, <= 1.2e-6 on the intercept, profiles/r2_parity_errors.jsonl)
+# (measured on these cases: <= 2.2e-6 scale-relative, <= 4.2e-6 on the intercept, profiles/r2_parity_errors.jsonl)
 COEF_FLOOR = 0.05      # per-coefficient relative error is checked for coefficients of at least 5 % of the largest one ...
-PER_COEF_TOL = 5e-5    # ... where the tf32 Gram's absolute error is up to 20x larger in relative terms (measured 1.8e-5)
+PER_COEF_TOL = 1e-4    # ... where the tf32 Gram's absolute error is up to 20x larger in relative terms (measured 1.8e-5
+                       # unweighted, 4.4e-5 with instance weights)
 
 
 @pytest.fixture()
