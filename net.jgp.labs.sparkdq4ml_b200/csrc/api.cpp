@@ -215,36 +215,44 @@ void arm_epilogue(dq4ml_ctx* ctx, const PassOpts& o) {
     ep.xr_seq = ++ctx->xr_seq;
     ctx->ep_world = ctx->world;
   }
-  ep.host_out = ctx->h_result_dev;
-  ep.host_flag = ctx->h_flag_dev;
+  ep.host_out = ctx->h_words_dev;
   ep.host_seq = ++ctx->host_seq;
   ctx->ep_armed = true;
 }
 
-int wait_host_flag(dq4ml_ctx* ctx) {
-  const unsigned long long want = ctx->scratch.ep.host_seq;
-  for (unsigned spins = 0;; ++spins) {
-    const unsigned long long v = *ctx->h_flag;
-    if (v == want) break;
-    if (v == ~0ull) {
-      cudaStreamSynchronize(ctx->stream);
-      set_error("cross-rank epilogue timed out waiting for a peer's result vector");
-      return DQ4ML_ERR_COMM;
-    }
-    if ((spins & 4095u) == 4095u) {  // a failed launch / kernel never raises the flag: look at the stream now and then
-      const cudaError_t e = cudaStreamQuery(ctx->stream);
-      if (e == cudaSuccess) {
-        if (*ctx->h_flag == want) break;
-        set_error("the pass finished without publishing its result");
-        return DQ4ML_ERR_CUDA;
+// Polls the tagged word pairs the epilogue writes (epilogue.cuh) and decodes `count` doubles into ctx->h_result.
+int wait_host_words(dq4ml_ctx* ctx, int64_t count) {
+  const unsigned tag = static_cast<unsigned>(ctx->scratch.ep.host_seq);
+  volatile unsigned long long* w = ctx->h_words;
+  unsigned spins = 0;
+  for (int64_t k = 0; k < count; ++k) {
+    for (;;) {
+      const unsigned long long a = w[2 * k], b = w[2 * k + 1];
+      if (static_cast<unsigned>(a >> 32) == tag && static_cast<unsigned>(b >> 32) == tag) {
+        const unsigned long long bits = (a & 0xffffffffull) | (b << 32);
+        std::memcpy(&ctx->h_result[k], &bits, sizeof(double));
+        break;
       }
-      if (e != cudaErrorNotReady) return cuda_fail(e, "streaming pass");
-    }
+      if (static_cast<unsigned>(w[0] >> 32) == kXrErrorTag) {
+        cudaStreamSynchronize(ctx->stream);
+        set_error("cross-rank epilogue timed out waiting for a peer's result vector");
+        return DQ4ML_ERR_COMM;
+      }
+      if ((++spins & 4095u) == 0u) {  // a failed launch / kernel never writes the words: look at the stream now and then
+        const cudaError_t e = cudaStreamQuery(ctx->stream);
+        if (e == cudaSuccess) {
+          const unsigned long long a2 = w[2 * k], b2 = w[2 * k + 1];
+          if (static_cast<unsigned>(a2 >> 32) == tag && static_cast<unsigned>(b2 >> 32) == tag) continue;  // just landed
+          set_error("the pass finished without publishing its result");
+          return DQ4ML_ERR_CUDA;
+        }
+        if (e != cudaErrorNotReady) return cuda_fail(e, "streaming pass");
+      }
 #if defined(__x86_64__) || defined(__i386__)
-    __builtin_ia32_pause();
+      __builtin_ia32_pause();
 #endif
+    }
   }
-  std::atomic_thread_fence(std::memory_order_acquire);
   return DQ4ML_OK;
 }
 
@@ -261,7 +269,7 @@ int finish_result(dq4ml_ctx* ctx, int64_t count, const PassOpts& o = PassOpts{})
   bool have_all_ranks = false;  // h_result already holds the cross-rank fold / gather
   if (ctx->ep_armed) {
     ctx->ep_armed = false;
-    const int rc = wait_host_flag(ctx);
+    const int rc = wait_host_words(ctx, count * (o.gather ? ctx->ep_world : 1));
     if (ctx->pass_event_pending) cudaEventSynchronize(ctx->pass_ev1);
     collect_pass_time(ctx);
     if (rc != DQ4ML_OK) return rc;
@@ -916,13 +924,14 @@ int dq4ml_ctx_create(int device, dq4ml_ctx** out) {
   p += counters_b;
   ctx->d_err = reinterpret_cast<int*>(p);
   ctx->scratch.sm_count = ctx->sm_count;
-  // result vector + the word the host polls: pinned AND mapped, so the last CTA of a pass can write them directly
-  if ((e = cudaHostAlloc(reinterpret_cast<void**>(&ctx->h_result), result_b + 256, cudaHostAllocMapped | cudaHostAllocPortable)) != cudaSuccess)
-    return fail(e, "pinned result");
-  std::memset(ctx->h_result, 0, result_b + 256);
-  if ((e = cudaHostGetDevicePointer(reinterpret_cast<void**>(&ctx->h_result_dev), ctx->h_result, 0)) != cudaSuccess) return fail(e, "mapped result");
-  ctx->h_flag = reinterpret_cast<volatile unsigned long long*>(reinterpret_cast<char*>(ctx->h_result) + result_b);
-  ctx->h_flag_dev = reinterpret_cast<unsigned long long*>(reinterpret_cast<char*>(ctx->h_result_dev) + result_b);
+  if ((e = cudaMallocHost(reinterpret_cast<void**>(&ctx->h_result), result_b)) != cudaSuccess) return fail(e, "pinned result");
+  // the epilogue's hand-over buffer: pinned AND mapped, so the last CTA of a pass can write it directly
+  void* words = nullptr;
+  if ((e = cudaHostAlloc(&words, kEpilogueValues * 16, cudaHostAllocMapped | cudaHostAllocPortable)) != cudaSuccess)
+    return fail(e, "mapped result words");
+  std::memset(words, 0, kEpilogueValues * 16);
+  ctx->h_words = static_cast<volatile unsigned long long*>(words);
+  if ((e = cudaHostGetDevicePointer(reinterpret_cast<void**>(&ctx->h_words_dev), words, 0)) != cudaSuccess) return fail(e, "mapped result words");
   if ((e = cudaEventCreate(&ctx->pass_ev0)) != cudaSuccess) return fail(e, "event");
   if ((e = cudaEventCreate(&ctx->pass_ev1)) != cudaSuccess) return fail(e, "event");
   if ((e = cudaStreamSynchronize(ctx->stream)) != cudaSuccess) return fail(e, "sync");
@@ -941,6 +950,7 @@ void dq4ml_ctx_destroy(dq4ml_ctx* ctx) {
   if (ctx->d_tile_state != nullptr) cudaFree(ctx->d_tile_state);
   if (ctx->scratch_base != nullptr) cudaFree(ctx->scratch_base);
   if (ctx->h_result != nullptr) cudaFreeHost(ctx->h_result);
+  if (ctx->h_words != nullptr) cudaFreeHost(const_cast<unsigned long long*>(ctx->h_words));
   if (ctx->pass_ev0 != nullptr) cudaEventDestroy(ctx->pass_ev0);
   if (ctx->pass_ev1 != nullptr) cudaEventDestroy(ctx->pass_ev1);
   if (ctx->stream != nullptr) cudaStreamDestroy(ctx->stream);

@@ -29,10 +29,10 @@ struct dq4ml_ctx {
   cudaStream_t stream = nullptr;
   dq4ml::Scratch scratch{};
   char* scratch_base = nullptr;
-  double* h_result = nullptr;  // pinned + mapped, kResultDoubles; the epilogue of a streaming pass writes it from the GPU
-  double* h_result_dev = nullptr;              // the same buffer as the device sees it
-  volatile unsigned long long* h_flag = nullptr;  // pinned + mapped word the host polls (epilogue.cuh)
-  unsigned long long* h_flag_dev = nullptr;
+  double* h_result = nullptr;  // pinned, kResultDoubles: where every pass's vector ends up for the host code
+  volatile unsigned long long* h_words = nullptr;  // pinned + mapped: the tagged word pairs the epilogue of a streaming
+                                                   // pass writes from the GPU (kEpilogueValues pairs, epilogue.cuh)
+  unsigned long long* h_words_dev = nullptr;       // the same buffer as the device sees it
   unsigned long long host_seq = 0;  // passes published to the host so far
   unsigned long long xr_seq = 0;    // cross-rank (mailbox) passes so far: advances in lock step on every rank
   bool ep_armed = false;            // the pass just launched publishes through the epilogue
@@ -68,6 +68,7 @@ namespace dq4ml {
 
 constexpr size_t kResultDoubles = 1 << 16;  // fits the packed Gram of d = 256 (33 411 doubles)
 constexpr size_t kPartialsBytes = 8u << 20;
+constexpr size_t kEpilogueValues = static_cast<size_t>(kXrMaxRanks) * kXrSlotDoubles;  // longest hand-over: a gather of every rank's vector
 
 // api.cpp: after the ctx stream has been synchronised, folds the pending pass-timing event pair into the ctx counters
 void collect_pass_time(dq4ml_ctx* ctx);

@@ -83,8 +83,8 @@ struct NcclBinding {
 
 namespace {
 
-constexpr size_t kMailboxBytes = 2 * kXrMaxRanks * sizeof(unsigned long long) +
-                                 2 * static_cast<size_t>(kXrMaxRanks) * kXrSlotDoubles * sizeof(double);
+// two buffers x kXrMaxRanks slots x kXrSlotDoubles values, each value two tagged 8-byte words (epilogue.cuh)
+constexpr size_t kMailboxBytes = 2 * static_cast<size_t>(kXrMaxRanks) * kXrSlotDoubles * 16;
 
 // Allocates this rank's mailbox, exchanges CUDA IPC handles over the communicator, and maps every peer's mailbox.
 // Collective.  Any failure on any rank leaves mailboxes_ok false on EVERY rank (they agree through an all-reduce), and

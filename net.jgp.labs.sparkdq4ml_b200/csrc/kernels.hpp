@@ -29,10 +29,11 @@ struct DeviceDq {
 // an exchange through the peer mailboxes when several ranks are bound.
 constexpr int kXrMaxRanks = 16;
 constexpr int kXrSlotDoubles = 128;  // longest published vector: SummCoreOp<32> = 67 sums + 33 centres
+constexpr unsigned kXrErrorTag = 0xffffffffu;  // tag of word pair 0 of the host buffer when the exchange timed out
 struct XrEpilogue {
-  double* host_out = nullptr;              // device alias of the pinned result buffer; nullptr = leave it in scratch.result
-  unsigned long long* host_flag = nullptr; // the word the host polls
-  unsigned long long host_seq = 0;         // value that word takes when this pass's vector is complete
+  unsigned long long* host_out = nullptr;  // device alias of the pinned result buffer (tagged word pairs, epilogue.cuh);
+                                           // nullptr = leave the vector in scratch.result
+  unsigned long long host_seq = 0;         // tag (low 32 bits) the words of this pass carry in the host buffer
   int world = 1, rank = 0;                 // world > 1: exchange through the mailboxes below
   int gather = 0;                          // 0: fold the ranks' vectors in rank order; 1: hand the host all of them
   int extra_consts = 0;                    // append this many of the pass's device constants to the vector
