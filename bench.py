@@ -183,7 +183,7 @@ class ClockSampler:
         self.proc = None
         try:
             self.proc = subprocess.Popen(
-                ["nvidia-smi", f"--query-gpu={self.FIELDS}", "--format=csv,noheader,nounits", "-lms", "50", "-i", str(index)],
+                ["nvidia-smi", f"--query-gpu={self.FIELDS}", "--format=csv,noheader,nounits", "-lms", "20", "-i", str(index)],
                 stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
         except OSError:
             self.proc = None
@@ -335,7 +335,7 @@ class Bench:
         for _ in range(warmup):
             model = lr.fit(df)
         # the timed region lasts only milliseconds: start the clock sampler first and keep the same step running
-        # untimed for a while so that nvidia-smi (50 ms period) sees the GPU under this load; every rank must run the
+        # untimed for a while so that nvidia-smi (20 ms period) sees the GPU under this load; every rank must run the
         # same number of steps (each fit contains a collective), so rank 0 sizes the pre-roll and tells the others
         smp = ClockSampler(self.local_rank) if (sampler and self.rank == 0) else None
         t0 = time.perf_counter()
@@ -357,6 +357,8 @@ class Bench:
         pass_ms, passes = ctx.pass_timing()
         ctx.enable_pass_timing(False)
         clocks = smp.stop() if smp is not None else None
+        if clocks is not None:
+            clocks["sampled_over"] = f"{args.preroll_seconds} s of untimed steps + the timed steps + the roofline steps, 20 ms period"
         res = {"rows": n, "ms": ms, "steps": steps, "value": self.world * n * steps / (ms / 1e3), "launches": int(launches),
                "pass_ms_avg": pass_ms / max(passes, 1), "passes": int(passes), "clocks": clocks,
                "fit": {"coefficient": float(model.coefficients()[0]), "intercept": model.intercept(),
@@ -519,7 +521,7 @@ def run_ours(args):
     line = {"metric": METRIC, "unit": UNIT, "n_gpus": b.world, "steps": args.steps, "warmup": warmup,
             "higher_is_better": True, "vs_baseline": None, "dtype": "f64", "data": "synthetic"}
     if cfg == 2:
-        r = b.config2(rows, args.steps, warmup)
+        r = b.config2(rows, args.steps, warmup, sampler=not args.no_clock_sampler)
         achieved = BYTES_PER_ROW * rows / (r["pass_ms_avg"] / 1e3) / 1e9
         line.update({
             "value": r["value"], "ms_per_step": r["ms"] / args.steps, "scaling": "weak", "config": config(2, rows),
@@ -589,10 +591,14 @@ def main():
     ap.add_argument("--cpu-seconds", type=float, default=16.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-extra", action="store_true", help="skip the config 3/4/5 side measurements")
+    ap.add_argument("--no-clock-sampler", action="store_true", help="diagnostic: do not run nvidia-smi beside the timed region")
     ap.add_argument("--config3-rows", type=int, default=1_000_000_000)
     ap.add_argument("--config4-rows", type=int, default=62_500_000)
     ap.add_argument("--config5-sizes", type=str, default="100000000,1000000000,4000000000")
-    ap.add_argument("--preroll-seconds", type=float, default=2.0, help="untimed steps under the clock sampler")
+    ap.add_argument("--preroll-seconds", type=float, default=0.3,
+                    help="untimed steps under the clock sampler before the timed ones (the timed region itself lasts 4 ms: "
+                         "nvidia-smi needs some load to look at; 2 s of back-to-back 6.5 TB/s passes run into sw_power_cap "
+                         "and cost the kernel 2-3 %%, so the pre-roll is kept short)")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)
