@@ -25,6 +25,9 @@
 // fp64 DMMA and DFMA both peak at 37.2 TFLOP/s on B200 (tools/fp64_peak.cu), so this pass is bound by the fp64 pipe,
 // not by HBM: 66 816 flop per row at d = 256 against 2 056 B.
 #include <algorithm>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
 #include <vector>
 
 #include "device_utils.cuh"
@@ -47,9 +50,10 @@ struct __align__(16) GramStage {
   double a[GT][GKC];       // column block bi
   double b[GT][GKC];       // column block bj (unused on diagonal pairs)
   double border[8][GKC];   // column 0 = sqrt(w) y, 1 = sqrt(w) keep, 2 = w keep, 3 = keep (w = 1 unweighted); 4..7 stay zero
-  double wt[GKC];          // weight chunk, replaced by sqrt(w) * keep during the fix-up (weighted fits only)
-  double dqp[GKC];         // DQ price chunk
-  int dqg[GKC];            // DQ guest chunk
+  // one copy per producer warp of gram_ws_kernel (the legacy kernel uses copy 0)
+  double wt[2][GKC];       // weight chunk, replaced by sqrt(w) * keep during the fix-up (weighted fits only)
+  double dqp[2][GKC];      // DQ price chunk
+  int dqg[2][GKC];         // DQ guest chunk
 };
 constexpr size_t kGramSmem = GSTAGES * sizeof(GramStage) + 2 * GT * sizeof(void*) + 2 * GT + 2 * GT + 64;
 
@@ -165,10 +169,10 @@ __global__ void __launch_bounds__(GTHREADS, 2) gram_tile_kernel(const GramArgs g
     }
     if (diag && tid < 16) cp_async16(&S.border[0][0] + (tid << 1), g.label + row + tid * 2);  // y: border column 0 (col & 7 == 0: no swizzle)
     if (g.has_dq) {
-      if (tid >= 32 && tid < 48) cp_async16(&S.dqp[(tid - 32) * 2], g.dq_price + row + (tid - 32) * 2);
-      if (tid >= 64 && tid < 72) cp_async16(&S.dqg[(tid - 64) * 4], g.dq_guest + row + (tid - 64) * 4);
+      if (tid >= 32 && tid < 48) cp_async16(&S.dqp[0][(tid - 32) * 2], g.dq_price + row + (tid - 32) * 2);
+      if (tid >= 64 && tid < 72) cp_async16(&S.dqg[0][(tid - 64) * 4], g.dq_guest + row + (tid - 64) * 4);
     }
-    if (W && tid >= 96 && tid < 112) cp_async16(&S.wt[(tid - 96) * 2], g.weight + row + (tid - 96) * 2);
+    if (W && tid >= 96 && tid < 112) cp_async16(&S.wt[0][(tid - 96) * 2], g.weight + row + (tid - 96) * 2);
   };
 
   const int wm = warp >> 1, wn = warp & 1;
@@ -193,15 +197,15 @@ __global__ void __launch_bounds__(GTHREADS, 2) gram_tile_kernel(const GramArgs g
     }
     if (warp == 0) {
       bool keep = lane < rows_valid;
-      if (keep && g.has_dq) keep = dq_keep(S.dqg[lane], S.dqp[lane], g.t);
+      if (keep && g.has_dq) keep = dq_keep(S.dqg[0][lane], S.dqp[0][lane], g.t);
       const unsigned m = __ballot_sync(0xffffffffu, keep);
       if (lane == 0) *mask_slot = static_cast<int>(m);
       // WeightedLeastSquares.Aggregator: wSum += w, wwSum += w^2, bSum += w y, aSum += w x, aaSum += w x x^T.  Every row of
       // the chunk is scaled by sqrt(w) below, so Z^T Z carries the weights; count and wwSum ride in two more border columns.
       if constexpr (W) {
-        const double w = keep ? S.wt[lane] : 0.0;
+        const double w = keep ? S.wt[0][lane] : 0.0;
         const double sw = sqrt(w);
-        S.wt[lane] = sw;
+        S.wt[0][lane] = sw;
         if (diag) {
           S.border[1][swz(1, lane)] = sw;
           S.border[2][swz(2, lane)] = w;
@@ -225,7 +229,7 @@ __global__ void __launch_bounds__(GTHREADS, 2) gram_tile_kernel(const GramArgs g
     if constexpr (W) {  // scale every row of both panels and of y by sqrt(w): the same 16-byte pieces this thread staged
       const int pch = tid & 15, slot_base = tid >> 4;
       const int lch = pch ^ ((slot_base & 7) << 1);  // logical chunk held at physical position pch: rows 2 lch, 2 lch + 1
-      const double s0 = S.wt[2 * lch], s1 = S.wt[2 * lch + 1];
+      const double s0 = S.wt[0][2 * lch], s1 = S.wt[0][2 * lch + 1];
       for (int slot = slot_base; slot < n_slots; slot += 8) {
         double2* q = reinterpret_cast<double2*>((slot < GT ? S.a[slot] : S.b[slot - GT]) + 2 * pch);
         double2 v = *q;
@@ -233,7 +237,7 @@ __global__ void __launch_bounds__(GTHREADS, 2) gram_tile_kernel(const GramArgs g
         v.y *= s1;
         *q = v;
       }
-      if (diag && tid < GKC) S.border[0][swz(0, tid)] *= S.wt[tid];
+      if (diag && tid < GKC) S.border[0][swz(0, tid)] *= S.wt[0][tid];
       __syncthreads();
     }
     const double(*A)[GKC] = S.a;
@@ -297,9 +301,9 @@ __global__ void __launch_bounds__(GTHREADS, 2) gram_tile_kernel(const GramArgs g
     }
     if (tid < GKC) {
       S.border[0][swz(0, tid)] = (diag && tid < tail_rows) ? g.label[row0 + tid] : 0.0;
-      S.dqg[tid] = (g.has_dq && tid < tail_rows) ? g.dq_guest[row0 + tid] : 0;
-      S.dqp[tid] = (g.has_dq && tid < tail_rows) ? g.dq_price[row0 + tid] : 0.0;
-      if (W) S.wt[tid] = tid < tail_rows ? g.weight[row0 + tid] : 0.0;
+      S.dqg[0][tid] = (g.has_dq && tid < tail_rows) ? g.dq_guest[row0 + tid] : 0;
+      S.dqp[0][tid] = (g.has_dq && tid < tail_rows) ? g.dq_price[row0 + tid] : 0.0;
+      if (W) S.wt[0][tid] = tid < tail_rows ? g.weight[row0 + tid] : 0.0;
     }
     __syncthreads();
     consume(S, &s_meta[4], false, tail_rows);
@@ -324,10 +328,469 @@ __global__ void __launch_bounds__(GTHREADS, 2) gram_tile_kernel(const GramArgs g
   }
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// Round 2: the same pass with the staging and the fix-up moved to a producer warp, and balanced diagonal CTAs.
+//
+//   * 160 threads: warps 0..3 only multiply, warp 4 stages and fixes up.  A stage goes producer -> consumers through
+//     a `full` mbarrier (32 arrivals: the producer lanes after their copies have landed and the chunk is fixed up) and
+//     back through an `empty` mbarrier (4 arrivals: one per consumer warp), so the four MMA warps never meet at a
+//     CTA-wide barrier and never wait for the mask, the int32 widening or the sqrt(w) scaling;
+//   * a diagonal pair needs only the upper triangle of its 64 x 64 tile: 36 of the 64 fragments, plus 8 border
+//     fragments and the corner.  Warp w takes fragment rows w and 7 - w (11 fragments each, 12 with the corner), i.e.
+//     a diagonal CTA costs 12/16 of an off-diagonal one per chunk and executes no sub-diagonal flop outside the 8 x 8
+//     diagonal fragments themselves;
+//   * because the two kinds of CTA now differ in cost, the row slices are handed out in proportion (s_diag slices per
+//     diagonal pair, s_off per off-diagonal pair, chosen on the host so that both kinds walk the rows at the same
+//     pace), and the producer warps keep the kinds within `lead` chunks of each other through one progress counter
+//     per pair: CTAs of different pairs read the same rows at about the same time and share them through L2.
+constexpr int GWS_THREADS = 192;  // 4 MMA warps + 2 producer warps
+constexpr int GWS_MMA_WARPS = 4;
+constexpr double kDiagCost = 12.0;  // cost of a diagonal sub-CTA per chunk on the scale where an off-diagonal one costs 16
+constexpr size_t kGramWsSmem = (kGramSmem + 64 + 2 * GT * sizeof(void*) + 127) & ~static_cast<size_t>(127);  // one sub-CTA: + the stage mbarriers and the fp64-only pointer table
+
+struct GramWsArgs {
+  GramArgs g;
+  int s_diag, s_off, s_max;       // row slices per diagonal / off-diagonal pair; partial slot stride
+  unsigned long long* progress;   // [kinds] chunks issued per pair, zeroed before the launch; nullptr = no pacing
+  int lead;                       // a producer does not run more than this many chunks ahead of the slowest pair
+  int debug;                      // DQ4ML_GRAM_DEBUG=1: slice 0 of every pair prints its run time
+};
+
+__device__ __forceinline__ void mbar_init(unsigned bar, unsigned count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(unsigned bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+// Waits for the phase with the given parity.  A pipeline bug would otherwise hang the GPU: after ~2^31 polls the CTA
+// traps, which fails the launch with an error instead.
+__device__ __forceinline__ void mbar_wait(unsigned bar, unsigned parity) {
+  unsigned done = 0, polls = 0;
+  do {
+    asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                 : "=r"(done) : "r"(bar), "r"(parity) : "memory");
+    if (!done && ++polls == 0x7fffffffu) __trap();
+  } while (!done);
+}
+__device__ __forceinline__ unsigned long long ld_relaxed_gpu(const unsigned long long* p) {
+  unsigned long long v;
+  asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ unsigned long long global_timer_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+
+// The MMAs of warp WQ of a diagonal CTA over one staged chunk: fragment rows r0 = WQ and r1 = 7 - WQ of the upper
+// triangle, the border fragment of both rows, and (warp 3 of pair (0,0)) the corner.  acc[] is used flat:
+//   [0 .. 7-WQ]          (r0, r0 + t)      [8-WQ]      (r0, border)
+//   [9-WQ .. 9]          (r1, r1 + t)      [10]        (r1, border)       [11]  corner
+template <int WQ>
+__device__ __forceinline__ void diag_chunk_mma(const GramStage& S, double (&acc)[16][2], int lane, bool corner) {
+  constexpr int R0 = WQ, R1 = 7 - WQ;
+  const int fr = lane >> 2, fk = lane & 3, sw = fr << 1;
+#pragma unroll
+  for (int k0 = 0; k0 < GKC; k0 += 4) {
+    const int off = (((((k0 + fk) >> 1) ^ sw) << 1) | (fk & 1));
+    double f[8];  // f[j]: fragment of column block j (A and B operand are the same data on a diagonal pair)
+#pragma unroll
+    for (int j = R0; j < 8; ++j) f[j] = S.a[j * 8 + fr][off];
+    const double bb = S.border[fr][off];
+#pragma unroll
+    for (int j = R0; j < 8; ++j) dmma884(acc[j - R0], f[R0], f[j]);
+    dmma884(acc[8 - WQ], f[R0], bb);
+#pragma unroll
+    for (int j = R1; j < 8; ++j) dmma884(acc[9 - WQ + (j - R1)], f[R1], f[j]);
+    dmma884(acc[10], f[R1], bb);
+    if (WQ == 3 && corner) dmma884(acc[11], bb, bb);
+  }
+}
+
+template <int WQ>
+__device__ __forceinline__ void diag_store(double* P, const double (&acc)[16][2], int lane, bool corner) {
+  constexpr int R0 = WQ, R1 = 7 - WQ;
+  const int fr = lane >> 2, fc = (lane & 3) * 2;
+#pragma unroll
+  for (int j = R0; j < 8; ++j)
+    *reinterpret_cast<double2*>(&P[(R0 * 8 + fr) * GT + j * 8 + fc]) = make_double2(acc[j - R0][0], acc[j - R0][1]);
+  *reinterpret_cast<double2*>(&P[GT * GT + (R0 * 8 + fr) * 8 + fc]) = make_double2(acc[8 - WQ][0], acc[8 - WQ][1]);
+#pragma unroll
+  for (int j = R1; j < 8; ++j)
+    *reinterpret_cast<double2*>(&P[(R1 * 8 + fr) * GT + j * 8 + fc]) =
+        make_double2(acc[9 - WQ + (j - R1)][0], acc[9 - WQ + (j - R1)][1]);
+  *reinterpret_cast<double2*>(&P[GT * GT + (R1 * 8 + fr) * 8 + fc]) = make_double2(acc[10][0], acc[10][1]);
+  if (WQ == 3 && corner) *reinterpret_cast<double2*>(&P[GT * GT + GT * 8 + fr * 8 + fc]) = make_double2(acc[11][0], acc[11][1]);
+}
+
+// dq_keep() on the bit pattern of the price.  The producer warps share their SM's fp64 pipe with the DMMAs, which keep
+// it saturated: a DSETP of the producer waited for it for ~27 % of the producer's time (profiles/r2_gram_ws_full.json
+// history in profiles/README.md), on the path that hands a chunk to the MMA warps.  Same truth table as dq_keep():
+//   keep  <=>  !(price < min_price) && !(price <= 0) && !(guest < min_guest && price > max_price),  IEEE compares
+// (false whenever an operand is NaN).  key() maps a non-NaN double to an unsigned integer with the same order; -0.0
+// is folded into +0.0 first because the two compare equal.
+struct DqKeys {
+  unsigned long long min_price, max_price;  // keys of the thresholds
+  bool min_nan, max_nan;
+  int min_guest;
+};
+__host__ __device__ __forceinline__ bool f64_bits_nan(unsigned long long b) { return (b & 0x7fffffffffffffffULL) > 0x7ff0000000000000ULL; }
+__host__ __device__ __forceinline__ unsigned long long f64_key(unsigned long long b) {
+  if ((b << 1) == 0ULL) b = 0ULL;
+  return (b >> 63) ? ~b : (b | 0x8000000000000000ULL);
+}
+__device__ __forceinline__ DqKeys make_dq_keys(const DqThresholds& t) {
+  DqKeys k;
+  const unsigned long long bmin = static_cast<unsigned long long>(__double_as_longlong(t.min_price));
+  const unsigned long long bmax = static_cast<unsigned long long>(__double_as_longlong(t.max_price));
+  k.min_price = f64_key(bmin);
+  k.max_price = f64_key(bmax);
+  k.min_nan = f64_bits_nan(bmin);
+  k.max_nan = f64_bits_nan(bmax);
+  k.min_guest = t.min_guest;
+  return k;
+}
+__device__ __forceinline__ bool dq_keep_bits(int guest, unsigned long long price_bits, const DqKeys& k) {
+  if (f64_bits_nan(price_bits)) return true;  // every IEEE compare is false: the row passes both rules and both filters
+  const unsigned long long key = f64_key(price_bits);
+  const bool lt_min = !k.min_nan && key < k.min_price;
+  const bool le_zero = key <= 0x8000000000000000ULL;
+  const bool gt_max = !k.max_nan && key > k.max_price;
+  return !lt_min && !le_zero && !(guest < k.min_guest && gt_max);
+}
+
+template <bool W>
+__global__ void __launch_bounds__(2 * GWS_THREADS, 1) gram_ws_kernel(const GramWsArgs a) {
+  const GramArgs& g = a.g;
+  extern __shared__ __align__(128) unsigned char smem_all[];
+  // one CTA per SM = two independent halves ("sub-CTAs": 4 MMA warps + 2 producer warps, own stages and mbarriers).
+  // Two sub-CTAs share the SM's DMMA pipe, and a pair of different kinds does not finish together (measured: an
+  // off-diagonal CTA next to a diagonal one ends at 117 ms, its neighbour at 139 ms, and the pipe is half idle in
+  // between), so both halves of a CTA always work on the same block pair: adjacent row slices of it.
+  const int sub = threadIdx.x / GWS_THREADS;
+  unsigned char* smem_raw = smem_all + sub * kGramWsSmem;
+  GramStage* st = reinterpret_cast<GramStage*>(smem_raw);
+  const void** s_colptr = reinterpret_cast<const void**>(smem_raw + GSTAGES * sizeof(GramStage));  // [2*GT]: A slots then B slots
+  unsigned char* s_isint = reinterpret_cast<unsigned char*>(s_colptr + 2 * GT);                    // [2*GT]
+  unsigned char* s_intslots = s_isint + 2 * GT;                                                    // [2*GT] compact list of int32 slots
+  int* s_meta = reinterpret_cast<int*>(s_intslots + 2 * GT);                                       // [0] = #int slots
+  unsigned long long* s_bar = reinterpret_cast<unsigned long long*>(s_meta + 16);                  // full[GSTAGES], empty[GSTAGES]
+  const void** s_f64ptr = reinterpret_cast<const void**>(s_bar + 2 * GSTAGES + 2);                 // [2*GT]: s_colptr with the int32 slots nulled
+
+  const int tid = threadIdx.x - sub * GWS_THREADS, warp = tid >> 5, lane = tid & 31;
+  const unsigned long long t_start = a.debug ? global_timer_ns() : 0ULL;
+  // sub-CTA -> (pair, row slice), pair-major: s_diag / s_off are even, so the two halves of a CTA get slices 2c and
+  // 2c + 1 of the same pair
+  int kind = 0, split = static_cast<int>(blockIdx.x) * 2 + sub;
+  bool active = false;
+  for (int i = 0, k = 0; i < g.nb && !active; ++i)
+    for (int j = i; j < g.nb; ++j, ++k) {
+      const int sk = i == j ? a.s_diag : a.s_off;
+      if (split < sk) { kind = k; active = true; break; }
+      split -= sk;
+    }
+  int bi = 0, bj = 0;
+  {
+    int k = kind;
+    for (bi = 0;; ++bi) {
+      const int row_len = g.nb - bi;
+      if (k < row_len) { bj = bi + k; break; }
+      k -= row_len;
+    }
+  }
+  const bool diag = bi == bj;
+  const int my_splits = diag ? a.s_diag : a.s_off;
+  const int n_slots = diag ? GT : 2 * GT;
+
+  for (int i = tid; i < static_cast<int>(GSTAGES * sizeof(GramStage) / 8); i += GWS_THREADS) reinterpret_cast<double*>(smem_raw)[i] = 0.0;
+  if (tid < 2 * GT) {
+    const int col = (tid < GT ? bi : bj) * GT + (tid & (GT - 1));
+    const bool live = active && tid < n_slots && col < g.d;
+    s_colptr[tid] = live ? g.col_ptr[col] : nullptr;
+    s_isint[tid] = live ? g.col_i32[col] : 0;
+    s_f64ptr[tid] = (live && g.col_i32[col] == 0) ? g.col_ptr[col] : nullptr;
+  }
+  if (tid == 0) {
+    for (int s = 0; s < GSTAGES; ++s) {
+      mbar_init(smem_u32(&s_bar[s]), 64);                        // full: every lane of both producer warps
+      mbar_init(smem_u32(&s_bar[GSTAGES + s]), GWS_MMA_WARPS);   // empty: one lane of every MMA warp
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+  if (tid == 0) {
+    int m = 0;
+    for (int s = 0; s < n_slots; ++s)
+      if (s_isint[s]) s_intslots[m++] = static_cast<unsigned char>(s);
+    s_meta[0] = m;
+  }
+  __syncthreads();
+  if (!active) return;  // the odd half of the last CTA when the slice count is odd (n < 64 rows)
+  const int n_int = s_meta[0];
+
+  const long long full_chunks = g.n / GKC;
+  const long long my_iters = full_chunks > split ? (full_chunks - split + my_splits - 1) / my_splits : 0;
+  const int tail_rows = static_cast<int>(g.n - full_chunks * GKC);
+  const bool has_tail = tail_rows > 0 && static_cast<int>(full_chunks % my_splits) == split;
+  const long long total = my_iters + (has_tail ? 1 : 0);  // the tail chunk (n % 32 rows) is one more, shorter, stage
+
+  if (warp >= GWS_MMA_WARPS) {
+    // ======================================================================================== producer warps
+    // Producer p stages and fixes up half of the column slots (off the diagonal: p = 0 the A panel, p = 1 the B
+    // panel); each keeps its own copy of the chunk's DQ columns and weights, so neither waits for the other's copies.
+    const int pw = warp - GWS_MMA_WARPS;
+    const int slot_lo = pw * (n_slots / 2), slot_hi = slot_lo + n_slots / 2;
+    const int ch = lane & 15, half = lane >> 4;
+    bool pacing = a.progress != nullptr && pw == 0;
+    const DqKeys keys = make_dq_keys(g.t);
+    // all of this warp's slots are live fp64 columns: the copy loop needs no per-slot test
+    bool plain = true;
+    for (int sl = slot_lo; sl < slot_hi; ++sl) plain = plain && s_f64ptr[sl] != nullptr;
+    int my_int = 0;  // does this warp own an int32 slot at all
+    for (int q = 0; q < n_int; ++q) my_int += (s_intslots[q] >= slot_lo && s_intslots[q] < slot_hi) ? 1 : 0;
+    // destination of this lane's piece of slot s0 + 2u relative to slot s0 - half (a multiple of 16, so the swizzle
+    // term depends on u alone): the column's 256-byte row, chunk position XOR-ed with twice the slot's index mod 8
+    unsigned dst_off[8];
+#pragma unroll
+    for (int u = 0; u < 8; ++u) dst_off[u] = static_cast<unsigned>((half + 2 * u) * 256 + ((ch ^ (((half + 2 * u) & 7) << 1)) << 4));
+    // stage `it`: cp.async for a full chunk, plain loads for the tail
+    auto fill = [&](long long it, int stage) {
+      GramStage& S = st[stage];
+      if (it < my_iters) {
+        const long long row = (split + it * my_splits) * GKC;
+        const unsigned sbase = smem_u32(&S.a[0][0]);
+        // two column chunks (2 x 16 pieces of 16 bytes) per warp instruction; the column pointers of eight
+        // instructions are fetched from shared memory first, so that the copies are not issued one shared-memory
+        // latency apart (no "memory" clobber on the copies themselves: wait_group carries it).  int32 columns are
+        // null in s_f64ptr and follow in their own short loop.
+        const long long src_off = row * 8 + ch * 16;
+        for (int s0 = slot_lo + half; s0 < slot_hi; s0 += 16) {
+          const char* base[8];
+#pragma unroll
+          for (int u = 0; u < 8; ++u) base[u] = static_cast<const char*>(s_f64ptr[s0 + 2 * u]);
+          const unsigned dst0 = sbase + (s0 - half) * 256u;
+          if (plain) {
+#pragma unroll
+            for (int u = 0; u < 8; ++u) asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst0 + dst_off[u]), "l"(base[u] + src_off));
+          } else {
+#pragma unroll
+            for (int u = 0; u < 8; ++u)
+              if (base[u] != nullptr) asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst0 + dst_off[u]), "l"(base[u] + src_off));
+          }
+        }
+        if (my_int > 0 && ch < 8) {  // an int32 chunk is 128 B: 8 pieces, parked in the upper half of the row until widened
+          for (int q = half; q < n_int; q += 2) {
+            const int slot = s_intslots[q];
+            if (slot >= slot_lo && slot < slot_hi)
+              asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(sbase + slot * 256u + 128u + ch * 16u),
+                           "l"(static_cast<const char*>(s_colptr[slot]) + row * 4 + ch * 16));
+          }
+        }
+        if (diag && pw == 0 && lane < 16) cp_async16(&S.border[0][0] + (lane << 1), g.label + row + lane * 2);  // y: border column 0 (no swizzle)
+        if (g.has_dq) {
+          if (lane >= 16) cp_async16(&S.dqp[pw][(lane - 16) * 2], g.dq_price + row + (lane - 16) * 2);
+          if (lane < 8) cp_async16(&S.dqg[pw][lane * 4], g.dq_guest + row + lane * 4);
+        }
+        if (W && lane >= 16) cp_async16(&S.wt[pw][(lane - 16) * 2], g.weight + row + (lane - 16) * 2);
+      } else {
+        const long long row0 = full_chunks * GKC;
+        for (int slot = slot_lo; slot < slot_hi; ++slot) {
+          double v = 0.0;
+          if (s_colptr[slot] != nullptr && lane < tail_rows)
+            v = s_isint[slot] ? static_cast<double>(static_cast<const int*>(s_colptr[slot])[row0 + lane])
+                              : static_cast<const double*>(s_colptr[slot])[row0 + lane];
+          (slot < GT ? S.a[slot] : S.b[slot - GT])[swz(slot, lane)] = v;
+        }
+        if (pw == 0) S.border[0][swz(0, lane)] = (diag && lane < tail_rows) ? g.label[row0 + lane] : 0.0;
+        S.dqg[pw][lane] = (g.has_dq && lane < tail_rows) ? g.dq_guest[row0 + lane] : 0;
+        S.dqp[pw][lane] = (g.has_dq && lane < tail_rows) ? g.dq_price[row0 + lane] : 0.0;
+        if (W) S.wt[pw][lane] = lane < tail_rows ? g.weight[row0 + lane] : 0.0;
+      }
+    };
+    // everything the MMA warps must not see raw: int32 -> fp64, the DQ predicate (dropped rows are zeroed, the ones
+    // column becomes the keep mask) and the sqrt(w) scaling.  lane = row of the chunk.
+    auto fix_up = [&](long long it, int stage) {
+      GramStage& S = st[stage];
+      const bool is_tail = it >= my_iters;
+      if (!is_tail && my_int > 0) {
+        for (int q = 0; q < n_int; ++q) {
+          const int slot = s_intslots[q];
+          if (slot < slot_lo || slot >= slot_hi) continue;
+          double* row = slot < GT ? S.a[slot] : S.b[slot - GT];
+          const int v = reinterpret_cast<const int*>(row)[GKC + lane];
+          __syncwarp();
+          row[swz(slot, lane)] = static_cast<double>(v);
+        }
+        __syncwarp();
+      }
+      bool keep = lane < (is_tail ? tail_rows : GKC);
+      if (keep && g.has_dq) keep = dq_keep_bits(S.dqg[pw][lane], reinterpret_cast<const unsigned long long*>(S.dqp[pw])[lane], keys);
+      const unsigned dropped = ~__ballot_sync(0xffffffffu, keep);
+      // WeightedLeastSquares.Aggregator: wSum += w, wwSum += w^2, bSum += w y, aSum += w x, aaSum += w x x^T.  Every row of
+      // the chunk is scaled by sqrt(w) below, so Z^T Z carries the weights; count and wwSum ride in two more border columns.
+      if constexpr (W) {
+        const double w = keep ? S.wt[pw][lane] : 0.0;
+        const double sw = sqrt(w);
+        S.wt[pw][lane] = sw;
+        if (diag && pw == 0) {
+          S.border[1][swz(1, lane)] = sw;
+          S.border[2][swz(2, lane)] = w;
+          S.border[3][swz(3, lane)] = keep ? 1.0 : 0.0;
+        }
+      } else {
+        if (diag && pw == 0) S.border[1][swz(1, lane)] = keep ? 1.0 : 0.0;  // count = wSum = wwSum: one border column is enough
+      }
+      for (unsigned m = dropped; m != 0u; m &= m - 1u) {
+        const int r = __ffs(m) - 1;
+        for (int slot = slot_lo + lane; slot < slot_hi; slot += 32) (slot < GT ? S.a[slot] : S.b[slot - GT])[swz(slot, r)] = 0.0;
+        if (diag && pw == 0 && lane == 0) S.border[0][swz(0, r)] = 0.0;
+      }
+      if constexpr (W) {
+        __syncwarp();
+        // piece p of a slot holds rows 2 lch, 2 lch + 1 with lch = p ^ ((slot & 7) << 1)
+        double* panel = &S.a[0][0];
+#pragma unroll 4
+        for (int slot = slot_lo + half; slot < slot_hi; slot += 2) {
+          const int lch = ch ^ ((slot & 7) << 1);
+          double2* q = reinterpret_cast<double2*>(panel + slot * GKC + 2 * ch);
+          double2 v = *q;
+          v.x *= S.wt[pw][2 * lch];
+          v.y *= S.wt[pw][2 * lch + 1];
+          *q = v;
+        }
+        if (diag && pw == 0) S.border[0][swz(0, lane)] *= S.wt[pw][lane];
+      }
+    };
+    // pacing: one counter per pair holds the chunks its CTAs have issued; a producer that is more than `lead` chunks
+    // ahead of the slowest pair sleeps (bounded: after 200 us it stops pacing for good, a stalled pair must not hang it)
+    unsigned long long seen = 0;  // the slowest pair's counter as this warp last read it (read one iteration early)
+    auto read_progress = [&]() {
+      unsigned long long lo = ~0ULL;
+      for (int k = lane; k < g.kinds; k += 32) {
+        const unsigned long long v = ld_relaxed_gpu(a.progress + k);
+        lo = v < lo ? v : lo;
+      }
+      return lo;
+    };
+    auto warp_min = [&](unsigned long long lo) {
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        const unsigned long long other = __shfl_xor_sync(0xffffffffu, lo, o);
+        lo = other < lo ? other : lo;
+      }
+      return lo;
+    };
+    auto pace = [&](long long it) {
+      if (!pacing) return;
+      if ((it & 3) == 3) seen = read_progress();  // consumed one iteration later: the load latency stays off the critical path
+      if ((it & 3) != 0) return;
+      if (lane == 0) atomicAdd(a.progress + kind, 4ULL);
+      const long long my_chunk = split + it * my_splits;
+      unsigned long long lo = warp_min(seen);
+      unsigned long long t0 = 0;
+      while (my_chunk > static_cast<long long>(lo) + a.lead) {
+        const unsigned long long now = global_timer_ns();
+        if (t0 == 0) t0 = now;
+        if (now - t0 > 200000ULL) { pacing = false; break; }
+        __nanosleep(500);
+        lo = warp_min(read_progress());
+      }
+    };
+
+    for (int pre = 0; pre < GSTAGES - 1; ++pre) {
+      if (pre < total) fill(pre, pre);
+      cp_async_commit();
+    }
+    int stage = 0, fill_stage = GSTAGES - 1;  // it % GSTAGES and (it + GSTAGES - 1) % GSTAGES, kept as counters
+    unsigned fill_round = 0;                  // (it + GSTAGES - 1) / GSTAGES
+    for (long long it = 0; it < total; ++it) {
+      cp_async_wait<GSTAGES - 2>();  // this lane's copies of chunk `it` have landed ...
+      __syncwarp();                  // ... and every lane's
+      fix_up(it, stage);
+      mbar_arrive(smem_u32(&s_bar[stage]));  // release: the 64 arrivals publish the chunk to the MMA warps
+      const long long nxt = it + GSTAGES - 1;
+      if (nxt < total) {
+        if (fill_round > 0) mbar_wait(smem_u32(&s_bar[GSTAGES + fill_stage]), (fill_round - 1u) & 1u);  // chunk it-1 is consumed
+        pace(nxt);
+        fill(nxt, fill_stage);
+      }
+      cp_async_commit();
+      stage = stage == GSTAGES - 1 ? 0 : stage + 1;
+      if (fill_stage == GSTAGES - 1) { fill_stage = 0; ++fill_round; } else { ++fill_stage; }
+    }
+    cp_async_wait<0>();
+    return;
+  }
+
+  // ========================================================================================== MMA warps
+  double acc[16][2];
+#pragma unroll
+  for (int i = 0; i < 16; ++i) acc[i][0] = acc[i][1] = 0.0;
+  const int wm = warp >> 1, wn = warp & 1;
+  const bool corner = bi == 0;
+  int s = 0;
+  unsigned phase = 0;
+  for (long long it = 0; it < total; ++it) {
+    mbar_wait(smem_u32(&s_bar[s]), phase);
+    const GramStage& S = st[s];
+    if (!diag) {
+      const int fr = lane >> 2, fk = lane & 3, sw = fr << 1;
+#pragma unroll
+      for (int k0 = 0; k0 < GKC; k0 += 4) {
+        const int off = (((((k0 + fk) >> 1) ^ sw) << 1) | (fk & 1));
+        double af[4], bf[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) af[i] = S.a[wm * 32 + i * 8 + fr][off];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) bf[j] = S.b[wn * 32 + j * 8 + fr][off];
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+#pragma unroll
+          for (int j = 0; j < 4; ++j) dmma884(acc[i * 4 + j], af[i], bf[j]);
+      }
+    } else {
+      switch (warp) {
+        case 0: diag_chunk_mma<0>(S, acc, lane, corner); break;
+        case 1: diag_chunk_mma<1>(S, acc, lane, corner); break;
+        case 2: diag_chunk_mma<2>(S, acc, lane, corner); break;
+        default: diag_chunk_mma<3>(S, acc, lane, corner); break;
+      }
+    }
+    __syncwarp();
+    if (lane == 0) mbar_arrive(smem_u32(&s_bar[GSTAGES + s]));
+    if (s == GSTAGES - 1) { s = 0; phase ^= 1u; } else { ++s; }
+  }
+
+  if (a.debug && split == 0 && tid == 0)
+    printf("gram_ws pair %d (%d,%d) slices %d iters %lld: %.3f ms\n", kind, bi, bj, my_splits, total, (global_timer_ns() - t_start) * 1e-6);
+  // -------------------------------------------------------------------- partial tile -> scratch slot [pair][slice]
+  double* P = g.partials + (static_cast<size_t>(kind) * a.s_max + split) * GPART;
+  if (!diag) {
+    const int fr = lane >> 2, fc = (lane & 3) * 2;
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int r = wm * 32 + i * 8 + fr, c = wn * 32 + j * 8 + fc;
+        *reinterpret_cast<double2*>(&P[r * GT + c]) = make_double2(acc[i * 4 + j][0], acc[i * 4 + j][1]);
+      }
+  } else {
+    switch (warp) {
+      case 0: diag_store<0>(P, acc, lane, corner); break;
+      case 1: diag_store<1>(P, acc, lane, corner); break;
+      case 2: diag_store<2>(P, acc, lane, corner); break;
+      default: diag_store<3>(P, acc, lane, corner); break;
+    }
+  }
+}
+
 // Sums the row slices in a fixed order and lays the result out as
 // [count, wSum, wwSum, bSum, bbSum, aSum[d], abSum[d], aaSum packed upper column-major].
+// Partial slots: [pair][slice] with stride s_max (s_diag slices for diagonal pairs, s_off for the others); the legacy
+// kernel's layout is [slice][pair] with the same number of slices for every pair (s_max = 0).
 __global__ void __launch_bounds__(256) gram_reduce_kernel(const double* __restrict__ partials, int d, int nb, int kinds,
-                                                          int splits, long long len, int weighted,
+                                                          int s_diag, int s_off, int s_max, long long len, int weighted,
                                                           double* __restrict__ out) {
   const long long e = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
   if (e >= len) return;
@@ -354,8 +817,13 @@ __global__ void __launch_bounds__(256) gram_reduce_kernel(const double* __restri
     off = static_cast<int>(i % GT) * GT + static_cast<int>(j % GT);
   }
   const int kind = bi * nb - bi * (bi - 1) / 2 + (bj - bi);
+  const int splits = bi == bj ? s_diag : s_off;
   double s = 0.0;
-  for (int sp = 0; sp < splits; ++sp) s += partials[(static_cast<size_t>(sp) * kinds + kind) * GPART + off];
+  if (s_max > 0) {
+    for (int sp = 0; sp < splits; ++sp) s += partials[(static_cast<size_t>(kind) * s_max + sp) * GPART + off];
+  } else {
+    for (int sp = 0; sp < splits; ++sp) s += partials[(static_cast<size_t>(sp) * kinds + kind) * GPART + off];
+  }
   out[e] = s;
 }
 
@@ -372,10 +840,34 @@ int gram_wls_moments(dq4ml_ctx* ctx, const std::vector<const void*>& col_ptrs, c
   int64_t splits = (2LL * ctx->sm_count) / kinds;
   if (splits > full_chunks) splits = full_chunks;
   if (splits < 1) splits = 1;
+  // Producer-warp kernel: slices in proportion to the cost of a pair (12 fragments per warp and chunk on the diagonal,
+  // 16 off it), chosen so that the slower kind is as fast as possible within one resident wave.
+  static const char* kernel_env = std::getenv("DQ4ML_GRAM_KERNEL");
+  const bool legacy = kernel_env != nullptr && std::strcmp(kernel_env, "legacy") == 0;
+  static const char* pace_env = std::getenv("DQ4ML_GRAM_PACE");
+  const int lead = pace_env != nullptr ? std::atoi(pace_env) : 256;
+  int s_diag = 1, s_off = 1;
+  {
+    const int n_diag = nb, n_off = kinds - nb, cap = 2 * ctx->sm_count;
+    double best = -1.0;
+    for (int sd = 2; sd * n_diag + (n_off > 0 ? 2 * n_off : 0) <= cap; sd += 2) {  // even: both halves of a CTA on one pair
+      const int so = n_off > 0 ? ((cap - sd * n_diag) / n_off) & ~1 : 0;
+      const double pace = n_off > 0 ? std::min(sd / kDiagCost, so / 16.0) : sd / kDiagCost;
+      if (pace >= best) { best = pace; s_diag = sd; s_off = so; }  // on a tie the split that fills more SMs
+    }
+    static const char* slices_env = std::getenv("DQ4ML_GRAM_SLICES");  // "s_diag,s_off": tuning only
+    if (slices_env != nullptr) std::sscanf(slices_env, "%d,%d", &s_diag, &s_off);
+    if (s_diag > full_chunks) s_diag = static_cast<int>(std::max<int64_t>(full_chunks, 1));
+    if (s_off > full_chunks) s_off = static_cast<int>(std::max<int64_t>(full_chunks, 1));
+    if (n_off == 0) s_off = 0;
+  }
+  const int s_max = std::max(s_diag, s_off);
+  const int64_t ws_blocks = static_cast<int64_t>(s_diag) * nb + static_cast<int64_t>(s_off) * (kinds - nb);
+  if (!legacy) splits = s_max;  // sizes the partial scratch: kinds * s_max slots
   const size_t table_bytes = (static_cast<size_t>(d) * 9 + 255) & ~static_cast<size_t>(255);
   const size_t part_bytes = static_cast<size_t>(splits) * kinds * GPART * sizeof(double);
   const size_t out_bytes = static_cast<size_t>(len) * sizeof(double);
-  const size_t need = table_bytes + part_bytes + out_bytes + 512;
+  const size_t need = table_bytes + part_bytes + out_bytes + 512 + 256 + static_cast<size_t>(kinds) * 8;  // + the pacing counters
   auto fail = [](cudaError_t e, const char* what) {
     set_error("%s: %s", what, cudaGetErrorString(e));
     return DQ4ML_ERR_CUDA;
@@ -401,6 +893,7 @@ int gram_wls_moments(dq4ml_ctx* ctx, const std::vector<const void*>& col_ptrs, c
   unsigned char* d_i32 = reinterpret_cast<unsigned char*>(base + static_cast<size_t>(d) * 8);
   double* d_part = reinterpret_cast<double*>(base + table_bytes);
   double* d_out = reinterpret_cast<double*>(base + table_bytes + part_bytes);
+  unsigned long long* d_progress = reinterpret_cast<unsigned long long*>(base + ((table_bytes + part_bytes + out_bytes + 255) & ~static_cast<size_t>(255)));
   std::vector<unsigned char> flags(d);
   for (int j = 0; j < d; ++j) flags[j] = dtypes[j] == DQ4ML_I32 ? 1 : 0;
   if ((e = cudaMemcpyAsync(d_ptrs, col_ptrs.data(), static_cast<size_t>(d) * 8, cudaMemcpyHostToDevice, ctx->stream)) != cudaSuccess) return fail(e, "column table upload");
@@ -430,14 +923,39 @@ int gram_wls_moments(dq4ml_ctx* ctx, const std::vector<const void*>& col_ptrs, c
       return fail(e, "gram smem attribute");
     if ((e = cudaFuncSetAttribute(gram_tile_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(kGramSmem))) != cudaSuccess)
       return fail(e, "gram smem attribute");
+    if ((e = cudaFuncSetAttribute(gram_ws_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(2 * kGramWsSmem))) != cudaSuccess)
+      return fail(e, "gram smem attribute");
+    if ((e = cudaFuncSetAttribute(gram_ws_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(2 * kGramWsSmem))) != cudaSuccess)
+      return fail(e, "gram smem attribute");
     attr_set[ctx->device] = true;
   }
+  GramWsArgs wa;
+  wa.g = g;
+  wa.s_diag = s_diag;
+  wa.s_off = s_off;
+  wa.s_max = s_max;
+  wa.progress = (lead > 0 && kinds > 1) ? d_progress : nullptr;
+  wa.lead = lead;
+  static const char* debug_env = std::getenv("DQ4ML_GRAM_DEBUG");
+  wa.debug = debug_env != nullptr && debug_env[0] == '1' ? 1 : 0;
+  if (!legacy && wa.progress != nullptr) {
+    if ((e = cudaMemsetAsync(d_progress, 0, static_cast<size_t>(kinds) * sizeof(unsigned long long), ctx->stream)) != cudaSuccess)
+      return fail(e, "gram pacing counters");
+  }
   if (ctx->pass_timing) cudaEventRecord(ctx->pass_ev0, ctx->stream);
-  if (weight != nullptr) gram_tile_kernel<true><<<static_cast<unsigned>(splits * kinds), GTHREADS, kGramSmem, ctx->stream>>>(g);
-  else gram_tile_kernel<false><<<static_cast<unsigned>(splits * kinds), GTHREADS, kGramSmem, ctx->stream>>>(g);
+  if (legacy) {
+    if (weight != nullptr) gram_tile_kernel<true><<<static_cast<unsigned>(splits * kinds), GTHREADS, kGramSmem, ctx->stream>>>(g);
+    else gram_tile_kernel<false><<<static_cast<unsigned>(splits * kinds), GTHREADS, kGramSmem, ctx->stream>>>(g);
+  } else {
+    const unsigned ws_grid = static_cast<unsigned>((ws_blocks + 1) / 2);
+    if (weight != nullptr) gram_ws_kernel<true><<<ws_grid, 2 * GWS_THREADS, 2 * kGramWsSmem, ctx->stream>>>(wa);
+    else gram_ws_kernel<false><<<ws_grid, 2 * GWS_THREADS, 2 * kGramWsSmem, ctx->stream>>>(wa);
+  }
   if ((e = cudaGetLastError()) != cudaSuccess) return fail(e, "gram tile kernel");
   ++ctx->launches;
-  gram_reduce_kernel<<<static_cast<unsigned>((len + 255) / 256), 256, 0, ctx->stream>>>(d_part, d, nb, kinds, static_cast<int>(splits), len, weight != nullptr ? 1 : 0, d_out);
+  gram_reduce_kernel<<<static_cast<unsigned>((len + 255) / 256), 256, 0, ctx->stream>>>(
+      d_part, d, nb, kinds, legacy ? static_cast<int>(splits) : s_diag, legacy ? static_cast<int>(splits) : s_off, legacy ? 0 : s_max, len,
+      weight != nullptr ? 1 : 0, d_out);
   if ((e = cudaGetLastError()) != cudaSuccess) return fail(e, "gram reduce kernel");
   ++ctx->launches;
   if (ctx->pass_timing) {

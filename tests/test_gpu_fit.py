@@ -299,6 +299,42 @@ def test_gram_nan_and_inf_rows(pkg, ctx):
     assert (np.isnan(ref) == np.isnan(got)).all() and got[0] == ref[0]
 
 
+def test_gram_dq_predicate_on_edge_prices(pkg, ctx):
+    """The Gram kernel's producer warps evaluate the two rules on the bit pattern of the price (no fp64 compare): every
+    edge of the IEEE ordering must come out as the oracle's fp64 compares do -- signed zeros, the thresholds
+    themselves and their neighbours, denormals, infinities, NaN with either sign."""
+    from sparkdq4ml_b200 import ml
+    d, n = 12, 4096 + 17
+    guest, price, feats = wide_table(n, d)
+    price = price.copy()
+    guest = guest.copy()
+    edges = [0.0, -0.0, 5e-324, -5e-324, 20.0, np.nextafter(20.0, 0), np.nextafter(20.0, 100), 90.0, np.nextafter(90.0, 0),
+             np.nextafter(90.0, 100), np.inf, -np.inf, np.nan, -np.nan, 1e308, -1e308, 2.2250738585072014e-308, 19.999999999, 90.000001]
+    k = 0
+    for g in (10, 13, 14, 15, 40):  # min_guest is 14: both sides of the correlation rule
+        for e in edges:
+            price[k * 7 + 3] = e
+            guest[k * 7 + 3] = g
+            k += 1
+    feats[0] = guest
+    from sparkdq4ml_b200 import _capi as capi
+    dfeats, dprice, dguest = to_dev(*feats), to_dev(price)[0], to_dev(guest)[0]
+    ref = passes.wls_moments(feats, price, dq=(guest, price))
+    got = ml.wls_moments(ctx, dfeats, dprice, dq=(dguest, dprice))
+    assert got[0] == ref[0]  # survivor count: the predicate agrees row for row on the planted edges
+    assert (np.isnan(ref) == np.isnan(got)).all()
+    # other thresholds (the oracle has the lab's constants only): the same truth table in numpy, IEEE compares
+    for min_price, max_price, min_guest in ((25.5, 60.25, 12), (-0.0, np.inf, 0), (0.0, 90.0, 14), (np.nan, np.nan, 14), (1e-310, 1e300, 41)):
+        with np.errstate(invalid="ignore"):
+            keep = ~(price < min_price) & ~(price <= 0.0) & ~((guest < min_guest) & (price > max_price))
+        ref = passes.wls_moments([np.ascontiguousarray(f[keep]) for f in feats], np.ascontiguousarray(price[keep]))
+        got = ml.wls_moments(ctx, dfeats, dprice, dq=(dguest, dprice), dq_params=capi.DqParams(min_price, min_guest, max_price))
+        assert got[0] == ref[0] == float(keep.sum())
+        assert (np.isnan(ref) == np.isnan(got)).all()
+        ok = ~np.isnan(ref)
+        assert float(np.max(np.abs(got[ok] - ref[ok]) / np.maximum(np.abs(ref[ok]), 1e-300))) < 1e-11
+
+
 @pytest.mark.parametrize("params", [dict(max_iter=40, reg_param=0.0, elastic_net_param=0.0, solver="normal"),
                                     dict(max_iter=40, reg_param=0.1, elastic_net_param=0.0),
                                     dict(max_iter=40, reg_param=0.05, elastic_net_param=0.5)])
