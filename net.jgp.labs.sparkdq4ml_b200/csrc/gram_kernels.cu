@@ -4,26 +4,28 @@
 // Spark reaches this from lr.fit (DataQuality4MachineLearningApp.java:126) when solver is auto/normal:
 // WeightedLeastSquares.Aggregator.add does BLAS.spr(w, x, aaSum) per row, i.e. a rank-1 update of the packed d x d
 // Gram.  Here the same sums are a tiled Z^T Z with Z = [x_0 .. x_{d-1} | y | 1]:
-//   * the d columns are cut into blocks of 64; one CTA owns one upper-triangular block pair (bi <= bj) and a slice of
-//     the rows, and walks its rows in chunks of 32;
-//   * the four warps stage each chunk of the 64 (+64) columns they need with 16-byte cp.async copies (the columnar
-//     layout makes a 32-row chunk of a column one contiguous 256-byte run) into an XOR-swizzled, padding-free layout,
-//     three stages deep.  (Round 1 first tried one TMA bulk copy -- cp.async.bulk + mbarrier -- per column chunk from
-//     a producer warp: 130 copies of 256 B per stage kept the consumers spinning on the full barrier and the pass
-//     stayed at 23 % of the fp64 peak, see profiles/r1_gram_tma_bulk_full.json; a column table of arbitrary pointers
-//     cannot be described by one tensor map, so the LSU path is the general one);
-//   * the warps then fix the chunk up in shared memory (int32 -> fp64 for integer columns, DQ predicate ->
-//     rows the rules drop are zeroed, the ones column becomes the keep mask), then each owns a 32 x 32 output tile as
-//     4 x 4 fragments of mma.sync.m8n8k4.f64 (DMMA) accumulated in registers; on diagonal pairs the fourth warp, whose
-//     tile lies below the diagonal, computes the border columns (X^T y, X^T 1) and the y/1 corner instead;
+//   * the d columns are cut into blocks of 64; a "pair" is one upper-triangular block pair (bi <= bj); the rows are cut
+//     into chunks of 32 and dealt out to row slices (slice s of a pair takes chunks s, s + S, s + 2 S, ...);
+//   * one CTA per SM = two independent halves ("sub-CTAs"), each 4 MMA warps + 2 producer warps with its own three
+//     stages and mbarriers, working on adjacent slices of the same pair;
+//   * the producer warps stage a chunk of the 64 (+64) columns with 16-byte cp.async copies (the columnar layout makes
+//     a 32-row chunk of a column one contiguous 256-byte run) into an XOR-swizzled, padding-free layout, then fix it
+//     up in shared memory (int32 -> fp64 for integer columns, DQ predicate -> rows the rules drop are zeroed, the ones
+//     column becomes the keep mask, sqrt(w) scaling) and hand it over through a `full` mbarrier; the MMA warps hand
+//     it back through an `empty` mbarrier.  No CTA-wide barrier inside the row loop;
+//   * off the diagonal each MMA warp owns a 32 x 32 output tile as 4 x 4 fragments of mma.sync.m8n8k4.f64 (DMMA)
+//     accumulated in registers; on the diagonal only the upper triangle is needed (36 of the 64 fragments, plus the 8
+//     border fragments X^T y / X^T 1 and the y/1 corner), dealt out so that every warp has 11 (12 with the corner);
 //   * partial tiles go to scratch, and a second small kernel sums the row slices in a fixed order straight into the
 //     WLS moment layout (deterministic, no atomics).
-// Two further experiments did not pay (round 1, 62.5 M x 256): rotating the warp roles between co-resident CTAs and
-// skipping the sub-diagonal fragments of diagonal warp tiles (174 ms vs 168 ms: the per-chunk barrier makes the
-// heaviest warp the critical path); an 11-fragment-per-warp balanced diagonal CTA with 11/16 as many row slices
-// (181 ms: CTAs of different pairs then walk different rows at the same time and the L2 reuse between them is lost).
 // fp64 DMMA and DFMA both peak at 37.2 TFLOP/s on B200 (tools/fp64_peak.cu), so this pass is bound by the fp64 pipe,
-// not by HBM: 66 816 flop per row at d = 256 against 2 056 B.
+// not by HBM: 66 816 flop per row at d = 256 against 2 056 B.  History of the kernel at 62.5 M x 256 (ms per pass,
+// profiles/r2_gram_fp64_history.jsonl): round 1's kernel (4 warps staging, fixing up and multiplying behind two
+// CTA-wide barriers per chunk, full 64 x 64 tile on the diagonal) 170; one producer warp with a branchy copy loop 333
+// (the MMA warps waited for it 29 % of the time); lean copy loop 156; two producer warps 150; both halves of an SM on
+// the same kind of pair, slices in proportion to the measured cost 136.  Round 1 had also tried one TMA bulk copy
+// (cp.async.bulk) per column chunk: 130 copies of 256 B per stage, 23 % of the fp64 peak
+// (profiles/r1_gram_tma_bulk_full.json); a column table of arbitrary pointers cannot be described by one tensor map.
 #include <algorithm>
 #include <cstdio>
 #include <cstdlib>
@@ -39,18 +41,17 @@ namespace {
 constexpr int GT = 64;          // CTA tile edge in columns
 constexpr int GKC = 32;         // rows per pipeline stage: one column chunk is 256 B (fp64) or 128 B (int32)
 constexpr int GSTAGES = 3;
-constexpr int GTHREADS = 128;   // 4 warps, each owning a 32 x 32 output tile
 constexpr int GPART = GT * GT + GT * 8 + 64;  // doubles per CTA partial: tile, border (64 x 8), corner (8 x 8)
 
 // Shared-memory layout of a staged chunk.  Each column chunk is a dense 256-byte row of 16 x 16-byte pieces; the
 // position of a piece is XOR-ed with twice the column's index mod 8, which makes the 8-byte fragment loads of
 // mma.m8n8k4 (8 columns x 4 consecutive rows per warp) conflict-free without any padding: 3 stages of both panels fit
-// twice in one SM's 227 KB.
+// twice (one per sub-CTA) in one SM's 227 KB.
 struct __align__(16) GramStage {
   double a[GT][GKC];       // column block bi
   double b[GT][GKC];       // column block bj (unused on diagonal pairs)
   double border[8][GKC];   // column 0 = sqrt(w) y, 1 = sqrt(w) keep, 2 = w keep, 3 = keep (w = 1 unweighted); 4..7 stay zero
-  // one copy per producer warp of gram_ws_kernel (the legacy kernel uses copy 0)
+  // one copy per producer warp
   double wt[2][GKC];       // weight chunk, replaced by sqrt(w) * keep during the fix-up (weighted fits only)
   double dqp[2][GKC];      // DQ price chunk
   int dqg[2][GKC];         // DQ guest chunk
@@ -64,7 +65,7 @@ __device__ __forceinline__ int swz(int col, int k) {  // index (in doubles) of e
 struct GramArgs {
   const void* const* col_ptr;  // device array [d]
   const unsigned char* col_i32;  // device array [d]: 1 = int32 column
-  int d, nb, kinds, splits;
+  int d, nb, kinds;
   const double* label;
   const double* weight;  // instance weights (weightCol), nullptr = all 1
   const int* dq_guest;
@@ -72,7 +73,7 @@ struct GramArgs {
   DqThresholds t;
   int has_dq;
   long long n;
-  double* partials;  // [splits * kinds][GPART]
+  double* partials;  // [kinds][s_max][GPART]
 };
 
 __device__ __forceinline__ unsigned smem_u32(const void* p) { return static_cast<unsigned>(__cvta_generic_to_shared(p)); }
@@ -87,270 +88,18 @@ __device__ __forceinline__ void dmma884(double (&c)[2], double a, double b) {
   asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};" : "+d"(c[0]), "+d"(c[1]) : "d"(a), "d"(b));
 }
 
-// W: instance weights present.  A template parameter so that the unweighted kernel carries none of the weight code
-// (as a run-time branch it cost 5 % at 62.5 M x 256: 178.5 ms against 169.9 ms).
-template <bool W>
-__global__ void __launch_bounds__(GTHREADS, 2) gram_tile_kernel(const GramArgs g) {
-  extern __shared__ __align__(128) unsigned char smem_raw[];
-  GramStage* st = reinterpret_cast<GramStage*>(smem_raw);
-  const void** s_colptr = reinterpret_cast<const void**>(smem_raw + GSTAGES * sizeof(GramStage));  // [2*GT]: A slots then B slots
-  unsigned char* s_isint = reinterpret_cast<unsigned char*>(s_colptr + 2 * GT);                    // [2*GT]
-  unsigned char* s_intslots = s_isint + 2 * GT;                                                    // [2*GT] compact list of int32 slots
-  int* s_meta = reinterpret_cast<int*>(s_intslots + 2 * GT);                                       // [0] = #int slots, [4..6] = keep mask per stage
-
-  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int kind = blockIdx.x % g.kinds, split = blockIdx.x / g.kinds;
-  int bi = 0, bj = 0;
-  {
-    int k = kind;
-    for (bi = 0;; ++bi) {
-      const int row_len = g.nb - bi;
-      if (k < row_len) { bj = bi + k; break; }
-      k -= row_len;
-    }
-  }
-  const bool diag = bi == bj;
-  const int n_slots = diag ? GT : 2 * GT;
-
-  // zero every stage once: padding columns (>= d), border columns 2..7 and unused rows stay zero for good
-  for (int i = tid; i < static_cast<int>(GSTAGES * sizeof(GramStage) / 8); i += GTHREADS) reinterpret_cast<double*>(smem_raw)[i] = 0.0;
-  if (tid < 2 * GT) {
-    const int col = (tid < GT ? bi : bj) * GT + (tid & (GT - 1));
-    const bool live = tid < n_slots && col < g.d;
-    s_colptr[tid] = live ? g.col_ptr[col] : nullptr;
-    s_isint[tid] = live ? g.col_i32[col] : 0;
-  }
-  __syncthreads();
-  if (tid == 0) {
-    int m = 0;
-    for (int s = 0; s < n_slots; ++s)
-      if (s_isint[s]) s_intslots[m++] = static_cast<unsigned char>(s);
-    s_meta[0] = m;
-  }
-  __syncthreads();
-  const int n_int = s_meta[0];
-
-  const long long full_chunks = g.n / GKC;
-  const long long my_iters = full_chunks > split ? (full_chunks - split + g.splits - 1) / g.splits : 0;
-
-  // Every thread copies the same 16 (8 on diagonal pairs) pieces of every stage: piece i = 16-byte chunk `ch` of column
-  // slot (tid >> 4) + 8 i.  Their global addresses differ between stages only by the row offset, so the per-piece base
-  // pointers live in registers for the whole kernel (loading them from shared memory per stage cost ~800 cycles per
-  // chunk in the first version: 16 dependent LDS -> branch pairs).
-  const int ch = tid & 15, slot0 = tid >> 4;
-  const char* src[16];
-  unsigned live = 0, ints = 0;
-#pragma unroll
-  for (int i = 0; i < 16; ++i) {
-    const int slot = slot0 + 8 * i;
-    const char* base = slot < n_slots ? static_cast<const char*>(s_colptr[slot]) : nullptr;
-    const bool is_int = base != nullptr && s_isint[slot] != 0;
-    src[i] = base != nullptr ? base + ch * 16 : nullptr;
-    if (base != nullptr && (!is_int || ch < 8)) live |= 1u << i;  // an int32 chunk is 128 B: only 8 pieces
-    if (is_int) ints |= 1u << i;
-  }
-  // destination of piece i inside a stage: its column's 256-byte row, chunk position XOR-swizzled (fp64) or parked
-  // unswizzled in the upper half of the row until it is widened (int32)
-  const unsigned dst_f64 = static_cast<unsigned>(slot0 * 256 + ((ch ^ ((slot0 & 7) << 1)) << 4));
-  const unsigned dst_i32 = static_cast<unsigned>(slot0 * 256 + 128 + ch * 16);
-
-  auto issue_stage = [&](long long it) {
-    GramStage& S = st[it % GSTAGES];
-    const long long row = (split + it * g.splits) * GKC;
-    const unsigned sbase = smem_u32(&S.a[0][0]);
-#pragma unroll
-    for (int i = 0; i < 16; ++i) {
-      if ((live >> i) & 1u) {
-        const bool is_int = (ints >> i) & 1u;
-        const char* p = src[i] + (is_int ? row * 4 : row * 8);
-        const unsigned dst = sbase + 2048u * i + (is_int ? dst_i32 : dst_f64);
-        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(p) : "memory");
-      }
-    }
-    if (diag && tid < 16) cp_async16(&S.border[0][0] + (tid << 1), g.label + row + tid * 2);  // y: border column 0 (col & 7 == 0: no swizzle)
-    if (g.has_dq) {
-      if (tid >= 32 && tid < 48) cp_async16(&S.dqp[0][(tid - 32) * 2], g.dq_price + row + (tid - 32) * 2);
-      if (tid >= 64 && tid < 72) cp_async16(&S.dqg[0][(tid - 64) * 4], g.dq_guest + row + (tid - 64) * 4);
-    }
-    if (W && tid >= 96 && tid < 112) cp_async16(&S.wt[0][(tid - 96) * 2], g.weight + row + (tid - 96) * 2);
-  };
-
-  const int wm = warp >> 1, wn = warp & 1;
-  const bool border_warp = diag && warp == 2;  // tile (1,0) of a diagonal pair lies below the diagonal
-  double acc[4][4][2];
-#pragma unroll
-  for (int i = 0; i < 4; ++i)
-#pragma unroll
-    for (int j = 0; j < 4; ++j) acc[i][j][0] = acc[i][j][1] = 0.0;
-  // the border warp keeps its 8 border fragments in acc[i & 3][i >> 2] and the corner in acc[0][2]
-
-  // fix-up of one staged chunk + the MMAs over it.  rows_valid < GKC only for the tail chunk.
-  auto consume = [&](GramStage& S, int* mask_slot, bool convert, int rows_valid) {
-    if (convert) {  // widen parked int32 chunks in place (whole warp reads before anyone writes)
-      for (int q = warp; q < n_int; q += GTHREADS / 32) {
-        const int slot = s_intslots[q];
-        double* row = slot < GT ? S.a[slot] : S.b[slot - GT];
-        const int v = reinterpret_cast<const int*>(row)[GKC + lane];
-        __syncwarp();
-        row[swz(slot, lane)] = static_cast<double>(v);
-      }
-    }
-    if (warp == 0) {
-      bool keep = lane < rows_valid;
-      if (keep && g.has_dq) keep = dq_keep(S.dqg[0][lane], S.dqp[0][lane], g.t);
-      const unsigned m = __ballot_sync(0xffffffffu, keep);
-      if (lane == 0) *mask_slot = static_cast<int>(m);
-      // WeightedLeastSquares.Aggregator: wSum += w, wwSum += w^2, bSum += w y, aSum += w x, aaSum += w x x^T.  Every row of
-      // the chunk is scaled by sqrt(w) below, so Z^T Z carries the weights; count and wwSum ride in two more border columns.
-      if constexpr (W) {
-        const double w = keep ? S.wt[0][lane] : 0.0;
-        const double sw = sqrt(w);
-        S.wt[0][lane] = sw;
-        if (diag) {
-          S.border[1][swz(1, lane)] = sw;
-          S.border[2][swz(2, lane)] = w;
-          S.border[3][swz(3, lane)] = keep ? 1.0 : 0.0;
-        }
-      } else {
-        if (diag) S.border[1][swz(1, lane)] = keep ? 1.0 : 0.0;  // count = wSum = wwSum: one border column is enough
-      }
-    }
-    __syncthreads();
-    const unsigned dropped = ~static_cast<unsigned>(*mask_slot);
-    if (dropped != 0u) {  // rows the DQ rules (or the end of the data) remove contribute nothing: zero them in every column
-      for (unsigned m = dropped; m != 0u; m &= m - 1u) {
-        const int r = __ffs(m) - 1;
-        if (tid < GT) S.a[tid][swz(tid, r)] = 0.0;
-        else if (!diag) S.b[tid - GT][swz(tid - GT, r)] = 0.0;
-        if (diag && tid == GT) S.border[0][swz(0, r)] = 0.0;
-      }
-      __syncthreads();
-    }
-    if constexpr (W) {  // scale every row of both panels and of y by sqrt(w): the same 16-byte pieces this thread staged
-      const int pch = tid & 15, slot_base = tid >> 4;
-      const int lch = pch ^ ((slot_base & 7) << 1);  // logical chunk held at physical position pch: rows 2 lch, 2 lch + 1
-      const double s0 = S.wt[0][2 * lch], s1 = S.wt[0][2 * lch + 1];
-      for (int slot = slot_base; slot < n_slots; slot += 8) {
-        double2* q = reinterpret_cast<double2*>((slot < GT ? S.a[slot] : S.b[slot - GT]) + 2 * pch);
-        double2 v = *q;
-        v.x *= s0;
-        v.y *= s1;
-        *q = v;
-      }
-      if (diag && tid < GKC) S.border[0][swz(0, tid)] *= S.wt[0][tid];
-      __syncthreads();
-    }
-    const double(*A)[GKC] = S.a;
-    const double(*B)[GKC] = diag ? S.a : S.b;
-    const int fr = lane >> 2, fk = lane & 3;
-    // fragment element (column c0 + fr, row k0 + fk): all columns of a fragment share (c & 7) == fr
-    const int sw = (fr << 1);
-    if (!border_warp) {
-#pragma unroll
-      for (int k0 = 0; k0 < GKC; k0 += 4) {
-        const int off = (((((k0 + fk) >> 1) ^ sw) << 1) | (fk & 1));
-        double af[4], bf[4];
-#pragma unroll
-        for (int i = 0; i < 4; ++i) af[i] = A[wm * 32 + i * 8 + fr][off];
-#pragma unroll
-        for (int j = 0; j < 4; ++j) bf[j] = B[wn * 32 + j * 8 + fr][off];
-#pragma unroll
-        for (int i = 0; i < 4; ++i)
-#pragma unroll
-          for (int j = 0; j < 4; ++j) dmma884(acc[i][j], af[i], bf[j]);
-      }
-    } else {
-#pragma unroll
-      for (int k0 = 0; k0 < GKC; k0 += 4) {
-        const int off = (((((k0 + fk) >> 1) ^ sw) << 1) | (fk & 1));
-        const double bb = S.border[fr][off];
-#pragma unroll
-        for (int i = 0; i < 8; ++i) dmma884(acc[i & 3][i >> 2], A[i * 8 + fr][off], bb);
-        if (bi == 0) dmma884(acc[0][2], bb, bb);
-      }
-    }
-  };
-
-  // ---- 3-stage cp.async pipeline: chunk it+2 is in flight while chunk it is fixed up and multiplied
-  for (int pre = 0; pre < GSTAGES - 1; ++pre) {
-    if (pre < my_iters) issue_stage(pre);
-    cp_async_commit();
-  }
-  for (long long it = 0; it < my_iters; ++it) {
-    cp_async_wait<GSTAGES - 2>();  // this thread's copies of chunk `it` have landed
-    __syncthreads();               // ... and everybody's; also: everyone is done with chunk it-1, whose stage is reused next
-    if (it + GSTAGES - 1 < my_iters) issue_stage(it + GSTAGES - 1);
-    cp_async_commit();
-    consume(st[it % GSTAGES], &s_meta[4 + it % GSTAGES], n_int > 0, GKC);
-  }
-  cp_async_wait<0>();
-
-  // tail chunk (n % 32 rows): plain loads by the CTA whose turn it is
-  const int tail_rows = static_cast<int>(g.n - full_chunks * GKC);
-  if (tail_rows > 0 && static_cast<int>(full_chunks % g.splits) == split) {
-    __syncthreads();
-    GramStage& S = st[0];
-    const long long row0 = full_chunks * GKC;
-    for (int idx = tid; idx < n_slots * GKC; idx += GTHREADS) {
-      const int r = idx % GKC, slot = idx / GKC;
-      double v = 0.0;
-      if (s_colptr[slot] != nullptr && r < tail_rows)
-        v = s_isint[slot] ? static_cast<double>(static_cast<const int*>(s_colptr[slot])[row0 + r])
-                          : static_cast<const double*>(s_colptr[slot])[row0 + r];
-      (slot < GT ? S.a[slot] : S.b[slot - GT])[swz(slot, r)] = v;
-    }
-    if (tid < GKC) {
-      S.border[0][swz(0, tid)] = (diag && tid < tail_rows) ? g.label[row0 + tid] : 0.0;
-      S.dqg[0][tid] = (g.has_dq && tid < tail_rows) ? g.dq_guest[row0 + tid] : 0;
-      S.dqp[0][tid] = (g.has_dq && tid < tail_rows) ? g.dq_price[row0 + tid] : 0.0;
-      if (W) S.wt[0][tid] = tid < tail_rows ? g.weight[row0 + tid] : 0.0;
-    }
-    __syncthreads();
-    consume(S, &s_meta[4], false, tail_rows);
-  }
-
-  // -------------------------------------------------------------------- partial tile -> scratch
-  double* P = g.partials + static_cast<size_t>(blockIdx.x) * GPART;
-  const int fr = lane >> 2, fc = (lane & 3) * 2;
-  if (!border_warp) {
-#pragma unroll
-    for (int i = 0; i < 4; ++i)
-#pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        const int r = wm * 32 + i * 8 + fr, c = wn * 32 + j * 8 + fc;
-        *reinterpret_cast<double2*>(&P[r * GT + c]) = make_double2(acc[i][j][0], acc[i][j][1]);
-      }
-  } else {
-#pragma unroll
-    for (int i = 0; i < 8; ++i)
-      *reinterpret_cast<double2*>(&P[GT * GT + (i * 8 + fr) * 8 + fc]) = make_double2(acc[i & 3][i >> 2][0], acc[i & 3][i >> 2][1]);
-    *reinterpret_cast<double2*>(&P[GT * GT + GT * 8 + fr * 8 + fc]) = make_double2(acc[0][2][0], acc[0][2][1]);
-  }
-}
-
-// ---------------------------------------------------------------------------------------------------------------
-// Round 2: the same pass with the staging and the fix-up moved to a producer warp, and balanced diagonal CTAs.
-//
-//   * 160 threads: warps 0..3 only multiply, warp 4 stages and fixes up.  A stage goes producer -> consumers through
-//     a `full` mbarrier (32 arrivals: the producer lanes after their copies have landed and the chunk is fixed up) and
-//     back through an `empty` mbarrier (4 arrivals: one per consumer warp), so the four MMA warps never meet at a
-//     CTA-wide barrier and never wait for the mask, the int32 widening or the sqrt(w) scaling;
-//   * a diagonal pair needs only the upper triangle of its 64 x 64 tile: 36 of the 64 fragments, plus 8 border
-//     fragments and the corner.  Warp w takes fragment rows w and 7 - w (11 fragments each, 12 with the corner), i.e.
-//     a diagonal CTA costs 12/16 of an off-diagonal one per chunk and executes no sub-diagonal flop outside the 8 x 8
-//     diagonal fragments themselves;
-//   * because the two kinds of CTA now differ in cost, the row slices are handed out in proportion (s_diag slices per
-//     diagonal pair, s_off per off-diagonal pair, chosen on the host so that both kinds walk the rows at the same
-//     pace), and the producer warps keep the kinds within `lead` chunks of each other through one progress counter
-//     per pair: CTAs of different pairs read the same rows at about the same time and share them through L2.
 constexpr int GWS_THREADS = 192;  // 4 MMA warps + 2 producer warps
 constexpr int GWS_MMA_WARPS = 4;
-constexpr double kDiagCost = 12.0;  // cost of a diagonal sub-CTA per chunk on the scale where an off-diagonal one costs 16
+// Measured time per chunk of a sub-CTA next to one of its own kind (62.5 M x 256, DQ4ML_GRAM_DEBUG=1), on the scale
+// where an off-diagonal pair costs its 16 fragments per warp: 2.26 us off the diagonal, 1.64 us on it (11 fragments per
+// warp), 1.69 us for pair (0,0) (warp 3 also has the corner).
+constexpr double kOffCost = 16.0, kDiagCost = 11.6, kDiag0Cost = 12.0;
 constexpr size_t kGramWsSmem = (kGramSmem + 64 + 2 * GT * sizeof(void*) + 127) & ~static_cast<size_t>(127);  // one sub-CTA: + the stage mbarriers and the fp64-only pointer table
 
 struct GramWsArgs {
   GramArgs g;
-  int s_diag, s_off, s_max;       // row slices per diagonal / off-diagonal pair; partial slot stride
+  int s_off, s_diag, s_diag0;     // row slices per off-diagonal pair, per diagonal pair, of pair (0,0) (it has the corner)
+  int s_max;                      // partial slot stride: slot [pair][slice]
   unsigned long long* progress;   // [kinds] chunks issued per pair, zeroed before the launch; nullptr = no pacing
   int lead;                       // a producer does not run more than this many chunks ahead of the slowest pair
   int debug;                      // DQ4ML_GRAM_DEBUG=1: slice 0 of every pair prints its run time
@@ -480,16 +229,18 @@ __global__ void __launch_bounds__(2 * GWS_THREADS, 1) gram_ws_kernel(const GramW
 
   const int tid = threadIdx.x - sub * GWS_THREADS, warp = tid >> 5, lane = tid & 31;
   const unsigned long long t_start = a.debug ? global_timer_ns() : 0ULL;
-  // sub-CTA -> (pair, row slice), pair-major: s_diag / s_off are even, so the two halves of a CTA get slices 2c and
-  // 2c + 1 of the same pair
+  // sub-CTA -> (pair, row slice): all slices of the off-diagonal pairs first, then those of the diagonal pairs, so that
+  // the two halves of a CTA work on pairs of the same cost (at most one CTA straddles the two kinds)
   int kind = 0, split = static_cast<int>(blockIdx.x) * 2 + sub;
   bool active = false;
-  for (int i = 0, k = 0; i < g.nb && !active; ++i)
-    for (int j = i; j < g.nb; ++j, ++k) {
-      const int sk = i == j ? a.s_diag : a.s_off;
-      if (split < sk) { kind = k; active = true; break; }
-      split -= sk;
-    }
+  for (int pass = 0; pass < 2 && !active; ++pass)
+    for (int i = 0, k = 0; i < g.nb && !active; ++i)
+      for (int j = i; j < g.nb; ++j, ++k) {
+        if ((i == j) != (pass == 1)) continue;
+        const int sk = i != j ? a.s_off : (i == 0 ? a.s_diag0 : a.s_diag);
+        if (split < sk) { kind = k; active = true; break; }
+        split -= sk;
+      }
   int bi = 0, bj = 0;
   {
     int k = kind;
@@ -500,7 +251,7 @@ __global__ void __launch_bounds__(2 * GWS_THREADS, 1) gram_ws_kernel(const GramW
     }
   }
   const bool diag = bi == bj;
-  const int my_splits = diag ? a.s_diag : a.s_off;
+  const int my_splits = !diag ? a.s_off : (bi == 0 ? a.s_diag0 : a.s_diag);
   const int n_slots = diag ? GT : 2 * GT;
 
   for (int i = tid; i < static_cast<int>(GSTAGES * sizeof(GramStage) / 8); i += GWS_THREADS) reinterpret_cast<double*>(smem_raw)[i] = 0.0;
@@ -662,8 +413,11 @@ __global__ void __launch_bounds__(2 * GWS_THREADS, 1) gram_ws_kernel(const GramW
         if (diag && pw == 0) S.border[0][swz(0, lane)] *= S.wt[pw][lane];
       }
     };
-    // pacing: one counter per pair holds the chunks its CTAs have issued; a producer that is more than `lead` chunks
-    // ahead of the slowest pair sleeps (bounded: after 200 us it stops pacing for good, a stalled pair must not hang it)
+    // Pacing (opt-in, DQ4ML_GRAM_PACE=<lead>): one counter per pair holds the chunks its CTAs have issued; a producer that
+    // is more than `lead` chunks ahead of the slowest pair sleeps (bounded: after 200 us it stops pacing for good, a
+    // stalled pair must not hang it).  It keeps the pairs on the same rows, so each block is read from DRAM once
+    // instead of 3.3 times (16.6 GB against 54.8 GB at 8 M x 256), but the pass is bound by the DMMA pipe, not by
+    // DRAM, and holding every pair to the slowest one costs more than the re-reads: 142.6 ms against 135.7 ms.
     unsigned long long seen = 0;  // the slowest pair's counter as this warp last read it (read one iteration early)
     auto read_progress = [&]() {
       unsigned long long lo = ~0ULL;
@@ -787,10 +541,9 @@ __global__ void __launch_bounds__(2 * GWS_THREADS, 1) gram_ws_kernel(const GramW
 
 // Sums the row slices in a fixed order and lays the result out as
 // [count, wSum, wwSum, bSum, bbSum, aSum[d], abSum[d], aaSum packed upper column-major].
-// Partial slots: [pair][slice] with stride s_max (s_diag slices for diagonal pairs, s_off for the others); the legacy
-// kernel's layout is [slice][pair] with the same number of slices for every pair (s_max = 0).
-__global__ void __launch_bounds__(256) gram_reduce_kernel(const double* __restrict__ partials, int d, int nb, int kinds,
-                                                          int s_diag, int s_off, int s_max, long long len, int weighted,
+// Partial slots: [pair][slice] with stride s_max.
+__global__ void __launch_bounds__(256) gram_reduce_kernel(const double* __restrict__ partials, int d, int nb, int s_off,
+                                                          int s_diag, int s_diag0, int s_max, long long len, int weighted,
                                                           double* __restrict__ out) {
   const long long e = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
   if (e >= len) return;
@@ -817,13 +570,9 @@ __global__ void __launch_bounds__(256) gram_reduce_kernel(const double* __restri
     off = static_cast<int>(i % GT) * GT + static_cast<int>(j % GT);
   }
   const int kind = bi * nb - bi * (bi - 1) / 2 + (bj - bi);
-  const int splits = bi == bj ? s_diag : s_off;
+  const int splits = bi != bj ? s_off : (bi == 0 ? s_diag0 : s_diag);
   double s = 0.0;
-  if (s_max > 0) {
-    for (int sp = 0; sp < splits; ++sp) s += partials[(static_cast<size_t>(kind) * s_max + sp) * GPART + off];
-  } else {
-    for (int sp = 0; sp < splits; ++sp) s += partials[(static_cast<size_t>(sp) * kinds + kind) * GPART + off];
-  }
+  for (int sp = 0; sp < splits; ++sp) s += partials[(static_cast<size_t>(kind) * s_max + sp) * GPART + off];
   out[e] = s;
 }
 
@@ -836,34 +585,35 @@ int gram_wls_moments(dq4ml_ctx* ctx, const std::vector<const void*>& col_ptrs, c
   const int kinds = nb * (nb + 1) / 2;
   const int64_t len = 5 + 2LL * d + static_cast<int64_t>(d) * (d + 1) / 2;
   const int64_t full_chunks = n / GKC;
-  // one wave exactly: 2 CTAs fit per SM (registers and shared memory), and a 297th CTA would double the run time
-  int64_t splits = (2LL * ctx->sm_count) / kinds;
-  if (splits > full_chunks) splits = full_chunks;
-  if (splits < 1) splits = 1;
-  // Producer-warp kernel: slices in proportion to the cost of a pair (12 fragments per warp and chunk on the diagonal,
-  // 16 off it), chosen so that the slower kind is as fast as possible within one resident wave.
-  static const char* kernel_env = std::getenv("DQ4ML_GRAM_KERNEL");
-  const bool legacy = kernel_env != nullptr && std::strcmp(kernel_env, "legacy") == 0;
+  // One wave exactly: two sub-CTAs per SM.  The slices are dealt out in proportion to the measured cost of a chunk
+  // (kOffCost : kDiagCost : kDiag0Cost), so that every pair finishes at about the same time.
   static const char* pace_env = std::getenv("DQ4ML_GRAM_PACE");
-  const int lead = pace_env != nullptr ? std::atoi(pace_env) : 256;
-  int s_diag = 1, s_off = 1;
+  const int lead = pace_env != nullptr ? std::atoi(pace_env) : 0;
+  int s_off = 0, s_diag = 0, s_diag0 = 1;
   {
-    const int n_diag = nb, n_off = kinds - nb, cap = 2 * ctx->sm_count;
-    double best = -1.0;
-    for (int sd = 2; sd * n_diag + (n_off > 0 ? 2 * n_off : 0) <= cap; sd += 2) {  // even: both halves of a CTA on one pair
-      const int so = n_off > 0 ? ((cap - sd * n_diag) / n_off) & ~1 : 0;
-      const double pace = n_off > 0 ? std::min(sd / kDiagCost, so / 16.0) : sd / kDiagCost;
-      if (pace >= best) { best = pace; s_diag = sd; s_off = so; }  // on a tie the split that fills more SMs
+    const int n_off = kinds - nb, n_diag = nb - 1, cap = 2 * ctx->sm_count;
+    double best = 1e300;
+    for (int so = n_off > 0 ? 1 : 0; so * n_off < cap; ++so) {
+      for (int sd = n_diag > 0 ? 1 : 0; so * n_off + sd * n_diag < cap; ++sd) {
+        const int sd0 = cap - so * n_off - sd * n_diag;
+        double t = kDiag0Cost / sd0;
+        if (n_off > 0) t = std::max(t, kOffCost / so);
+        if (n_diag > 0) t = std::max(t, kDiagCost / sd);
+        if (t < best) { best = t; s_off = so; s_diag = sd; s_diag0 = sd0; }
+        if (n_diag == 0) break;
+      }
+      if (n_off == 0) break;
     }
-    static const char* slices_env = std::getenv("DQ4ML_GRAM_SLICES");  // "s_diag,s_off": tuning only
-    if (slices_env != nullptr) std::sscanf(slices_env, "%d,%d", &s_diag, &s_off);
-    if (s_diag > full_chunks) s_diag = static_cast<int>(std::max<int64_t>(full_chunks, 1));
-    if (s_off > full_chunks) s_off = static_cast<int>(std::max<int64_t>(full_chunks, 1));
-    if (n_off == 0) s_off = 0;
+    static const char* slices_env = std::getenv("DQ4ML_GRAM_SLICES");  // "s_off,s_diag,s_diag0": tuning only
+    if (slices_env != nullptr) std::sscanf(slices_env, "%d,%d,%d", &s_off, &s_diag, &s_diag0);
+    const int most = static_cast<int>(std::max<int64_t>(std::min<int64_t>(full_chunks, cap), 1));
+    s_off = n_off > 0 ? std::max(std::min(s_off, most), 1) : 0;
+    s_diag = n_diag > 0 ? std::max(std::min(s_diag, most), 1) : 0;
+    s_diag0 = std::max(std::min(s_diag0, most), 1);
   }
-  const int s_max = std::max(s_diag, s_off);
-  const int64_t ws_blocks = static_cast<int64_t>(s_diag) * nb + static_cast<int64_t>(s_off) * (kinds - nb);
-  if (!legacy) splits = s_max;  // sizes the partial scratch: kinds * s_max slots
+  const int s_max = std::max(s_diag0, std::max(s_diag, s_off));
+  const int64_t ws_blocks = static_cast<int64_t>(s_off) * (kinds - nb) + static_cast<int64_t>(s_diag) * (nb - 1) + s_diag0;
+  const int64_t splits = s_max;  // sizes the partial scratch: kinds * s_max slots
   const size_t table_bytes = (static_cast<size_t>(d) * 9 + 255) & ~static_cast<size_t>(255);
   const size_t part_bytes = static_cast<size_t>(splits) * kinds * GPART * sizeof(double);
   const size_t out_bytes = static_cast<size_t>(len) * sizeof(double);
@@ -906,7 +656,6 @@ int gram_wls_moments(dq4ml_ctx* ctx, const std::vector<const void*>& col_ptrs, c
   g.d = d;
   g.nb = nb;
   g.kinds = kinds;
-  g.splits = static_cast<int>(splits);
   g.label = label;
   g.weight = weight;
   g.dq_guest = dq.guest;
@@ -919,10 +668,6 @@ int gram_wls_moments(dq4ml_ctx* ctx, const std::vector<const void*>& col_ptrs, c
   g.partials = d_part;
   static bool attr_set[64] = {false};
   if (ctx->device < 64 && !attr_set[ctx->device]) {
-    if ((e = cudaFuncSetAttribute(gram_tile_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(kGramSmem))) != cudaSuccess)
-      return fail(e, "gram smem attribute");
-    if ((e = cudaFuncSetAttribute(gram_tile_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(kGramSmem))) != cudaSuccess)
-      return fail(e, "gram smem attribute");
     if ((e = cudaFuncSetAttribute(gram_ws_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(2 * kGramWsSmem))) != cudaSuccess)
       return fail(e, "gram smem attribute");
     if ((e = cudaFuncSetAttribute(gram_ws_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(2 * kGramWsSmem))) != cudaSuccess)
@@ -931,30 +676,26 @@ int gram_wls_moments(dq4ml_ctx* ctx, const std::vector<const void*>& col_ptrs, c
   }
   GramWsArgs wa;
   wa.g = g;
-  wa.s_diag = s_diag;
   wa.s_off = s_off;
+  wa.s_diag = s_diag;
+  wa.s_diag0 = s_diag0;
   wa.s_max = s_max;
   wa.progress = (lead > 0 && kinds > 1) ? d_progress : nullptr;
   wa.lead = lead;
   static const char* debug_env = std::getenv("DQ4ML_GRAM_DEBUG");
   wa.debug = debug_env != nullptr && debug_env[0] == '1' ? 1 : 0;
-  if (!legacy && wa.progress != nullptr) {
+  if (wa.progress != nullptr) {
     if ((e = cudaMemsetAsync(d_progress, 0, static_cast<size_t>(kinds) * sizeof(unsigned long long), ctx->stream)) != cudaSuccess)
       return fail(e, "gram pacing counters");
   }
   if (ctx->pass_timing) cudaEventRecord(ctx->pass_ev0, ctx->stream);
-  if (legacy) {
-    if (weight != nullptr) gram_tile_kernel<true><<<static_cast<unsigned>(splits * kinds), GTHREADS, kGramSmem, ctx->stream>>>(g);
-    else gram_tile_kernel<false><<<static_cast<unsigned>(splits * kinds), GTHREADS, kGramSmem, ctx->stream>>>(g);
-  } else {
-    const unsigned ws_grid = static_cast<unsigned>((ws_blocks + 1) / 2);
-    if (weight != nullptr) gram_ws_kernel<true><<<ws_grid, 2 * GWS_THREADS, 2 * kGramWsSmem, ctx->stream>>>(wa);
-    else gram_ws_kernel<false><<<ws_grid, 2 * GWS_THREADS, 2 * kGramWsSmem, ctx->stream>>>(wa);
-  }
+  const unsigned ws_grid = static_cast<unsigned>((ws_blocks + 1) / 2);
+  if (weight != nullptr) gram_ws_kernel<true><<<ws_grid, 2 * GWS_THREADS, 2 * kGramWsSmem, ctx->stream>>>(wa);
+  else gram_ws_kernel<false><<<ws_grid, 2 * GWS_THREADS, 2 * kGramWsSmem, ctx->stream>>>(wa);
   if ((e = cudaGetLastError()) != cudaSuccess) return fail(e, "gram tile kernel");
   ++ctx->launches;
   gram_reduce_kernel<<<static_cast<unsigned>((len + 255) / 256), 256, 0, ctx->stream>>>(
-      d_part, d, nb, kinds, legacy ? static_cast<int>(splits) : s_diag, legacy ? static_cast<int>(splits) : s_off, legacy ? 0 : s_max, len,
+      d_part, d, nb, s_off, s_diag, s_diag0, s_max, len,
       weight != nullptr ? 1 : 0, d_out);
   if ((e = cudaGetLastError()) != cudaSuccess) return fail(e, "gram reduce kernel");
   ++ctx->launches;
