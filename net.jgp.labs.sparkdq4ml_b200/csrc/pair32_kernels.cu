@@ -18,6 +18,8 @@
 // one-row-per-thread consumer is a serial fp64 chain (the 32-term dot product) on 8 warps and the whole pass measured
 // 0.45 (0.52 with 16-byte cp.async pieces); it needs several rows per thread, which the tile size in shared memory does
 // not allow at 32 columns.
+#include <cstdlib>
+
 #include "pair32.hpp"
 
 namespace dq4ml {
@@ -49,7 +51,7 @@ __device__ __forceinline__ int final_index(int h, int k, int hs, int d) {
   return h == 0 ? 1 + 2 * 32 + (k - 1 - 2 * PH) : -1;
 }
 
-template <int OP, int DQMODE, bool VEC, int PH>
+template <int OP, int DQMODE, bool VEC, int PH, int G>
 __device__ __forceinline__ void pair_rows(double (&acc)[PairShape<OP, PH>::NT], const double (&cst)[PH], const double lab_c,
                                           const double offset, const double inv_ystd, const ColTable& cols, const int d,
                                           const int hs, const double* __restrict__ label, const DqArgs& dq,
@@ -118,7 +120,7 @@ __device__ __forceinline__ void pair_rows(double (&acc)[PairShape<OP, PH>::NT], 
   } else if (DQMODE == kDqLab) {  // guest is feature column 0 (held by the even lane), price is the label
 #pragma unroll
     for (int r = 0; r < PR; ++r) {
-      const int g = __shfl_sync(0xffffffffu, g0[r], (threadIdx.x & 31) & ~1);
+      const int g = __shfl_sync(0xffffffffu, g0[r], (threadIdx.x & 31) & ~(G - 1));
       keep[r] = dq_keep(g, y[r], dq.t);
     }
   } else {
@@ -139,7 +141,8 @@ __device__ __forceinline__ void pair_rows(double (&acc)[PairShape<OP, PH>::NT], 
         x[j][r] = keep[r] ? x[j][r] : 0.0;  // dropped rows may hold NaN / Inf payload
         part = fma(x[j][r], cst[j], part);
       }
-      const double dot = part + __shfl_xor_sync(0xffffffffu, part, 1);
+      double dot = part + __shfl_xor_sync(0xffffffffu, part, 1);
+      if (G == 4) dot += __shfl_xor_sync(0xffffffffu, dot, 2);  // (p0 + p1) + (p2 + p3) on every lane of the group
       const double diff = keep[r] ? dot - yr * inv_ystd + offset : 0.0;
       if (h == 0) {
         acc[0] = fma(0.5 * diff, diff, acc[0]);
@@ -169,14 +172,14 @@ struct PairConsts {
   double offset, inv_ystd;
 };
 
-template <int OP, int DQMODE, int PH, int BLK>
+template <int OP, int DQMODE, int PH, int BLK, int G>
 __global__ void __launch_bounds__(BLK, 1)
     pair32_kernel(const PairConsts c, const ColTable cols, const int d, const double* __restrict__ label, const DqArgs dq,
                   const int64_t n, const int hs, const double* __restrict__ centres, double* __restrict__ partials,
                   unsigned int* __restrict__ ticket, double* __restrict__ result, const XrEpilogue ep) {
   constexpr int NT = PairShape<OP, PH>::NT;
-  constexpr int kPairTile = (BLK / 2) * PR;
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, h = lane & 1;
+  constexpr int kPairTile = (BLK / G) * PR;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, h = lane & (G - 1);
   double acc[NT];
 #pragma unroll
   for (int k = 0; k < NT; ++k) acc[k] = 0.0;
@@ -189,27 +192,27 @@ __global__ void __launch_bounds__(BLK, 1)
   const double lab_c = OP == kPairLsq ? 0.0 : __ldg(centres + 32);
 
   const int64_t full_tiles = n / kPairTile;
-  const int64_t in_tile = static_cast<int64_t>(threadIdx.x >> 1) * PR;
+  const int64_t in_tile = static_cast<int64_t>(threadIdx.x / G) * PR;
   for (int64_t tile = blockIdx.x; tile < full_tiles; tile += gridDim.x)
-    pair_rows<OP, DQMODE, true, PH>(acc, cst, lab_c, c.offset, c.inv_ystd, cols, d, hs, label, dq, tile * kPairTile + in_tile, n, h);
+    pair_rows<OP, DQMODE, true, PH, G>(acc, cst, lab_c, c.offset, c.inv_ystd, cols, d, hs, label, dq, tile * kPairTile + in_tile, n, h);
   if (full_tiles * kPairTile < n && static_cast<int64_t>(blockIdx.x) == full_tiles % gridDim.x)  // the ragged end, guarded loads
-    pair_rows<OP, DQMODE, false, PH>(acc, cst, lab_c, c.offset, c.inv_ystd, cols, d, hs, label, dq, full_tiles * kPairTile + in_tile, n, h);
+    pair_rows<OP, DQMODE, false, PH, G>(acc, cst, lab_c, c.offset, c.inv_ystd, cols, d, hs, label, dq, full_tiles * kPairTile + in_tile, n, h);
 
-  // ---- CTA reduction, the two lane classes kept apart: even shuffle distances stay within a class
-  __shared__ double s_warp[(BLK / 32) * 2 * NT];
+  // ---- CTA reduction, the G lane classes kept apart: shuffle distances that are multiples of G stay within a class
+  __shared__ double s_warp[(BLK / 32) * G * NT];
   __shared__ bool s_last;
 #pragma unroll
   for (int k = 0; k < NT; ++k) {
     double v = acc[k];
 #pragma unroll
-    for (int off = 16; off > 1; off >>= 1) v += __shfl_down_sync(0xffffffffu, v, off);
-    if (lane < 2) s_warp[(warp * 2 + lane) * NT + k] = v;
+    for (int off = 16; off >= G; off >>= 1) v += __shfl_down_sync(0xffffffffu, v, off);
+    if (lane < G) s_warp[(warp * G + lane) * NT + k] = v;
   }
   __syncthreads();
-  for (int e = threadIdx.x; e < 2 * NT; e += BLK) {
+  for (int e = threadIdx.x; e < G * NT; e += BLK) {
     double v = s_warp[e];
-    for (int w = 1; w < BLK / 32; ++w) v += s_warp[w * 2 * NT + e];
-    partials[static_cast<size_t>(blockIdx.x) * 2 * NT + e] = v;
+    for (int w = 1; w < BLK / 32; ++w) v += s_warp[w * G * NT + e];
+    partials[static_cast<size_t>(blockIdx.x) * G * NT + e] = v;
   }
   // ---- grid reduction by whichever CTA finishes last, in a fixed order
   __threadfence();
@@ -219,11 +222,11 @@ __global__ void __launch_bounds__(BLK, 1)
   if (!s_last) return;
   __threadfence();
   __shared__ double s_red[BLK / 32];
-  for (int e = 0; e < 2 * NT; ++e) {
+  for (int e = 0; e < G * NT; ++e) {
     const int out = final_index<OP, PH>(e / NT, e % NT, hs, d);
     if (out < 0) continue;  // uniform over the CTA
     double v = 0.0;
-    for (unsigned b = threadIdx.x; b < gridDim.x; b += BLK) v += __ldcg(partials + static_cast<size_t>(b) * 2 * NT + e);
+    for (unsigned b = threadIdx.x; b < gridDim.x; b += BLK) v += __ldcg(partials + static_cast<size_t>(b) * G * NT + e);
     v = block_reduce(v, kSum, s_red);
     if (threadIdx.x == 0) result[out] = v;
   }
@@ -232,32 +235,43 @@ __global__ void __launch_bounds__(BLK, 1)
   xr_publish(ep, result, OP == kPairLsq ? 2 + 32 : 1 + 2 * 33, centres, [](int) { return static_cast<int>(kSum); });
 }
 
-template <int OP, int PH, int BLK>
+template <int OP, int PH, int BLK, int G>
 cudaError_t launch_shape(int dq_mode, const PairConsts& c, const ColTable& cols, int d, const double* label, const DqArgs& dq,
                          int64_t n, const Scratch& scratch, cudaStream_t stream) {
-  constexpr int kPairTile = (BLK / 2) * PR;
+  constexpr int kPairTile = (BLK / G) * PR;
   const int64_t tiles = (n + kPairTile - 1) / kPairTile;
   int64_t grid = scratch.sm_count;
   if (grid > tiles) grid = tiles;
   if (grid < 1) grid = 1;
-  if (static_cast<size_t>(grid) * 2 * PairShape<OP, PH>::NT * sizeof(double) > scratch.partials_bytes) return cudaErrorMemoryAllocation;
+  if (static_cast<size_t>(grid) * G * PairShape<OP, PH>::NT * sizeof(double) > scratch.partials_bytes) return cudaErrorMemoryAllocation;
   const unsigned gsz = static_cast<unsigned>(grid);
-  const int hs = (d + 1) / 2;  // columns per lane: the table is split evenly over the pair
+  const int hs = (d + G - 1) / G;  // columns per lane: the table is split evenly over the lane group
   if (dq_mode == kDqNone)
-    pair32_kernel<OP, kDqNone, PH, BLK><<<gsz, BLK, 0, stream>>>(c, cols, d, label, dq, n, hs, scratch.consts, scratch.partials, scratch.ticket, scratch.result, scratch.ep);
+    pair32_kernel<OP, kDqNone, PH, BLK, G><<<gsz, BLK, 0, stream>>>(c, cols, d, label, dq, n, hs, scratch.consts, scratch.partials, scratch.ticket, scratch.result, scratch.ep);
   else if (dq_mode == kDqSeparate)
-    pair32_kernel<OP, kDqSeparate, PH, BLK><<<gsz, BLK, 0, stream>>>(c, cols, d, label, dq, n, hs, scratch.consts, scratch.partials, scratch.ticket, scratch.result, scratch.ep);
+    pair32_kernel<OP, kDqSeparate, PH, BLK, G><<<gsz, BLK, 0, stream>>>(c, cols, d, label, dq, n, hs, scratch.consts, scratch.partials, scratch.ticket, scratch.result, scratch.ep);
   else
-    pair32_kernel<OP, kDqLab, PH, BLK><<<gsz, BLK, 0, stream>>>(c, cols, d, label, dq, n, hs, scratch.consts, scratch.partials, scratch.ticket, scratch.result, scratch.ep);
+    pair32_kernel<OP, kDqLab, PH, BLK, G><<<gsz, BLK, 0, stream>>>(c, cols, d, label, dq, n, hs, scratch.consts, scratch.partials, scratch.ticket, scratch.result, scratch.ep);
   return cudaGetLastError();
 }
 
 template <int OP>
 cudaError_t launch_mode(int dq_mode, const PairConsts& c, const ColTable& cols, int d, const double* label, const DqArgs& dq,
                         int64_t n, const Scratch& scratch, cudaStream_t stream) {
-  if (d <= 24) return launch_shape<OP, 12, 384>(dq_mode, c, cols, d, label, dq, n, scratch, stream);
+  static const char* shape24_env = std::getenv("DQ4ML_PAIR24_SHAPE");
+  const int shape24 = shape24_env != nullptr ? std::atoi(shape24_env) : 0;
+  if (d <= 24) {
+    if (shape24 == 1) return launch_shape<OP, 6, 512, 4>(dq_mode, c, cols, d, label, dq, n, scratch, stream);
+    if (shape24 == 2) return launch_shape<OP, 6, 640, 4>(dq_mode, c, cols, d, label, dq, n, scratch, stream);
+    return launch_shape<OP, 12, 384, 2>(dq_mode, c, cols, d, label, dq, n, scratch, stream);
+  }
   // (320 threads for 25..32 columns: ptxas spills 350..630 bytes per thread at that occupancy, 0.73 against 0.88)
-  return launch_shape<OP, 16, 256>(dq_mode, c, cols, d, label, dq, n, scratch, stream);
+  static const char* shape_env = std::getenv("DQ4ML_PAIR32_SHAPE");
+  const int shape = shape_env != nullptr ? std::atoi(shape_env) : 1;
+  if (shape == 0) return launch_shape<OP, 16, 256, 2>(dq_mode, c, cols, d, label, dq, n, scratch, stream);
+  if (shape == 2) return launch_shape<OP, 8, 384, 4>(dq_mode, c, cols, d, label, dq, n, scratch, stream);
+  if (shape == 3) return launch_shape<OP, 8, 448, 4>(dq_mode, c, cols, d, label, dq, n, scratch, stream);
+  return launch_shape<OP, 8, 512, 4>(dq_mode, c, cols, d, label, dq, n, scratch, stream);
 }
 
 }  // namespace
