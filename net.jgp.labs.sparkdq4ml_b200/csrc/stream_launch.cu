@@ -7,6 +7,7 @@
 
 #include "kernels.hpp"
 #include "ops.cuh"
+#include "lane_group.hpp"
 #include "pair32.hpp"
 #include "stream_reduce.cuh"
 
@@ -203,7 +204,12 @@ cudaError_t launch_stream_pass(StreamOpKind op, const DeviceCols& cols, const do
   a.scratch = scratch;
   a.stream = stream;
   cudaError_t e;
-  if ((op == kOpLsq || op == kOpSummCore) && cols.n > 16) {  // 17..32 columns: the lane-pair kernels (pair32_kernels.cu)
+  if (lane_group_takes(op, cols.n)) {  // 9..12 columns, 8..16 weighted features: the lane-group kernels (lane_group_kernels.cu)
+    e = launch_lane_group(op, a.cols, a.d, a.label, a.dq, a.dq_mode, a.n, host_consts, row_out, scratch, stream);
+    if (e == cudaSuccess) ++*launches;
+    return e;
+  }
+  if ((op == kOpLsq || op == kOpSummCore) && cols.n > 16) {  // 17..32 columns: the lane-pair / lane-quad kernels (pair32_kernels.cu)
     e = launch_pair32(op == kOpLsq ? kPairLsq : kPairSumm, a.cols, a.d, a.label, a.dq, a.dq_mode, a.n,
                       static_cast<const LsqConsts*>(host_consts), scratch, stream);
     if (e == cudaSuccess) ++*launches;

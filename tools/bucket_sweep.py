@@ -51,7 +51,8 @@ def main():
             cols["w"] = torch.rand(rows, dtype=torch.float64, device="cuda:0") + 0.5
         df = ml.Frame(ctx, cols).with_fused_dq("guest", "label")
         df = ml.VectorAssembler().setInputCols(names).setOutputCol("features").transform(df)
-        lr = ml.LinearRegression().setMaxIter(3).setRegParam(0.1).setElasticNetParam(0.5).setSolver("l-bfgs").setLoss(args.loss)
+        lr = ml.LinearRegression().setMaxIter(3).setRegParam(0.1).setElasticNetParam(0.0 if args.loss == "huber" else 0.5)
+        lr = lr.setSolver("l-bfgs").setLoss(args.loss)
         if args.weighted:
             lr = lr.setWeightCol("w")
         bytes_row = 4 + 8 * (d - 1) + 8 + (8 if args.weighted else 0)
