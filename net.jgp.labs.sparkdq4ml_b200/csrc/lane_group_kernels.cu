@@ -25,10 +25,14 @@
 // 16: 0.70 / 0.97 (0.53 / 0.66).  The kernels are written for groups of 4 lanes as well (17..32 columns), but there
 // round 1's lane-pair kernels (pair32_kernels.cu: 12 register columns at 384 threads up to 24 columns, groups of 4 x 8
 // columns at 512 threads above) stay ahead by 3-10 % and keep those passes.  Also tried and dropped for 17..32
-// columns: landing the next tiles in per-thread slots of shared memory with cp.async (16-byte pieces, two per 4-row
-// column chunk, no barrier) so that the bytes in flight are bounded by shared memory instead of registers: a flat
-// 0.53 of the peak whatever the width -- each 32-byte sector is requested twice, half used each time
-// (profiles/r2_lg_ring_ldc_full.json).
+// columns: landing the next tiles in shared memory with cp.async so that the bytes in flight are bounded by the 227 KB
+// of shared memory instead of the registers.  (a) per-thread slots, 16-byte pieces, two per 4-row column chunk, no
+// barrier: a flat 0.53 of the peak whatever the width (profiles/r2_lg_ring_ldc_full.json: every 32-byte sector
+// requested twice, L2 hit rate 56 %); (b) warp-private rings of 2-3 stages filled with coalesced copies (one
+// instruction = two whole 256-byte column chunks), __syncwarp, conflict-free 128-bit reads, refill before the
+// arithmetic, ~200 KB in flight: 0.45-0.65 (profiles/r2_lane_group_shapes.jsonl, "wc" lines).  The tcgen05 Gram
+// kernel's cp.async staging stops at the same 0.65 with its loads alone: on this part LDGSTS does not stream at the
+// HBM rate, whatever is in flight; the filter's cp.async.bulk ring does (0.80 with its compaction, 0.91 loads alone).
 #include <cstdlib>
 
 #include "lane_group.hpp"

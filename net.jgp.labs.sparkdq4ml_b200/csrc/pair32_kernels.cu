@@ -3,21 +3,23 @@
 //
 // The generic streaming kernel keeps a whole row group in registers: at 32 columns that is 2 rows per thread, 128-bit
 // loads and ~250 registers, and it measured 0.78 of the HBM roofline, against 0.99 for the 16-column bucket with 4 rows
-// per thread and 256-bit loads.  Here the columns of a row group are split evenly over a lane pair: lane h of a pair
-// holds columns hs h .. hs h + hs - 1, hs = ceil(d / 2) <= 16, of 4 consecutive rows (the 16-column kernel's shape), the two partial dot products of a row
-// are exchanged with one shuffle, and each lane keeps the gradient (or the power sums) of its own columns.  Label and DQ
-// columns are requested by both lanes at the same addresses, which the load unit merges.  One persistent 256-thread CTA
-// per SM; warp shuffle over same-parity lanes -> shared memory -> one partial per CTA -> the CTA that takes the last
-// ticket folds the partials in a fixed order, like stream_reduce_kernel.
+// per thread and 256-bit loads.  Here the columns of a row group are split evenly over a group of G = 2 or 4
+// neighbouring lanes: lane h holds columns hs h .. hs h + hs - 1, hs = ceil(d / G), of 4 consecutive rows, the partial
+// dot products of a row are exchanged with one or two shuffles, and each lane keeps the gradient (or the power sums)
+// of its own columns.  Label and DQ columns are requested by all lanes of a group at the same addresses, which the
+// load unit merges.  One persistent CTA per SM; warp shuffle over the lanes of one class -> shared memory -> one
+// partial per CTA -> the CTA that takes the last ticket folds the partials in a fixed order, like stream_reduce_kernel.
 //
-// Measured (4 x 10^8 rows, one loss/gradient pass, fraction of the measured HBM peak): 0.90 at 32 columns with 256
-// threads; up to 24 columns the 12-register-column variant fits 384 threads per SM, half as many bytes again in flight:
-// 0.92 at 17 columns, 0.98 at 20, 1.02 at 24 (0.65 / 0.74 / 0.82 with 256 threads -- the pass is bound by how many
-// loads the registers of an SM can hold in flight, ~140 KB at 32 columns).  Tried instead: a 3-stage shared-memory ring (256-row tiles, one cp.async.bulk of 2 KB per column slot on an
+// A pass is bound by how many loaded-but-unused bytes the registers of an SM can hold in flight (~130-150 KB are
+// needed).  Round 1 (lane pairs only; 4 x 10^8 rows, one loss/gradient pass timed alone): 12 register columns at 384
+// threads up to 24 columns 0.92-1.02, 16 register columns at 256 threads (230 registers, 8 warps) 0.90 at 32 columns.
+// Round 2 added the groups of four lanes (8 register columns at 512 threads for 25..32 columns: 0.93 / 1.00 / 1.04 at
+// 25 / 28 / 32 columns timed alone, 0.85-0.92 inside a fit where the lane pairs gave 0.82-0.88; ncu of the lane pair
+// at 32 columns: profiles/r2_pair32_lsq_d32_full.json) and picks the shape per op from profiles/r2_bucket_sweep.jsonl.
+// Tried instead in round 1: a 3-stage shared-memory ring (256-row tiles, one cp.async.bulk of 2 KB per column slot on an
 // mbarrier, one row per thread out of shared memory into the generic Op bodies).  Its loads alone reach 0.91, but the
 // one-row-per-thread consumer is a serial fp64 chain (the 32-term dot product) on 8 warps and the whole pass measured
-// 0.45 (0.52 with 16-byte cp.async pieces); it needs several rows per thread, which the tile size in shared memory does
-// not allow at 32 columns.
+// 0.45 (0.52 with 16-byte cp.async pieces).
 #include <cstdlib>
 
 #include "pair32.hpp"
@@ -26,8 +28,7 @@ namespace dq4ml {
 namespace {
 
 constexpr int PR = 4;    // rows per lane pair and tile
-// PH = register columns per lane (16, or 12 when the table has at most 24 columns), BLK = threads per CTA (256, or 384
-// with the smaller register footprint of PH = 12: half as many bytes again in flight per SM); a tile is BLK / 2 x PR rows.
+// PH = register columns per lane, G = lanes per row group, BLK = threads per CTA; a tile is BLK / G x PR rows.
 
 template <int OP, int PH>
 struct PairShape {
@@ -258,19 +259,16 @@ cudaError_t launch_shape(int dq_mode, const PairConsts& c, const ColTable& cols,
 template <int OP>
 cudaError_t launch_mode(int dq_mode, const PairConsts& c, const ColTable& cols, int d, const double* label, const DqArgs& dq,
                         int64_t n, const Scratch& scratch, cudaStream_t stream) {
-  static const char* shape24_env = std::getenv("DQ4ML_PAIR24_SHAPE");
-  const int shape24 = shape24_env != nullptr ? std::atoi(shape24_env) : 0;
+  // Shapes by measurement (profiles/r2_bucket_sweep.jsonl, r2_lane_group_shapes.jsonl; fractions of the measured HBM peak
+  // inside a fit).  Up to 24 columns: the loss/gradient pass streams best as lane pairs of 12 register columns at 384
+  // threads (0.89-0.96; groups of four lanes x 6 columns at 512 threads: 0.74-0.82), the summarizer the other way round
+  // (0.82-0.96 against 0.79-0.82).  25..32 columns: groups of four lanes x 8 columns at 512 threads (0.85-0.92 and
+  // 0.88-0.98; lane pairs of 16 columns at 256 threads, 230 registers: 0.82-0.88; at 320 threads ptxas spills 350..630
+  // bytes per thread: 0.73).
   if (d <= 24) {
-    if (shape24 == 1) return launch_shape<OP, 6, 512, 4>(dq_mode, c, cols, d, label, dq, n, scratch, stream);
-    if (shape24 == 2) return launch_shape<OP, 6, 640, 4>(dq_mode, c, cols, d, label, dq, n, scratch, stream);
+    if (OP == kPairSumm) return launch_shape<OP, 6, 512, 4>(dq_mode, c, cols, d, label, dq, n, scratch, stream);
     return launch_shape<OP, 12, 384, 2>(dq_mode, c, cols, d, label, dq, n, scratch, stream);
   }
-  // (320 threads for 25..32 columns: ptxas spills 350..630 bytes per thread at that occupancy, 0.73 against 0.88)
-  static const char* shape_env = std::getenv("DQ4ML_PAIR32_SHAPE");
-  const int shape = shape_env != nullptr ? std::atoi(shape_env) : 1;
-  if (shape == 0) return launch_shape<OP, 16, 256, 2>(dq_mode, c, cols, d, label, dq, n, scratch, stream);
-  if (shape == 2) return launch_shape<OP, 8, 384, 4>(dq_mode, c, cols, d, label, dq, n, scratch, stream);
-  if (shape == 3) return launch_shape<OP, 8, 448, 4>(dq_mode, c, cols, d, label, dq, n, scratch, stream);
   return launch_shape<OP, 8, 512, 4>(dq_mode, c, cols, d, label, dq, n, scratch, stream);
 }
 
