@@ -440,7 +440,8 @@ cudaError_t launch_op(const LgArgs& a, const Scratch& scratch, cudaStream_t stre
     return cudaErrorInvalidValue;  // up to 8 unweighted columns are the generic kernel's
   }
   if (a.d <= 16) return launch_group<OP, W, 2>(a, scratch, stream);
-  return cudaErrorInvalidValue;  // 17..32 columns: pair32_kernels.cu / the generic 32-column bucket
+  if constexpr (!W && (OP == kLgHuber || OP == kLgEval || OP == kLgGrad)) return launch_shape<OP, W, 4, 8, 4, 512>(a, scratch, stream);
+  return cudaErrorInvalidValue;  // the other ops at 17..32 columns: pair32_kernels.cu / the generic 32-column bucket
 }
 
 }  // namespace
@@ -450,7 +451,14 @@ bool lane_group_takes(StreamOpKind op, int table_cols) {
   if (off != nullptr && off[0] == '0') return false;
   switch (op) {
     // measured against the generic kernel of the same bucket, op by op (profiles/r2_bucket_sweep*.jsonl):
-    case kOpLsq: case kOpSummCore: case kOpHuber: case kOpEval: case kOpGrad:
+    case kOpHuber: case kOpEval: case kOpGrad:
+      if (table_cols >= 17 && table_cols <= kMaxCols) {  // groups of four lanes x 8 columns at 512 threads: evaluation 0.81 / 0.91 at 24 / 32
+                                                         // columns against 0.77 / 0.81 in the generic 32-column bucket, huber level
+        static const char* quad = std::getenv("DQ4ML_LG_QUAD");
+        return quad == nullptr || quad[0] != '0';
+      }
+      return table_cols >= 9 && table_cols <= 12;
+    case kOpLsq: case kOpSummCore:
       return table_cols >= 9 && table_cols <= 12;   // 0.88-0.96 against 0.76-0.90; from 13 columns the generic bucket is level
     case kOpLsqW: case kOpHuberW:
       return table_cols >= 9 && table_cols <= 17;   // the weight + 8..16 features: 0.85-1.07 against 0.66-0.95
