@@ -152,7 +152,8 @@ def test_fit_synth_small_all_solvers(pkg, ctx, golden, parity_log, fit_name):
         np.testing.assert_allclose(model.coefficients(), ref["sklearn_coefficients"], rtol=2e-5, atol=2e-6)
 
 
-@pytest.mark.parametrize("d", [1, 3, 8, 16, 17, 32])
+# 9..12: lane-group kernels; 13..16: generic bucket; 17..24: lane pairs; 25..32: groups of four lanes
+@pytest.mark.parametrize("d", [1, 3, 8, 9, 10, 12, 13, 16, 17, 20, 24, 25, 28, 32])
 def test_summarizer_and_lsq_passes_vs_oracle(pkg, ctx, d):
     from sparkdq4ml_b200 import ml
     n = 150_001
@@ -199,6 +200,38 @@ def test_config3_shape_d16_owlqn_fused(pkg, ctx, parity_log, reg_param):
     s = model.summary()
     assert s.totalIterations() == ref.total_iterations and model.data_passes == ref.data_passes
     check_fit(parity_log, f"config3_shape_reg{reg_param}", model, ref.coefficients, ref.intercept, ref.objective_history, RTOL)
+
+
+@pytest.mark.parametrize("d,n", [(9, 30_001), (10, 4_095), (12, 50_000), (14, 20_003), (20, 30_000), (24, 12_289), (28, 20_000)])
+def test_lbfgs_fit_and_evaluation_by_column_bucket(pkg, ctx, parity_log, d, n):
+    """One l-bfgs fit and one evaluation per kernel family of the streaming passes (9..12 columns: lane-group kernels,
+    13..16: generic bucket, 17..24: lane pairs / groups of four for the summarizer, 25..32: groups of four lanes): the
+    fit against the oracle, the evaluation's per-row residuals and metrics against numpy on the surviving rows."""
+    guest, price, feats = synth(n, d, p_low=0.03, p_high=0.03)
+    params = dict(max_iter=30, reg_param=0.2, elastic_net_param=0.5, solver="l-bfgs")
+    ref = spark_ml.linear_regression_fit(feats, price, spark_ml.LRParams(**params), dq=(guest, price), threads=4)
+    dfeats, dprice = to_dev(*feats), to_dev(price)[0]
+    cols = {"guest": dfeats[0], "label": dprice}
+    names = ["guest"]
+    for k in range(1, d):
+        cols[f"x{k}"] = dfeats[k]
+        names.append(f"x{k}")
+    df = pkg.VectorAssembler().setInputCols(names).transform(pkg.Frame(ctx, cols).with_fused_dq("guest", "label"))
+    model = estimator(pkg, params).fit(df)
+    assert model.solver_used == ref.solver_used == "owlqn"
+    assert model.summary().totalIterations() == ref.total_iterations and model.data_passes == ref.data_passes
+    check_fit(parity_log, f"bucket_d{d}", model, ref.coefficients, ref.intercept, ref.objective_history, RTOL)
+    keep = np.array([bool(passes.lib().orc_dq_keep(int(a), float(b))) for a, b in zip(guest, price)])
+    X = np.stack([np.asarray(f, dtype=np.float64) for f in feats], axis=1)
+    res_ref = price - (X @ model.coefficients() + model.intercept())
+    ev = model.evaluate(df, want_residuals=True)
+    res = ev.residuals().cpu().numpy()
+    np.testing.assert_allclose(res[keep], res_ref[keep], rtol=0, atol=1e-9 * max(1.0, float(np.abs(price).max())))
+    assert ev.numInstances() == int(keep.sum())
+    assert rel_err(ev.rootMeanSquaredError(), float(np.sqrt(np.mean(res_ref[keep] ** 2)))) < 1e-9
+    assert rel_err(ev.meanAbsoluteError(), float(np.mean(np.abs(res_ref[keep])))) < 1e-9
+    lo, hi = ev.devianceResiduals()
+    assert rel_err(lo, float(res_ref[keep].min())) < 1e-9 and rel_err(hi, float(res_ref[keep].max())) < 1e-9
 
 
 def test_host_buffers_equal_device_buffers(pkg, ctx):

@@ -48,7 +48,10 @@ CASES = [
     (4, 80_003, dict(reg_param=0.1)),
     (4, 80_003, dict(reg_param=0.1, standardization=False)),
     (4, 50_000, dict(fit_intercept=False, epsilon=2.0)),
+    (10, 30_001, dict(reg_param=0.05)),   # 9..12 columns: lane-group kernels (weighted: the weight + 8..16 features)
+    (12, 20_000, dict(reg_param=0.02, fit_intercept=False)),
     (16, 120_000, dict(reg_param=0.05, solver="l-bfgs")),
+    (24, 25_003, dict(reg_param=0.03)),   # 17..32 columns: groups of four lanes
     (32, 40_000, dict(reg_param=0.01)),
     (40, 30_000, dict(reg_param=0.02)),   # wider than one streaming launch: column-walking row pass + gradient groups
     (70, 20_003, dict(reg_param=0.05, fit_intercept=False)),

@@ -83,7 +83,9 @@ def test_weighted_fit_equals_replicated_rows(pkg, ctx):
     assert abs(mw.intercept() - mr.intercept()) < 1e-7 * max(1.0, abs(mr.intercept()))
 
 
-@pytest.mark.parametrize("d,n", [(1, 2_000), (3, 50_001), (15, 8_000), (31, 6_001), (32, 6_001), (40, 9_000), (70, 5_003)])
+# 8..16 features: lane-group kernels with the weight as a row scalar (8 and 16: the weighted summarizer as well)
+@pytest.mark.parametrize("d,n", [(1, 2_000), (3, 50_001), (8, 9_001), (9, 4_096), (12, 7_000), (15, 8_000), (16, 7_001), (31, 6_001), (32, 6_001), (40, 9_000),
+                                 (70, 5_003)])
 @pytest.mark.parametrize("reg", [(0.0, 0.0), (0.2, 0.0), (0.3, 0.8)])
 @pytest.mark.parametrize("fused", [False, True])
 def test_weighted_lbfgs_fit_vs_oracle(pkg, ctx, d, n, reg, fused):
