@@ -440,7 +440,7 @@ cudaError_t launch_op(const LgArgs& a, const Scratch& scratch, cudaStream_t stre
     return cudaErrorInvalidValue;  // up to 8 unweighted columns are the generic kernel's
   }
   if (a.d <= 16) return launch_group<OP, W, 2>(a, scratch, stream);
-  if constexpr (!W && (OP == kLgHuber || OP == kLgEval || OP == kLgGrad)) return launch_shape<OP, W, 4, 8, 4, 512>(a, scratch, stream);
+  if constexpr (!W && (OP == kLgHuber || OP == kLgEval || OP == kLgGrad)) return launch_group<OP, W, 4>(a, scratch, stream);
   return cudaErrorInvalidValue;  // the other ops at 17..32 columns: pair32_kernels.cu / the generic 32-column bucket
 }
 
