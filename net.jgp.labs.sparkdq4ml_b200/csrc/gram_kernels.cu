@@ -102,7 +102,7 @@ struct GramWsArgs {
   int s_max;                      // partial slot stride: slot [pair][slice]
   unsigned long long* progress;   // [kinds] chunks issued per pair, zeroed before the launch; nullptr = no pacing
   int lead;                       // a producer does not run more than this many chunks ahead of the slowest pair
-  int debug;                      // DQ4ML_GRAM_DEBUG=1: slice 0 of every pair prints its run time
+  int debug;                      // profile build only (DQ4ML_GRAM_PROFILE) + DQ4ML_GRAM_DEBUG=1: slice 0 of every pair prints its run time
 };
 
 __device__ __forceinline__ void mbar_init(unsigned bar, unsigned count) {
@@ -228,7 +228,9 @@ __global__ void __launch_bounds__(2 * GWS_THREADS, 1) gram_ws_kernel(const GramW
   const void** s_f64ptr = reinterpret_cast<const void**>(s_bar + 2 * GSTAGES + 2);                 // [2*GT]: s_colptr with the int32 slots nulled
 
   const int tid = threadIdx.x - sub * GWS_THREADS, warp = tid >> 5, lane = tid & 31;
+#ifdef DQ4ML_GRAM_PROFILE
   const unsigned long long t_start = a.debug ? global_timer_ns() : 0ULL;
+#endif
   // sub-CTA -> (pair, row slice): all slices of the off-diagonal pairs first, then those of the diagonal pairs, so that
   // the two halves of a CTA work on pairs of the same cost (at most one CTA straddles the two kinds)
   int kind = 0, split = static_cast<int>(blockIdx.x) * 2 + sub;
@@ -516,8 +518,10 @@ __global__ void __launch_bounds__(2 * GWS_THREADS, 1) gram_ws_kernel(const GramW
     if (s == GSTAGES - 1) { s = 0; phase ^= 1u; } else { ++s; }
   }
 
+#ifdef DQ4ML_GRAM_PROFILE  // make PTXAS_V=-DDQ4ML_GRAM_PROFILE: slice 0 of every pair prints its run time (how kOffCost : kDiagCost were measured)
   if (a.debug && split == 0 && tid == 0)
     printf("gram_ws pair %d (%d,%d) slices %d iters %lld: %.3f ms\n", kind, bi, bj, my_splits, total, (global_timer_ns() - t_start) * 1e-6);
+#endif
   // -------------------------------------------------------------------- partial tile -> scratch slot [pair][slice]
   double* P = g.partials + (static_cast<size_t>(kind) * a.s_max + split) * GPART;
   if (!diag) {
