@@ -1,6 +1,10 @@
 // stream_launch.cu -- instantiates stream_reduce_kernel for every (op, column-group bucket, DQ mode) the path uses
 // and picks one at run time.  Buckets 1,2 stream 8 rows per thread per tile, buckets 4,8,16 stream 4, bucket 32 streams 2
 // (register budget); grids are sized to (CTAs resident per SM) x (SM count) so the whole pass is one wave of persistent CTAs.
+// Dispatch of a pass by (op, table columns), each choice from profiles/r2_bucket_sweep*.jsonl: the lane-group kernels
+// (lane_group_kernels.cu) take 9..12 columns, the weighted loss/gradient and huber passes over 8..16 features, and the
+// evaluation / huber / gradient-group passes over 17..32 columns; the lane-pair / lane-quad kernels (pair32_kernels.cu)
+// take the summarizer and the loss/gradient pass over 17..32 columns; everything else is the generic kernel here.
 #include <cstdlib>
 #include <map>
 #include <mutex>
