@@ -529,7 +529,7 @@ def run_ours(args):
         line.update({
             "value": r["value"], "ms_per_step": r["ms"] / args.steps, "scaling": "weak", "config": config(2, rows),
             "e2e": r["e2e"], "gpu_launches": r["launches"],
-            "roofline": {"bound": "hbm", "kernel": "stream_reduce_kernel<WlsOp<1>,1,8,kDqLab> (fused DQ + WLS moments)",
+            "roofline": {"bound": "hbm", "kernel": "stream_pipe_kernel<WlsOp<1>,3,kDqLab> (fused DQ + WLS moments)",
                          "achieved": achieved, "peak": b.peak, "unit": "GB/s", "frac": achieved / b.peak,
                          "traffic": ncu_traffic_per_launch("wls_moments_d1_lab"), "peak_source": b.peak_src,
                          "algorithmic_bytes_per_launch": BYTES_PER_ROW * rows, "avg_launch_ms": r["pass_ms_avg"],

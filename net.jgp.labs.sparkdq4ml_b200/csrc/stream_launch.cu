@@ -92,8 +92,33 @@ cudaError_t launch_one(const Op& op, const PassArgs& a) {
   return cudaGetLastError();
 }
 
+// The software-pipelined kernel for the lab's own shape: one int32 feature column + the label, DQ in the lab layout or off
+// (stream_pipe_kernel: 24 rows per thread in the arithmetic, 24 more in flight, one CTA per SM).
+constexpr int kPipeVectors = 3;
+template <class Op, int DQMODE>
+cudaError_t launch_pipe(const Op& op, const PassArgs& a) {
+  constexpr int64_t kTile = static_cast<int64_t>(kBlock) * 8 * kPipeVectors;
+  const int64_t n_tiles = (a.n + kTile - 1) / kTile;
+  int64_t grid = a.scratch.sm_count;
+  if (grid > n_tiles) grid = n_tiles;
+  if (grid < 1) grid = 1;
+  if (static_cast<size_t>(grid) * Op::NACC * sizeof(double) > a.scratch.partials_bytes) return cudaErrorMemoryAllocation;
+  stream_pipe_kernel<Op, kPipeVectors, DQMODE><<<static_cast<unsigned>(grid), kBlock, 0, a.stream>>>(
+      op, static_cast<const int*>(a.cols.ptr[0]), a.label, a.dq.t, a.n, a.dev_consts, a.row_out, a.scratch.partials, a.scratch.ticket,
+      a.scratch.result, a.scratch.ep);
+  return cudaGetLastError();
+}
+inline bool pipe_takes(const PassArgs& a) {
+  static const char* off = std::getenv("DQ4ML_STREAM_PIPE");  // DQ4ML_STREAM_PIPE=0: the grid-strided kernel (A/B)
+  if (off != nullptr && off[0] == '0') return false;
+  return a.d == 1 && (a.cols.i32_mask & 1u) != 0u && (a.dq_mode == kDqNone || a.dq_mode == kDqLab);
+}
+
 template <class Op, int DMAX, int ROWS>
 cudaError_t launch_mode(const Op& op, const PassArgs& a) {
+  if constexpr (DMAX == 1) {
+    if (pipe_takes(a)) return a.dq_mode == kDqLab ? launch_pipe<Op, kDqLab>(op, a) : launch_pipe<Op, kDqNone>(op, a);
+  }
   switch (a.dq_mode) {
     case kDqNone: return launch_one<Op, DMAX, ROWS, kDqNone>(op, a);
     case kDqSeparate: return launch_one<Op, DMAX, ROWS, kDqSeparate>(op, a);

@@ -97,39 +97,13 @@ __device__ __forceinline__ void process_rows(const Op& op, double (&acc)[Op::NAC
   }
 }
 
-template <class Op, int DMAX, int ROWS, int DQMODE>
-__global__ void __launch_bounds__(kBlock, (DMAX * ROWS >= 64 ? 1 : (DMAX <= 2 ? 4 : (DMAX == 4 ? 3 : 2))))
-    stream_reduce_kernel(const Op op, const ColTable cols, const int d, const double* __restrict__ label,
-                         const DqArgs dq, const int64_t n, const double* __restrict__ dev_consts,
-                         double* __restrict__ row_out, double* __restrict__ partials, unsigned int* __restrict__ ticket,
-                         double* __restrict__ result, const XrEpilogue ep) {
+// CTA reduction (shuffle inside each warp, one shared-memory hop across the 8 warps), one partial per CTA, grid
+// reduction in a fixed order by whichever CTA finishes last, hand-over of the result (epilogue.cuh).
+template <class Op>
+__device__ __forceinline__ void reduce_and_publish(double (&acc)[Op::NACC], const double* __restrict__ dev_consts,
+                                                   double* __restrict__ partials, unsigned int* __restrict__ ticket,
+                                                   double* __restrict__ result, const XrEpilogue& ep) {
   constexpr int NACC = Op::NACC;
-  double acc[NACC];
-#pragma unroll
-  for (int k = 0; k < NACC; ++k) acc[k] = Op::identity(k);
-  double consts[Op::NCONST > 0 ? Op::NCONST : 1];
-#pragma unroll
-  for (int k = 0; k < Op::NCONST; ++k) consts[k] = __ldg(dev_consts + k);
-
-  // Full tiles first, with no tail test inside the loop so that it can be unrolled and the loads of the next tile are
-  // in flight during the arithmetic of this one (the ragged end of the table is one extra partial tile below).
-  const int64_t tile_rows = static_cast<int64_t>(kBlock) * ROWS;
-  const int64_t full_tiles = n / tile_rows;
-#pragma unroll (DMAX >= 32 ? 1 : 2)
-  for (int64_t tile = blockIdx.x; tile < full_tiles; tile += gridDim.x) {
-    const int64_t row = tile * tile_rows + static_cast<int64_t>(threadIdx.x) * ROWS;
-    process_rows<Op, DMAX, ROWS, DQMODE, true>(op, acc, consts, cols, d, label, dq, row, row_out);
-  }
-  if (full_tiles * tile_rows < n && static_cast<int64_t>(blockIdx.x) == full_tiles % gridDim.x) {
-    const int64_t row = full_tiles * tile_rows + static_cast<int64_t>(threadIdx.x) * ROWS;
-    if (row + ROWS <= n) {
-      process_rows<Op, DMAX, ROWS, DQMODE, true>(op, acc, consts, cols, d, label, dq, row, row_out);
-    } else {
-      for (int64_t r = row; r < n; ++r) process_rows<Op, DMAX, 1, DQMODE, false>(op, acc, consts, cols, d, label, dq, r, row_out);
-    }
-  }
-
-  // ---- CTA reduction: shuffle inside each warp, then one shared-memory hop across the 8 warps
   __shared__ double s_warp[(kBlock / 32) * NACC];
   __shared__ bool s_last;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -162,6 +136,129 @@ __global__ void __launch_bounds__(kBlock, (DMAX * ROWS >= 64 ? 1 : (DMAX <= 2 ? 
   }
   if (threadIdx.x == 0) *ticket = 0u;  // ready for the next launch on this stream
   xr_publish(ep, result, NACC, dev_consts, [](int k) { return Op::kind(k); });
+}
+
+template <class Op, int DMAX, int ROWS, int DQMODE>
+__global__ void __launch_bounds__(kBlock, (DMAX * ROWS >= 64 ? 1 : (DMAX <= 2 ? 4 : (DMAX == 4 ? 3 : 2))))
+    stream_reduce_kernel(const Op op, const ColTable cols, const int d, const double* __restrict__ label,
+                         const DqArgs dq, const int64_t n, const double* __restrict__ dev_consts,
+                         double* __restrict__ row_out, double* __restrict__ partials, unsigned int* __restrict__ ticket,
+                         double* __restrict__ result, const XrEpilogue ep) {
+  constexpr int NACC = Op::NACC;
+  double acc[NACC];
+#pragma unroll
+  for (int k = 0; k < NACC; ++k) acc[k] = Op::identity(k);
+  double consts[Op::NCONST > 0 ? Op::NCONST : 1];
+#pragma unroll
+  for (int k = 0; k < Op::NCONST; ++k) consts[k] = __ldg(dev_consts + k);
+
+  // Full tiles first, with no tail test inside the loop so that it can be unrolled and the loads of the next tile are
+  // in flight during the arithmetic of this one (the ragged end of the table is one extra partial tile below).
+  const int64_t tile_rows = static_cast<int64_t>(kBlock) * ROWS;
+  const int64_t full_tiles = n / tile_rows;
+#pragma unroll (DMAX >= 32 ? 1 : 2)
+  for (int64_t tile = blockIdx.x; tile < full_tiles; tile += gridDim.x) {
+    const int64_t row = tile * tile_rows + static_cast<int64_t>(threadIdx.x) * ROWS;
+    process_rows<Op, DMAX, ROWS, DQMODE, true>(op, acc, consts, cols, d, label, dq, row, row_out);
+  }
+  if (full_tiles * tile_rows < n && static_cast<int64_t>(blockIdx.x) == full_tiles % gridDim.x) {
+    const int64_t row = full_tiles * tile_rows + static_cast<int64_t>(threadIdx.x) * ROWS;
+    if (row + ROWS <= n) {
+      process_rows<Op, DMAX, ROWS, DQMODE, true>(op, acc, consts, cols, d, label, dq, row, row_out);
+    } else {
+      for (int64_t r = row; r < n; ++r) process_rows<Op, DMAX, 1, DQMODE, false>(op, acc, consts, cols, d, label, dq, r, row_out);
+    }
+  }
+
+  reduce_and_publish<Op>(acc, dev_consts, partials, ticket, result, ep);
+}
+
+// The same pass for the lab's own shape -- ONE int32 feature column (guest) + the label, DQ in the lab layout or off --
+// software-pipelined: every thread holds NV 8-row vectors of the tile it works on and has the NV vectors of its next
+// tile in flight while it does the arithmetic, one 256-thread CTA per SM.  tools/k2_variants.cu (10^8 rows of 12 B):
+// the grid-strided shape above 0.187-0.190 ms at its best occupancy, this one 0.174-0.175 ms with 24 rows per thread
+// (a pure read of the same bytes: 0.170-0.172 ms).  Fewer, fatter threads: the bytes in flight (2 x 24 rows x 12 B x
+// 256 threads = 147 KB per SM) do not depend on the warp scheduler finding another warp to run.
+template <class Op, int NV, int DQMODE>
+__global__ void __launch_bounds__(kBlock, 1)
+    stream_pipe_kernel(const Op op, const int* __restrict__ col0, const double* __restrict__ label, const DqThresholds t,
+                       const int64_t n, const double* __restrict__ dev_consts, double* __restrict__ row_out,
+                       double* __restrict__ partials, unsigned int* __restrict__ ticket, double* __restrict__ result,
+                       const XrEpilogue ep) {
+  static_assert(DQMODE == kDqNone || DQMODE == kDqLab, "separate DQ columns take the grid-strided kernel");
+  constexpr int NACC = Op::NACC;
+  double acc[NACC];
+#pragma unroll
+  for (int k = 0; k < NACC; ++k) acc[k] = Op::identity(k);
+  double consts[Op::NCONST > 0 ? Op::NCONST : 1];
+#pragma unroll
+  for (int k = 0; k < Op::NCONST; ++k) consts[k] = __ldg(dev_consts + k);
+
+  constexpr int64_t kTile = static_cast<int64_t>(kBlock) * 8 * NV;
+  const int64_t full_tiles = n / kTile;
+  auto load = [&](int64_t tile, int (&g)[NV][8], double (&y)[NV][8]) {
+#pragma unroll
+    for (int v = 0; v < NV; ++v) {
+      const int64_t row = tile * kTile + (static_cast<int64_t>(v) * kBlock + threadIdx.x) * 8;
+      load_i32<8, true>(col0, row, g[v]);
+      if (label != nullptr) {
+        load_f64<8, true>(label, row, y[v]);
+      } else {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) y[v][k] = 0.0;
+      }
+    }
+  };
+  auto compute = [&](int64_t tile, const int (&g)[NV][8], const double (&y)[NV][8]) {
+#pragma unroll
+    for (int v = 0; v < NV; ++v) {
+      double o[8];
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        const bool keep = DQMODE == kDqLab ? dq_keep(g[v][k], y[v][k], t) : true;
+        const double xr[1] = {keep ? static_cast<double>(g[v][k]) : 0.0};
+        o[k] = op.row(acc, consts, xr, keep ? y[v][k] : 0.0, keep, 1);
+      }
+      if (Op::HAS_OUT && row_out != nullptr) {
+        const int64_t row = tile * kTile + (static_cast<int64_t>(v) * kBlock + threadIdx.x) * 8;
+#pragma unroll
+        for (int k = 0; k < 8; k += 2) stg_stream_d2(row_out + row + k, make_double2(o[k], o[k + 1]));
+      }
+    }
+  };
+  int64_t tile = blockIdx.x;
+  if (tile < full_tiles) {
+    int g[NV][8];
+    double y[NV][8];
+    load(tile, g, y);
+    for (int64_t nxt = tile + gridDim.x; nxt < full_tiles; nxt += gridDim.x) {
+      int gn[NV][8];
+      double yn[NV][8];
+      load(nxt, gn, yn);  // in flight during the arithmetic below
+      compute(tile, g, y);
+#pragma unroll
+      for (int v = 0; v < NV; ++v)
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          g[v][k] = gn[v][k];
+          y[v][k] = yn[v][k];
+        }
+      tile = nxt;
+    }
+    compute(tile, g, y);
+  }
+  if (full_tiles * kTile < n && static_cast<int64_t>(blockIdx.x) == full_tiles % gridDim.x) {  // the ragged end, one row at a time
+    ColTable cols;
+    cols.ptr[0] = col0;
+    cols.i32_mask = 1u;
+    DqArgs dq;
+    dq.guest = col0;
+    dq.price = label;
+    dq.t = t;
+    for (int64_t r = full_tiles * kTile + threadIdx.x; r < n; r += kBlock)
+      process_rows<Op, 1, 1, DQMODE, false>(op, acc, consts, cols, 1, label, dq, r, row_out);
+  }
+  reduce_and_publish<Op>(acc, dev_consts, partials, ticket, result, ep);
 }
 
 }  // namespace dq4ml

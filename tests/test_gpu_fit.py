@@ -54,7 +54,11 @@ def test_wls_moments_vs_oracle(pkg, ctx, d, n):
     assert got[0] == ref[0] and got[1] == ref[1]  # survivor count is exact
     assert rel_err(got, ref) < 1e-11
     got2 = ml.wls_moments(ctx, dfeats, dprice, dq=(dfeats[0].clone(), dprice.clone()))  # DQ columns passed separately
-    assert got2.tobytes() == got.tobytes()
+    # same rows, same rules; at d = 1 the lab layout takes the software-pipelined kernel, whose threads own other rows
+    # than the grid-strided kernel's, so the sums may differ in the last bit
+    assert got2[0] == got[0] and rel_err(got2, got) < 1e-13
+    if d > 1:
+        assert got2.tobytes() == got.tobytes()
     no_dq = ml.wls_moments(ctx, dfeats, dprice)
     assert rel_err(no_dq, passes.wls_moments(feats, price, threads=4)) < 1e-11
     host = ml.wls_moments(ctx, feats, price, dq=(guest, price))  # host buffers through the same entry point

@@ -170,8 +170,172 @@ __global__ void __launch_bounds__(256) varG(const int* g, const double* p, long 
   finish(a, out);
 }
 
+// ---- round 2: what separates the shipped shape (C) from the pure read (E)?
+// the product's reduced predicate (three fp64 compares) and the same on the bit pattern of the price (integer compares)
+__device__ __forceinline__ bool keep3(int g, double p) { return !(p < 20.0) && !(p <= 0.0) && !(g < 14 && p > 90.0); }
+__device__ __forceinline__ unsigned long long f64_key(unsigned long long b) {
+  if ((b << 1) == 0ULL) b = 0ULL;
+  return (b >> 63) ? ~b : (b | 0x8000000000000000ULL);
+}
+__device__ __forceinline__ bool keep_bits(int g, double p) {
+  const unsigned long long b = (unsigned long long)__double_as_longlong(p);
+  if ((b & 0x7fffffffffffffffULL) > 0x7ff0000000000000ULL) return true;
+  const unsigned long long k = f64_key(b);
+  const unsigned long long k20 = f64_key((unsigned long long)__double_as_longlong(20.0)), k90 = f64_key((unsigned long long)__double_as_longlong(90.0));
+  return !(k < k20) && !(k <= 0x8000000000000000ULL) && !(g < 14 && k > k90);
+}
+template <int PRED>
+__device__ __forceinline__ void add_row2(Acc& a, int g, double p) {
+  const bool k = PRED == 0 ? keep3(g, p) : keep_bits(g, p);
+  const double x = k ? (double)g : 0.0, y = k ? p : 0.0;
+  a.n += k ? 1.0 : 0.0;
+  a.sy += y;
+  a.syy = fma(y, y, a.syy);
+  a.sx += x;
+  a.sxy = fma(x, y, a.sxy);
+  a.sxx = fma(x, x, a.sxx);
+}
+// H: C with the reduced predicate (PRED 0) or the integer predicate (PRED 1)
+template <int PRED>
+__global__ void __launch_bounds__(256) varH(const int* g, const double* p, long long n, double* out) {
+  Acc a{};
+  const long long tiles = n / 2048;
+  for (long long t = blockIdx.x; t < tiles; t += gridDim.x) {
+    const long long r = t * 2048 + threadIdx.x * 8;
+    int gv[8];
+    double p0[4], p1[4];
+    ld_i8(g + r, gv);
+    ld_d4(p + r, p0);
+    ld_d4(p + r + 4, p1);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) add_row2<PRED>(a, gv[k], p0[k]);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) add_row2<PRED>(a, gv[4 + k], p1[k]);
+  }
+  finish(a, out);
+}
+// I: H, software-pipelined: the next tile's loads are issued before this tile's arithmetic
+template <int PRED>
+__global__ void __launch_bounds__(256) varI(const int* g, const double* p, long long n, double* out) {
+  Acc a{};
+  const long long tiles = n / 2048;
+  long long t = blockIdx.x;
+  if (t >= tiles) { finish(a, out); return; }
+  int gv[8];
+  double p0[4], p1[4];
+  long long r = t * 2048 + threadIdx.x * 8;
+  ld_i8(g + r, gv); ld_d4(p + r, p0); ld_d4(p + r + 4, p1);
+  for (t += gridDim.x; t < tiles; t += gridDim.x) {
+    r = t * 2048 + threadIdx.x * 8;
+    int gn[8];
+    double n0[4], n1[4];
+    ld_i8(g + r, gn); ld_d4(p + r, n0); ld_d4(p + r + 4, n1);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) add_row2<PRED>(a, gv[k], p0[k]);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) add_row2<PRED>(a, gv[4 + k], p1[k]);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) gv[k] = gn[k];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) { p0[k] = n0[k]; p1[k] = n1[k]; }
+  }
+#pragma unroll
+  for (int k = 0; k < 4; ++k) add_row2<PRED>(a, gv[k], p0[k]);
+#pragma unroll
+  for (int k = 0; k < 4; ++k) add_row2<PRED>(a, gv[4 + k], p1[k]);
+  finish(a, out);
+}
+// J: 16 rows per thread per tile
+template <int PRED>
+__global__ void __launch_bounds__(256) varJ(const int* g, const double* p, long long n, double* out) {
+  Acc a{};
+  const long long tiles = n / 4096;
+  for (long long t = blockIdx.x; t < tiles; t += gridDim.x) {
+    const long long r = t * 4096 + threadIdx.x * 16;
+    int g0[8], g1[8];
+    double p0[4], p1[4], p2[4], p3[4];
+    ld_i8(g + r, g0); ld_i8(g + r + 8, g1);
+    ld_d4(p + r, p0); ld_d4(p + r + 4, p1); ld_d4(p + r + 8, p2); ld_d4(p + r + 12, p3);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) add_row2<PRED>(a, g0[k], p0[k]);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) add_row2<PRED>(a, g0[4 + k], p1[k]);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) add_row2<PRED>(a, g1[k], p2[k]);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) add_row2<PRED>(a, g1[4 + k], p3[k]);
+  }
+  finish(a, out);
+}
+// K: pipelined, NV 8-row vectors per thread and tile (NV = 2: 16 rows), BLK threads per CTA
+template <int NV, int BLK>
+__global__ void __launch_bounds__(BLK) varK(const int* g, const double* p, long long n, double* out) {
+  Acc a{};
+  constexpr long long kTile = static_cast<long long>(BLK) * 8 * NV;
+  const long long tiles = n / kTile;
+  long long t = blockIdx.x;
+  if (t >= tiles) { finish(a, out); return; }
+  int gv[NV][8];
+  double pv[NV][8];
+  auto load = [&](long long tt, int (&G)[NV][8], double (&P)[NV][8]) {
+#pragma unroll
+    for (int v = 0; v < NV; ++v) {
+      const long long r = tt * kTile + (static_cast<long long>(v) * BLK + threadIdx.x) * 8;
+      ld_i8(g + r, G[v]);
+      double lo[4], hi[4];
+      ld_d4(p + r, lo);
+      ld_d4(p + r + 4, hi);
+#pragma unroll
+      for (int k = 0; k < 4; ++k) { P[v][k] = lo[k]; P[v][4 + k] = hi[k]; }
+    }
+  };
+  auto compute = [&](const int (&G)[NV][8], const double (&P)[NV][8]) {
+#pragma unroll
+    for (int v = 0; v < NV; ++v)
+#pragma unroll
+      for (int k = 0; k < 8; ++k) add_row2<0>(a, G[v][k], P[v][k]);
+  };
+  load(t, gv, pv);
+  for (t += gridDim.x; t < tiles; t += gridDim.x) {
+    int gn[NV][8];
+    double pn[NV][8];
+    load(t, gn, pn);
+    compute(gv, pv);
+#pragma unroll
+    for (int v = 0; v < NV; ++v)
+#pragma unroll
+      for (int k = 0; k < 8; ++k) { gv[v][k] = gn[v][k]; pv[v][k] = pn[v][k]; }
+  }
+  compute(gv, pv);
+  finish(a, out);
+}
+template <class K>
+void run_blk(const char* name, K kernel, int per_sm, int blk, const int* g, const double* p, long long n, double* out);
+
+// E8: pure read with the 256-bit loads of C
+__global__ void __launch_bounds__(256) varE8(const int* g, const double* p, long long n, double* out) {
+  double s = 0.0;
+  int q = 0;
+  const long long tiles = n / 2048;
+  for (long long t = blockIdx.x; t < tiles; t += gridDim.x) {
+    const long long r = t * 2048 + threadIdx.x * 8;
+    int gv[8];
+    double p0[4], p1[4];
+    ld_i8(g + r, gv); ld_d4(p + r, p0); ld_d4(p + r + 4, p1);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) q ^= gv[k];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) s += p0[k] + p1[k];
+  }
+  if (s == 1.2345 && q == 77) out[0] = s;
+}
+
 template <class K>
 void run(const char* name, K kernel, int per_sm, const int* g, const double* p, long long n, double* out) {
+  run_blk(name, kernel, per_sm, 256, g, p, n, out);
+}
+template <class K>
+void run_blk(const char* name, K kernel, int per_sm, int blk, const int* g, const double* p, long long n, double* out) {
   int sms = 0;
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, 0);
   cudaEvent_t e0, e1;
@@ -179,11 +343,11 @@ void run(const char* name, K kernel, int per_sm, const int* g, const double* p, 
   cudaEventCreate(&e1);
   float best = 1e30f, sum = 0.f;
   const int reps = 20;
-  for (int i = 0; i < 3; ++i) kernel<<<sms * per_sm, 256>>>(g, p, n, out);
+  for (int i = 0; i < 3; ++i) kernel<<<sms * per_sm, blk>>>(g, p, n, out);
   for (int i = 0; i < reps; ++i) {
     cudaMemsetAsync(out, 0, 64);
     cudaEventRecord(e0);
-    kernel<<<sms * per_sm, 256>>>(g, p, n, out);
+    kernel<<<sms * per_sm, blk>>>(g, p, n, out);
     cudaEventRecord(e1);
     cudaEventSynchronize(e1);
     float ms;
@@ -215,6 +379,38 @@ int main(int argc, char** argv) {
   cudaMalloc(&out, 64);
   fill<<<148 * 8, 256>>>(g, p, n);
   cudaDeviceSynchronize();
+  if (argc > 3) {  // pipelined shapes
+    for (int per_sm : {1, 2, 3, 4}) {
+      run_blk("K_pipe_8rows_256thr", varK<1, 256>, per_sm, 256, g, p, n, out);
+      run_blk("K_pipe_16rows_256thr", varK<2, 256>, per_sm, 256, g, p, n, out);
+      run_blk("K_pipe_24rows_256thr", varK<3, 256>, per_sm, 256, g, p, n, out);
+      run_blk("K_pipe_8rows_512thr", varK<1, 512>, per_sm, 512, g, p, n, out);
+      run_blk("K_pipe_16rows_512thr", varK<2, 512>, per_sm, 512, g, p, n, out);
+      run_blk("K_pipe_32rows_256thr", varK<4, 256>, per_sm, 256, g, p, n, out);
+      run_blk("K_pipe_24rows_384thr", varK<3, 384>, per_sm, 384, g, p, n, out);
+      run_blk("K_pipe_32rows_128thr", varK<4, 128>, per_sm, 128, g, p, n, out);
+      run_blk("K_pipe_48rows_128thr", varK<6, 128>, per_sm, 128, g, p, n, out);
+      run_blk("K_pipe_24rows_192thr", varK<3, 192>, per_sm, 192, g, p, n, out);
+      run_blk("K_pipe_8rows_384thr", varK<1, 384>, per_sm, 384, g, p, n, out);
+      run_blk("K_pipe_16rows_384thr", varK<2, 384>, per_sm, 384, g, p, n, out);
+      run("E8_pure_read_256bit", varE8, per_sm, g, p, n, out);
+      run("C_256bit", varC, per_sm, g, p, n, out);
+    }
+    return 0;
+  }
+  if (argc > 2) {  // round 2 variants only
+    for (int per_sm : {2, 3, 4, 5, 6}) {
+      run("C_256bit", varC, per_sm, g, p, n, out);
+      run("E8_pure_read_256bit", varE8, per_sm, g, p, n, out);
+      run("H_pred3", varH<0>, per_sm, g, p, n, out);
+      run("H_pred_int", varH<1>, per_sm, g, p, n, out);
+      run("I_pipelined_pred3", varI<0>, per_sm, g, p, n, out);
+      run("I_pipelined_pred_int", varI<1>, per_sm, g, p, n, out);
+      run("J_16rows_pred3", varJ<0>, per_sm, g, p, n, out);
+      run("J_16rows_pred_int", varJ<1>, per_sm, g, p, n, out);
+    }
+    return 0;
+  }
   for (int per_sm : {2, 3, 4, 5, 6, 7, 8}) {
     run("A_4rows", varA, per_sm, g, p, n, out);
     run("C_256bit", varC, per_sm, g, p, n, out);
