@@ -7,7 +7,5 @@ cut -c1-300 gpurun_out/p_bench_n1.json
 python bench.py --steps 5 --warmup 3 --no-extra --no-cpu-baseline > gpurun_out/p_plain.log 2>&1 && \
 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/p_launches.csv python bench.py --steps 5 --warmup 3 --no-extra --no-cpu-baseline > gpurun_out/p_ncu1.log 2>&1
 echo "launch list rc=$?"
-ncu --set full --section WarpStateStats --section SourceCounters --clock-control none --import-source on -k regex:stream_reduce_kernel -s 4 -c 2 -o gpurun_out/p_k2 python bench.py --steps 5 --warmup 3 --no-extra --no-cpu-baseline > gpurun_out/p_ncu2.log 2>&1
+ncu --set full --section WarpStateStats --section SourceCounters --clock-control none --import-source on -k regex:stream_pipe_kernel -s 4 -c 2 -o gpurun_out/p_k2 python bench.py --steps 5 --warmup 3 --no-extra --no-cpu-baseline > gpurun_out/p_ncu2.log 2>&1
 echo "k2 full rc=$?"
-ncu --set full --section WarpStateStats --section SourceCounters --clock-control none --import-source on -k regex:dq_filter_stream -s 1 -c 1 -o gpurun_out/p_filter python tools/bench_configs.py --config 5 --sizes 1000000000 --reps 1 > gpurun_out/p_ncu3.log 2>&1
-echo "filter full rc=$?"
