@@ -65,6 +65,31 @@ def test_wls_moments_vs_oracle(pkg, ctx, d, n):
     assert host.tobytes() == got.tobytes()
 
 
+@pytest.mark.parametrize("n", [6143, 6144, 6145, 12_288, 148 * 6144 - 1, 148 * 6144, 148 * 6144 + 1, 149 * 6144 + 777])
+def test_pipelined_single_column_kernel_tile_boundaries(pkg, ctx, n):
+    """The lab's shape (one int32 feature + label, DQ in the lab layout or off) takes the software-pipelined kernel:
+    6144-row tiles, one CTA per SM (148 on a B200), the ragged end row by row.  Moments, evaluation sums and the per-row
+    residuals on both sides of every boundary, against the oracle."""
+    from sparkdq4ml_b200 import ml
+    guest, price, feats = synth(n, 1, p_low=0.03, p_high=0.03)
+    dguest, dprice = to_dev(guest, price)
+    for dq_host, dq_dev in (((guest, price), (dguest, dprice)), (None, None)):
+        ref = passes.wls_moments(feats, price, dq=dq_host, threads=4)
+        got = ml.wls_moments(ctx, [dguest], dprice, dq=dq_dev)
+        assert got[0] == ref[0] and rel_err(got, ref) < 1e-11
+        assert ml.wls_moments(ctx, [dguest], dprice, dq=dq_dev).tobytes() == got.tobytes()  # fixed-order reduction
+    cols = {"guest": dguest, "label": dprice}
+    df = pkg.VectorAssembler().setInputCols(["guest"]).transform(pkg.Frame(ctx, cols).with_fused_dq("guest", "label"))
+    model = pkg.LinearRegression().setMaxIter(40).setRegParam(1.0).setElasticNetParam(1.0).fit(df)
+    keep = np.array([bool(passes.lib().orc_dq_keep(int(a), float(b))) for a, b in zip(guest, price)])
+    res_ref = price - (guest * model.coefficients()[0] + model.intercept())
+    ev = model.evaluate(df, want_residuals=True)
+    res = ev.residuals().cpu().numpy()
+    np.testing.assert_allclose(res[keep], res_ref[keep], rtol=0, atol=1e-9 * float(np.abs(price).max()))
+    assert np.all(res[~keep] == 0.0) and ev.numInstances() == int(keep.sum())
+    assert rel_err(ev.rootMeanSquaredError(), float(np.sqrt(np.mean(res_ref[keep] ** 2)))) < 1e-10
+
+
 def test_wls_moments_empty_and_all_dropped(pkg, ctx):
     from sparkdq4ml_b200 import ml
     g = torch.zeros(0, dtype=torch.int32, device="cuda")

@@ -1,5 +1,4 @@
 #!/bin/bash
 set -x
 mkdir -p gpurun_out
-timeout 1500 python -m pytest tests -m gpu -q 2>&1 | tail -30 > gpurun_out/y2_fail.txt
-cat gpurun_out/y2_fail.txt | cut -c1-250
+timeout 900 python -m pytest tests/test_gpu_fit.py -m gpu -x -q -k "tile_boundaries or wls_moments or lab_app or config2" 2>&1 | tail -15 | cut -c1-250
