@@ -8,6 +8,7 @@
 #include <cstdlib>
 #include <map>
 #include <mutex>
+#include <type_traits>
 
 #include "kernels.hpp"
 #include "ops.cuh"
@@ -55,9 +56,26 @@ struct PassArgs {
   cudaStream_t stream;
 };
 
-template <class Op, int DMAX, int ROWS, int DQMODE>
+// A table whose shape is known at compile time (every column of the bucket present, at most one int32 column, in
+// position 0 or 1): the loss/gradient, summarizer, huber, evaluation and gradient-group passes then run with a load
+// phase without per-column tests (stream_reduce.cuh, DENSE).  Returns 0, or 1 + the bit mask of the int32 columns.
+inline int dense_id(const PassArgs& a, int dmax) {
+  static const char* off = std::getenv("DQ4ML_STREAM_DENSE");  // DQ4ML_STREAM_DENSE=0: the general load phase (A/B)
+  if (off != nullptr && off[0] == '0') return 0;
+  if (a.d != dmax || a.cols.i32_mask > 2u) return 0;
+  return 1 + static_cast<int>(a.cols.i32_mask);
+}
+template <class Op, int DMAX>
+constexpr bool kDenseOp = std::is_same<Op, LsqOp<DMAX>>::value || std::is_same<Op, SummCoreOp<DMAX>>::value ||
+                          std::is_same<Op, EvalOp<DMAX>>::value || std::is_same<Op, HuberOp<DMAX>>::value ||
+                          std::is_same<Op, GradOp<DMAX>>::value;
+template <class Op, int DMAX>
+constexpr bool kDenseWeightedOp = std::is_same<Op, LsqWOp<DMAX>>::value || std::is_same<Op, SummCoreWOp<DMAX>>::value ||
+                                  std::is_same<Op, HuberWOp<DMAX>>::value;
+
+template <class Op, int DMAX, int ROWS, int DQMODE, int DENSE = 0>
 cudaError_t launch_one(const Op& op, const PassArgs& a) {
-  auto kernel = stream_reduce_kernel<Op, DMAX, ROWS, DQMODE>;
+  auto kernel = stream_reduce_kernel<Op, DMAX, ROWS, DQMODE, DENSE>;
   static std::mutex mu;
   static std::map<int, int> blocks_per_sm;  // per device
   int dev = 0;
@@ -119,6 +137,15 @@ cudaError_t launch_mode(const Op& op, const PassArgs& a) {
   if constexpr (DMAX == 1) {
     if (pipe_takes(a)) return a.dq_mode == kDqLab ? launch_pipe<Op, kDqLab>(op, a) : launch_pipe<Op, kDqNone>(op, a);
   }
+  if constexpr ((DMAX == 32 || DMAX == 16 || DMAX == 8) && kDenseOp<Op, DMAX>) {
+    const int dense = dense_id(a, DMAX);
+    if (dense == 2) {  // column 0 int32: the lab layout, or the same table without the rules
+      if (a.dq_mode == kDqLab) return launch_one<Op, DMAX, ROWS, kDqLab, 2>(op, a);
+      if (a.dq_mode == kDqNone) return launch_one<Op, DMAX, ROWS, kDqNone, 2>(op, a);
+    } else if (dense == 1 && a.dq_mode == kDqNone) {
+      return launch_one<Op, DMAX, ROWS, kDqNone, 1>(op, a);
+    }
+  }
   switch (a.dq_mode) {
     case kDqNone: return launch_one<Op, DMAX, ROWS, kDqNone>(op, a);
     case kDqSeparate: return launch_one<Op, DMAX, ROWS, kDqSeparate>(op, a);
@@ -129,6 +156,11 @@ cudaError_t launch_mode(const Op& op, const PassArgs& a) {
 // the weighted ops never see the lab layout (column 0 is the weight), so two DQ modes are enough
 template <class Op, int DMAX, int ROWS>
 cudaError_t launch_mode2(const Op& op, const PassArgs& a) {
+  if constexpr ((DMAX == 8 || DMAX == 16 || DMAX == 32) && kDenseWeightedOp<Op, DMAX>) {  // weight, then all fp64 or guest (int32) first
+    const int dense = dense_id(a, DMAX);
+    if (dense == 1) return a.dq_mode == kDqNone ? launch_one<Op, DMAX, ROWS, kDqNone, 1>(op, a) : launch_one<Op, DMAX, ROWS, kDqSeparate, 1>(op, a);
+    if (dense == 3) return a.dq_mode == kDqNone ? launch_one<Op, DMAX, ROWS, kDqNone, 3>(op, a) : launch_one<Op, DMAX, ROWS, kDqSeparate, 3>(op, a);
+  }
   if (a.dq_mode == kDqNone) return launch_one<Op, DMAX, ROWS, kDqNone>(op, a);
   return launch_one<Op, DMAX, ROWS, kDqSeparate>(op, a);
 }
@@ -171,7 +203,7 @@ cudaError_t launch_bucket_rows(StreamOpKind kind, const PassArgs& a, const void*
       if constexpr (DMAX <= 4) return launch_mode<SummFullOp<DMAX>, DMAX, ROWS>(SummFullOp<DMAX>{}, a);
       return cudaErrorInvalidValue;
     case kOpEval: return launch_mode<EvalOp<DMAX>, DMAX, ROWS>(make_eval<DMAX>(*static_cast<const EvalConsts*>(host_consts)), a);
-    case kOpGrad: return launch_one<GradOp<DMAX>, DMAX, ROWS, kDqNone>(GradOp<DMAX>{}, a);
+    case kOpGrad: return launch_mode<GradOp<DMAX>, DMAX, ROWS>(GradOp<DMAX>{}, a);  // always kDqNone
     case kOpSummCoreW:
       if constexpr (DMAX >= 2) return launch_mode2<SummCoreWOp<DMAX>, DMAX, ROWS>(SummCoreWOp<DMAX>{}, a);
       return cudaErrorInvalidValue;
@@ -233,12 +265,20 @@ cudaError_t launch_stream_pass(StreamOpKind op, const DeviceCols& cols, const do
   a.scratch = scratch;
   a.stream = stream;
   cudaError_t e;
-  if (lane_group_takes(op, cols.n)) {  // 9..12 columns, 8..16 weighted features: the lane-group kernels (lane_group_kernels.cu)
+  // a full bucket (8, 16 or 32 table columns, at most one int32 column in position 0 or 1) runs the generic kernel with
+  // its compile-time load phase: 1.08-1.11 of the measured copy peak, ahead of the lane-group / lane-pair kernels
+  const bool weighted_op = op == kOpLsqW || op == kOpSummCoreW || op == kOpHuberW;
+  const bool dense_family = weighted_op || op == kOpLsq || op == kOpSummCore || op == kOpEval || op == kOpHuber || op == kOpGrad;
+  const bool dense_mode = weighted_op ? a.dq_mode != kDqLab : a.dq_mode != kDqSeparate;
+  const bool dense_mask = weighted_op ? (a.cols.i32_mask == 0u || a.cols.i32_mask == 2u) : a.cols.i32_mask <= 1u;
+  const bool full_bucket = dense_family && dense_mode && dense_mask && (cols.n == 8 || cols.n == 16 || cols.n == 32) &&
+                           dense_id(a, cols.n) != 0 && !(a.dq_mode == kDqLab && a.cols.i32_mask != 1u);
+  if (!full_bucket && lane_group_takes(op, cols.n)) {  // 9..12 columns, 8..16 weighted features: the lane-group kernels (lane_group_kernels.cu)
     e = launch_lane_group(op, a.cols, a.d, a.label, a.dq, a.dq_mode, a.n, host_consts, row_out, scratch, stream);
     if (e == cudaSuccess) ++*launches;
     return e;
   }
-  if ((op == kOpLsq || op == kOpSummCore) && cols.n > 16) {  // 17..32 columns: the lane-pair / lane-quad kernels (pair32_kernels.cu)
+  if (!full_bucket && (op == kOpLsq || op == kOpSummCore) && cols.n > 16) {  // 17..32 columns: the lane-pair / lane-quad kernels (pair32_kernels.cu)
     e = launch_pair32(op == kOpLsq ? kPairLsq : kPairSumm, a.cols, a.d, a.label, a.dq, a.dq_mode, a.n,
                       static_cast<const LsqConsts*>(host_consts), scratch, stream);
     if (e == cudaSuccess) ++*launches;

@@ -30,7 +30,13 @@ constexpr int kDqNone = 0;      // every row counts
 constexpr int kDqSeparate = 1;  // guest/price are loaded as extra columns
 constexpr int kDqLab = 2;       // the lab's layout: guest is feature column 0 (int32) and price is the label -> no extra bytes
 
-template <class Op, int DMAX, int ROWS, int DQMODE, bool VEC>
+// DENSE: what the table looks like is known at compile time -- 0 = nothing (d and the column types are tested per
+// column and tile); otherwise all DMAX columns are there and DENSE - 1 is the bit mask of the int32 columns: 1 = all
+// fp64, 2 = column 0 is int32 (the lab's layout: guest first), 3 = column 1 is int32 (weighted: weight, guest, ...).
+// The tests of the general form put ~14 instructions between two loads of a tile; with them gone a thread issues its
+// 17 loads back to back: 10^9 rows x 16 columns 21.0 -> 18.3 ms per pass, 0.96 -> 1.10 of the measured copy peak
+// (tools/k4_variants.cu reaches the same 1.11 with this shape outside the library, a pure read 1.10-1.11).
+template <class Op, int DMAX, int ROWS, int DQMODE, bool VEC, int DENSE = 0>
 __device__ __forceinline__ void process_rows(const Op& op, double (&acc)[Op::NACC], const double* consts,
                                              const ColTable& cols, int d,
                                              const double* __restrict__ label, const DqArgs& dq, int64_t row,
@@ -45,8 +51,8 @@ __device__ __forceinline__ void process_rows(const Op& op, double (&acc)[Op::NAC
   }
 #pragma unroll
   for (int j = 0; j < DMAX; ++j) {
-    if (j < d) {
-      if ((cols.i32_mask >> j) & 1u) {
+    if (DENSE != 0 || j < d) {
+      if (DENSE == 0 ? ((cols.i32_mask >> j) & 1u) != 0u : ((((DENSE - 1) >> j) & 1) != 0)) {
         int t[ROWS];
         load_i32<ROWS, VEC>(static_cast<const int*>(cols.ptr[j]), row, t);
 #pragma unroll
@@ -138,7 +144,7 @@ __device__ __forceinline__ void reduce_and_publish(double (&acc)[Op::NACC], cons
   xr_publish(ep, result, NACC, dev_consts, [](int k) { return Op::kind(k); });
 }
 
-template <class Op, int DMAX, int ROWS, int DQMODE>
+template <class Op, int DMAX, int ROWS, int DQMODE, int DENSE = 0>
 __global__ void __launch_bounds__(kBlock, (DMAX * ROWS >= 64 ? 1 : (DMAX <= 2 ? 4 : (DMAX == 4 ? 3 : 2))))
     stream_reduce_kernel(const Op op, const ColTable cols, const int d, const double* __restrict__ label,
                          const DqArgs dq, const int64_t n, const double* __restrict__ dev_consts,
@@ -159,12 +165,12 @@ __global__ void __launch_bounds__(kBlock, (DMAX * ROWS >= 64 ? 1 : (DMAX <= 2 ? 
 #pragma unroll (DMAX >= 32 ? 1 : 2)
   for (int64_t tile = blockIdx.x; tile < full_tiles; tile += gridDim.x) {
     const int64_t row = tile * tile_rows + static_cast<int64_t>(threadIdx.x) * ROWS;
-    process_rows<Op, DMAX, ROWS, DQMODE, true>(op, acc, consts, cols, d, label, dq, row, row_out);
+    process_rows<Op, DMAX, ROWS, DQMODE, true, DENSE>(op, acc, consts, cols, d, label, dq, row, row_out);
   }
   if (full_tiles * tile_rows < n && static_cast<int64_t>(blockIdx.x) == full_tiles % gridDim.x) {
     const int64_t row = full_tiles * tile_rows + static_cast<int64_t>(threadIdx.x) * ROWS;
     if (row + ROWS <= n) {
-      process_rows<Op, DMAX, ROWS, DQMODE, true>(op, acc, consts, cols, d, label, dq, row, row_out);
+      process_rows<Op, DMAX, ROWS, DQMODE, true, DENSE>(op, acc, consts, cols, d, label, dq, row, row_out);
     } else {
       for (int64_t r = row; r < n; ++r) process_rows<Op, DMAX, 1, DQMODE, false>(op, acc, consts, cols, d, label, dq, r, row_out);
     }
