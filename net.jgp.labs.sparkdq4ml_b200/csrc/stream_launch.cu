@@ -58,13 +58,20 @@ struct PassArgs {
 
 // A table whose shape is known at compile time (every column of the bucket present, at most one int32 column, in
 // position 0 or 1): the loss/gradient, summarizer, huber, evaluation and gradient-group passes then run with a load
-// phase without per-column tests (stream_reduce.cuh, DENSE).  Returns 0, or 1 + the bit mask of the int32 columns.
+// phase without per-column tests (stream_reduce.cuh, DENSE).  Returns 0, or 1 + the bit mask of the int32 columns for a
+// full bucket, 5 + the mask for a narrower table of the same column types.
 inline int dense_id(const PassArgs& a, int dmax) {
   static const char* off = std::getenv("DQ4ML_STREAM_DENSE");  // DQ4ML_STREAM_DENSE=0: the general load phase (A/B)
   if (off != nullptr && off[0] == '0') return 0;
-  if (a.d != dmax || a.cols.i32_mask > 2u) return 0;
-  return 1 + static_cast<int>(a.cols.i32_mask);
+  if (a.d > dmax || a.cols.i32_mask > 2u) return 0;
+  return (a.d == dmax ? 1 : 5) + static_cast<int>(a.cols.i32_mask);
 }
+// ops whose narrower tables also gain from compile-time column types (the width test stays): the dot-product ops
+template <class Op, int DMAX>
+constexpr bool kPartialOp = std::is_same<Op, LsqOp<DMAX>>::value || std::is_same<Op, EvalOp<DMAX>>::value ||
+                            std::is_same<Op, HuberOp<DMAX>>::value || std::is_same<Op, GradOp<DMAX>>::value;
+template <class Op, int DMAX>
+constexpr bool kPartialWeightedOp = std::is_same<Op, LsqWOp<DMAX>>::value || std::is_same<Op, HuberWOp<DMAX>>::value;
 template <class Op, int DMAX>
 constexpr bool kDenseOp = std::is_same<Op, LsqOp<DMAX>>::value || std::is_same<Op, SummCoreOp<DMAX>>::value ||
                           std::is_same<Op, EvalOp<DMAX>>::value || std::is_same<Op, HuberOp<DMAX>>::value ||
@@ -145,6 +152,14 @@ cudaError_t launch_mode(const Op& op, const PassArgs& a) {
     } else if (dense == 1 && a.dq_mode == kDqNone) {
       return launch_one<Op, DMAX, ROWS, kDqNone, 1>(op, a);
     }
+    if constexpr ((DMAX == 32 || DMAX == 16) && kPartialOp<Op, DMAX>) {
+      if (dense == 6) {
+        if (a.dq_mode == kDqLab) return launch_one<Op, DMAX, ROWS, kDqLab, 6>(op, a);
+        if (a.dq_mode == kDqNone) return launch_one<Op, DMAX, ROWS, kDqNone, 6>(op, a);
+      } else if (dense == 5 && a.dq_mode == kDqNone) {
+        return launch_one<Op, DMAX, ROWS, kDqNone, 5>(op, a);
+      }
+    }
   }
   switch (a.dq_mode) {
     case kDqNone: return launch_one<Op, DMAX, ROWS, kDqNone>(op, a);
@@ -160,6 +175,10 @@ cudaError_t launch_mode2(const Op& op, const PassArgs& a) {
     const int dense = dense_id(a, DMAX);
     if (dense == 1) return a.dq_mode == kDqNone ? launch_one<Op, DMAX, ROWS, kDqNone, 1>(op, a) : launch_one<Op, DMAX, ROWS, kDqSeparate, 1>(op, a);
     if (dense == 3) return a.dq_mode == kDqNone ? launch_one<Op, DMAX, ROWS, kDqNone, 3>(op, a) : launch_one<Op, DMAX, ROWS, kDqSeparate, 3>(op, a);
+    if constexpr ((DMAX == 16 || DMAX == 32) && kPartialWeightedOp<Op, DMAX>) {
+      if (dense == 5) return a.dq_mode == kDqNone ? launch_one<Op, DMAX, ROWS, kDqNone, 5>(op, a) : launch_one<Op, DMAX, ROWS, kDqSeparate, 5>(op, a);
+      if (dense == 7) return a.dq_mode == kDqNone ? launch_one<Op, DMAX, ROWS, kDqNone, 7>(op, a) : launch_one<Op, DMAX, ROWS, kDqSeparate, 7>(op, a);
+    }
   }
   if (a.dq_mode == kDqNone) return launch_one<Op, DMAX, ROWS, kDqNone>(op, a);
   return launch_one<Op, DMAX, ROWS, kDqSeparate>(op, a);
@@ -265,14 +284,25 @@ cudaError_t launch_stream_pass(StreamOpKind op, const DeviceCols& cols, const do
   a.scratch = scratch;
   a.stream = stream;
   cudaError_t e;
-  // a full bucket (8, 16 or 32 table columns, at most one int32 column in position 0 or 1) runs the generic kernel with
-  // its compile-time load phase: 1.08-1.11 of the measured copy peak, ahead of the lane-group / lane-pair kernels
+  // Which tables the generic kernel takes with a compile-time load phase (at most one int32 column, in position 0, or 1
+  // behind a weight): a full bucket of 8, 16 or 32 columns for every op (1.07-1.13 of the measured copy peak, ahead of
+  // the lane-group / lane-pair kernels); narrower tables for the dot-product ops where they measured ahead
+  // (profiles/r2_bucket_sweep_dense.jsonl) -- 9..15 and 21..31 columns for the loss/gradient pass (17..20 stay lane
+  // pairs), 9..31 for evaluation, huber and the gradient groups, weighted loss/gradient and huber over 9..14 and 17..30
+  // features.  The summarizer's narrower tables stay on the lane-group / lane-pair kernels.
   const bool weighted_op = op == kOpLsqW || op == kOpSummCoreW || op == kOpHuberW;
   const bool dense_family = weighted_op || op == kOpLsq || op == kOpSummCore || op == kOpEval || op == kOpHuber || op == kOpGrad;
   const bool dense_mode = weighted_op ? a.dq_mode != kDqLab : a.dq_mode != kDqSeparate;
   const bool dense_mask = weighted_op ? (a.cols.i32_mask == 0u || a.cols.i32_mask == 2u) : a.cols.i32_mask <= 1u;
-  const bool full_bucket = dense_family && dense_mode && dense_mask && (cols.n == 8 || cols.n == 16 || cols.n == 32) &&
-                           dense_id(a, cols.n) != 0 && !(a.dq_mode == kDqLab && a.cols.i32_mask != 1u);
+  const bool dense_ok = dense_family && dense_mode && dense_mask && dense_id(a, stream_bucket(cols.n > 0 ? cols.n : 1)) != 0 &&
+                        !(a.dq_mode == kDqLab && a.cols.i32_mask != 1u);
+  bool full_bucket = dense_ok && (cols.n == 8 || cols.n == 16 || cols.n == 32);
+  if (dense_ok && !full_bucket) {
+    const int w = cols.n;
+    if (op == kOpLsq) full_bucket = (w >= 9 && w <= 15) || (w >= 21 && w <= 31);
+    else if (op == kOpEval || op == kOpHuber || op == kOpGrad) full_bucket = w >= 9 && w <= 31;
+    else if (op == kOpLsqW || op == kOpHuberW) full_bucket = (w >= 10 && w <= 15) || (w >= 18 && w <= 31);
+  }
   if (!full_bucket && lane_group_takes(op, cols.n)) {  // 9..12 columns, 8..16 weighted features: the lane-group kernels (lane_group_kernels.cu)
     e = launch_lane_group(op, a.cols, a.d, a.label, a.dq, a.dq_mode, a.n, host_consts, row_out, scratch, stream);
     if (e == cudaSuccess) ++*launches;

@@ -36,6 +36,9 @@ constexpr int kDqLab = 2;       // the lab's layout: guest is feature column 0 (
 // The tests of the general form put ~14 instructions between two loads of a tile; with them gone a thread issues its
 // 17 loads back to back: 10^9 rows x 16 columns 21.0 -> 18.3 ms per pass, 0.96 -> 1.10 of the measured copy peak
 // (tools/k4_variants.cu reaches the same 1.11 with this shape outside the library, a pure read 1.10-1.11).
+// 5, 6, 7: the same column types (mask DENSE - 5) with fewer than DMAX columns: the width test stays, the type tests go
+// (loss/gradient at 12 / 14 / 28 columns: 1.05 / 1.08 / 1.06 against 0.94-1.01 / 0.93 / 0.89-0.96 on the lane-group
+// and lane-pair kernels; the width test costs the summarizer more than it gains, which keeps those kernels).
 template <class Op, int DMAX, int ROWS, int DQMODE, bool VEC, int DENSE = 0>
 __device__ __forceinline__ void process_rows(const Op& op, double (&acc)[Op::NACC], const double* consts,
                                              const ColTable& cols, int d,
@@ -51,8 +54,8 @@ __device__ __forceinline__ void process_rows(const Op& op, double (&acc)[Op::NAC
   }
 #pragma unroll
   for (int j = 0; j < DMAX; ++j) {
-    if (DENSE != 0 || j < d) {
-      if (DENSE == 0 ? ((cols.i32_mask >> j) & 1u) != 0u : ((((DENSE - 1) >> j) & 1) != 0)) {
+    if ((DENSE >= 1 && DENSE <= 3) || j < d) {
+      if (DENSE == 0 ? ((cols.i32_mask >> j) & 1u) != 0u : (((((DENSE - 1) & 3) >> j) & 1) != 0)) {
         int t[ROWS];
         load_i32<ROWS, VEC>(static_cast<const int*>(cols.ptr[j]), row, t);
 #pragma unroll
