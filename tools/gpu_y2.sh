@@ -1,8 +1,7 @@
 #!/bin/bash
-# GPU call: full-bucket and narrower dense load phases, final dispatch: parity, sweeps
+# GPU call: lane-group kernels with uniform pointer loads + select
 set -x
 mkdir -p gpurun_out
-timeout 1500 python -m pytest tests -m gpu -x -q 2>&1 | tail -2
-python tools/bucket_sweep.py --rows 200000000 --features 8,9,10,12,14,16,17,20,24,28,32 > gpurun_out/y_sweep_final.jsonl
-python tools/bucket_sweep.py --rows 200000000 --features 7,8,12,15,16,24,31 --weighted > gpurun_out/y_sweep_final_w.jsonl
-python tools/bucket_sweep.py --rows 200000000 --features 9,12,16,24,32 --loss huber > gpurun_out/y_sweep_final_h.jsonl
+timeout 1500 python -m pytest tests -m gpu -x -q -k "summarizer_and_lsq or by_column_bucket or weighted or huber" 2>&1 | tail -1
+python tools/bucket_sweep.py --rows 200000000 --features 9,10,12,14 > gpurun_out/y_sweep_uni.jsonl
+python tools/bucket_sweep.py --rows 200000000 --features 8,12,16 --weighted > gpurun_out/y_sweep_uni_w.jsonl
