@@ -231,11 +231,13 @@ def test_config3_shape_d16_owlqn_fused(pkg, ctx, parity_log, reg_param):
     check_fit(parity_log, f"config3_shape_reg{reg_param}", model, ref.coefficients, ref.intercept, ref.objective_history, RTOL)
 
 
-@pytest.mark.parametrize("d,n", [(9, 30_001), (10, 4_095), (12, 50_000), (14, 20_003), (20, 30_000), (24, 12_289), (28, 20_000)])
+@pytest.mark.parametrize("d,n", [(8, 20_001), (9, 30_001), (10, 4_095), (12, 50_000), (14, 20_003), (16, 40_003), (20, 30_000), (24, 12_289),
+                                 (28, 20_000), (32, 25_001)])
 def test_lbfgs_fit_and_evaluation_by_column_bucket(pkg, ctx, parity_log, d, n):
-    """One l-bfgs fit and one evaluation per kernel family of the streaming passes (9..12 columns: lane-group kernels,
-    13..16: generic bucket, 17..24: lane pairs / groups of four for the summarizer, 25..32: groups of four lanes): the
-    fit against the oracle, the evaluation's per-row residuals and metrics against numpy on the surviving rows."""
+    """One l-bfgs fit and one evaluation per kernel family of the streaming passes (full buckets of 8 / 16 / 32 columns:
+    generic kernel with the compile-time load phase; narrower tables: compile-time column types for the dot-product ops,
+    lane-group / lane-pair kernels for the summarizer and for 17..20 columns): the fit against the oracle, the
+    evaluation's per-row residuals and metrics against numpy on the surviving rows."""
     guest, price, feats = synth(n, d, p_low=0.03, p_high=0.03)
     params = dict(max_iter=30, reg_param=0.2, elastic_net_param=0.5, solver="l-bfgs")
     ref = spark_ml.linear_regression_fit(feats, price, spark_ml.LRParams(**params), dq=(guest, price), threads=4)
