@@ -1,4 +1,5 @@
 #!/bin/bash
 set -x
 mkdir -p gpurun_out
-timeout 900 python -m pytest tests/test_gpu_fit.py -m gpu -x -q -k "by_column_bucket" 2>&1 | tail -3
+python tools/fuzz_passes.py 120 7 2>&1 | tail -3 | tee gpurun_out/y_fuzz.json
+python tools/fuzz_passes.py 120 11 2>&1 | tail -3 | tee -a gpurun_out/y_fuzz.json
